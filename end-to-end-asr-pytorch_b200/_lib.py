@@ -1,0 +1,85 @@
+"""ctypes binding of csrc/libb2asr.so (the C ABI declared in include/b2asr.h).
+
+There is deliberately NO fallback: if the shared library is missing or was not built for
+sm_100a, importing a kernel raises.  Tensors cross the boundary as raw device pointers plus
+sizes/strides; the CUDA stream is torch's current stream so launches are stream-ordered and
+CUDA-graph capturable.
+"""
+import ctypes
+import os
+import re
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libb2asr.so")
+HEADER_PATH = os.path.join(_HERE, "..", "include", "b2asr.h")
+
+_lib = None
+
+c_p = ctypes.c_void_p
+c_i = ctypes.c_int
+c_i64 = ctypes.c_int64
+c_f = ctypes.c_float
+c_sz = ctypes.c_size_t
+
+# name -> (restype, argtypes); must list every symbol include/b2asr.h declares.
+_SIGNATURES = {
+    "b2asr_last_error": (ctypes.c_char_p, []),
+    "b2asr_version": (c_i, []),
+    "b2asr_arch": (c_i, []),
+    "b2asr_ctc_workspace_bytes": (c_sz, [c_i, c_i, c_i, c_i, c_i]),
+    "b2asr_ctc_loss_fwd_bwd": (c_i, [c_p, c_i64, c_i64, c_p, c_i64, c_p, c_p,
+                                     c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_f,
+                                     c_p, c_p, c_p, c_i64, c_i64, c_p, c_sz, c_p]),
+    "b2asr_rescale_if_needed": (c_i, [c_p, c_i64, c_p, c_f, c_p]),
+}
+
+
+class B2asrError(RuntimeError):
+    pass
+
+
+def declared_symbols():
+    """Every function name include/b2asr.h declares (used by the CPU-side ABI test)."""
+    text = open(HEADER_PATH).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(b2asr_[a-z0-9_]+)\s*\(", text)))
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise B2asrError(
+                "libb2asr.so is missing (%s). Build it with `python __graft_entry__.py build`; "
+                "there is no CPU or PyTorch fallback for the CUDA hot path." % LIB_PATH)
+        L = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def check(rc, what):
+    if rc != 0:
+        msg = lib().b2asr_last_error().decode("utf-8", "replace")
+        if rc in (-1, -2, -3):
+            raise ValueError("%s failed (%d): %s" % (what, rc, msg))
+        raise B2asrError("%s failed (%d): %s" % (what, rc, msg))
+
+
+def stream_ptr():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def ptr(t):
+    return 0 if t is None else t.data_ptr()
+
+
+def require_cuda(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise B2asrError("b2asr kernels need CUDA tensors; got a %s tensor (no CPU fallback)" % t.device)

@@ -1,0 +1,88 @@
+// Shared device/host helpers for the b2asr sm_100a kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+
+#include "../../include/b2asr.h"
+
+namespace b2asr {
+
+// ---- error plumbing (host) -------------------------------------------------
+void set_error(const char* fmt, ...);
+int  cuda_fail(cudaError_t e, const char* what);
+
+#define B2_CUDA_TRY(expr)                                             \
+  do {                                                                \
+    cudaError_t e__ = (expr);                                         \
+    if (e__ != cudaSuccess) return ::b2asr::cuda_fail(e__, #expr);    \
+  } while (0)
+
+#define B2_REQUIRE(cond, code, ...)                                   \
+  do {                                                                \
+    if (!(cond)) { ::b2asr::set_error(__VA_ARGS__); return (code); }  \
+  } while (0)
+
+static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// ---- device helpers ----------------------------------------------------------
+constexpr float kNeg   = -1.0e30f;           // finite stand-in for log(0): never yields inf-inf
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2   = 0.6931471805599453f;
+constexpr unsigned kFull = 0xffffffffu;
+
+__device__ __forceinline__ float ex2(float x) {      // MUFU.EX2, 2 ulp, flushes to 0 for very negative x
+  float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y;
+}
+__device__ __forceinline__ float lg2(float x) {      // MUFU.LG2
+  float y; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y;
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+  float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y;
+}
+
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(kFull, v, o));
+  return v;
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFull, v, o);
+  return v;
+}
+
+// cp.async (LDGSTS) 16-byte copy global -> shared, generic proxy.
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
+  unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// thread-block cluster helpers
+__device__ __forceinline__ unsigned cluster_ctarank() {
+  unsigned r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r;
+}
+__device__ __forceinline__ unsigned cluster_nctarank() {
+  unsigned r; asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r)); return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// map a local shared-memory address to the same offset in CTA `rank` of the cluster
+__device__ __forceinline__ unsigned dsmem_addr(const void* local_smem, unsigned rank) {
+  unsigned a = (unsigned)__cvta_generic_to_shared(local_smem), r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ float ld_dsmem_f32(unsigned addr) {
+  float v; asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory"); return v;
+}
+__device__ __forceinline__ void st_dsmem_f32(unsigned addr, float v) {
+  asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+
+}  // namespace b2asr
