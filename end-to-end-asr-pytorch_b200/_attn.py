@@ -1,0 +1,51 @@
+"""Raw (no-autograd) Python entry points of the attention kernels; autograd wiring lives in asr.py."""
+import torch
+
+from . import _lib
+
+MODES = {"dot": 0, "loc": 1}
+
+
+def lens_i32(lens, device):
+    if torch.is_tensor(lens):
+        return lens.to(device=device, dtype=torch.int32, non_blocking=True).contiguous()
+    return torch.as_tensor([int(v) for v in lens], dtype=torch.int32).to(device, non_blocking=True)
+
+
+def step_forward(mode, s, w_phi, keys, h, lens, prev_att, w_conv, w_lproj, w_gen, b_gen, scale=2.0,
+                 cluster=0, want_q=False, shared_memory=False, out=None):
+    """One attention step.  keys/h: [B,T,A]/[B,T,D], or [1,T,*] with shared_memory=True (beam decode:
+    every row of `s` attends over the same utterance).  Returns (att [B,T], ctx [B,D], q [B,A] | None)."""
+    _lib.require_cuda(s, keys, h, lens)
+    B, dec = s.shape
+    T, A = keys.shape[-2], keys.shape[-1]
+    D = h.shape[-1]
+    keys = keys.contiguous()
+    h = h.contiguous()
+    if s.stride(1) != 1:
+        s = s.contiguous()
+    if out is None:
+        att = torch.empty(B, T, dtype=torch.float32, device=s.device)
+        ctx = torch.empty(B, D, dtype=torch.float32, device=s.device)
+    else:
+        att, ctx = out
+    q = torch.empty(B, A, dtype=torch.float32, device=s.device) if want_q else None
+    kb = 0 if shared_memory else T * A
+    hb = 0 if shared_memory else T * D
+    loc = mode == "loc"
+    if loc:
+        C, KW1 = w_conv.shape[0], w_conv.shape[-1]
+        Kw = (KW1 - 1) // 2
+        w_conv = w_conv.contiguous()
+        w_lproj = w_lproj.contiguous()
+        w_gen = w_gen.contiguous()
+    else:
+        C, Kw = 0, 0
+    rc = _lib.lib().b2asr_attn_step_fwd(
+        MODES[mode], s.data_ptr(), s.stride(0), _lib.ptr(w_phi), keys.data_ptr(), kb, h.data_ptr(), hb,
+        lens.data_ptr(), _lib.ptr(prev_att), _lib.ptr(w_conv) if loc else 0, C, Kw,
+        _lib.ptr(w_lproj) if loc else 0, _lib.ptr(w_gen) if loc else 0,
+        _lib.ptr(b_gen) if loc else 0, float(scale), att.data_ptr(), ctx.data_ptr(), _lib.ptr(q),
+        B, T, D, A, dec, int(cluster), _lib.stream_ptr())
+    _lib.check(rc, "b2asr_attn_step_fwd")
+    return att, ctx, q

@@ -80,6 +80,31 @@ int b2asr_ctc_loss_fwd_bwd(const float* x, int64_t sx_t, int64_t sx_b,
  * upstream gradient differs from the prescale folded in at forward time. */
 int b2asr_rescale_if_needed(float* buf, int64_t n, const float* upstream, float assumed, void* stream);
 
+/* ------------------------------------------------------------------------
+ * Kernel group (2b): one decoder step of Attention.forward, reference
+ * src/asr.py:410-462 (query projection :422, location conv + projection :452,
+ * tanh energy :453, mask + softmax(scale*e) :454-455, context bmm :457; dot
+ * mode :426-432).  One launch per step; a thread-block cluster of `cluster`
+ * CTAs (0 = choose; else 1,2,4,8) works on each batch row.
+ *
+ *   mode       0 = dot, 1 = loc
+ *   s          [B,dec] decoder state, row stride s_stride
+ *   Wphi       [A,dec] phi.weight, or NULL when proj=False (then A == dec, q = s)
+ *   keys       [*,T,A] cached tanh(psi(h)) (asr.py:419); batch stride k_bstride
+ *              (0 = every row attends over the same utterance: beam decode)
+ *   h          [*,T,D] encoder features, batch stride h_bstride
+ *   lens       [B] int32 valid frames per row (mask of asr.py:415-418)
+ *   prev_att   [B,T] previous alignment, or NULL = uniform 1/len (asr.py:444-449)
+ *   Wc [C,2Kw+1] loc_conv.weight, Wl [A,C] loc_proj.weight, wg [A] / bg [1] gen_energy
+ *   att [B,T] out (0 on padding), ctx [B,D] out, q_out [B,A] out or NULL
+ * ---------------------------------------------------------------------- */
+int b2asr_attn_step_fwd(int mode, const float* s, int64_t s_stride, const float* Wphi,
+                        const float* keys, int64_t k_bstride, const float* h, int64_t h_bstride,
+                        const int32_t* lens, const float* prev_att,
+                        const float* Wc, int C, int Kw, const float* Wl, const float* wg, const float* bg,
+                        float scale, float* att, float* ctx, float* q_out,
+                        int B, int T, int D, int A, int dec, int cluster, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,119 @@
+"""GPU parity: kernel (2b) attention step vs oracle/attention_oracle.py (restating asr.py:410-462).
+
+Tolerance (north_star: attention outputs within 1e-4 relative in fp32):
+  |a-b| <= 1e-4*|b| + 1e-6 for alpha (values in [0,1]) and 1e-4*|b| + 1e-5*max|ctx| for the context,
+checked against the oracle evaluated in float64.
+"""
+import importlib
+
+import pytest
+import torch
+
+from oracle import attention_oracle as ao
+
+pytestmark = pytest.mark.gpu
+
+
+def _attn():
+    return importlib.import_module("end-to-end-asr-pytorch_b200._attn")
+
+
+def make_weights(A, D, dec, C=10, Kw=100, seed=0):
+    g = torch.Generator().manual_seed(seed)
+
+    def n(*s, sd=1.0):
+        return torch.randn(*s, generator=g) * sd
+
+    return dict(phi=n(A, dec, sd=dec ** -0.5), psi_w=n(A, D, sd=D ** -0.5), psi_b=n(A, sd=0.1),
+                loc_conv=n(C, 1, 2 * Kw + 1, sd=(2 * Kw + 1) ** -0.5), loc_proj=n(A, C, sd=C ** -0.5),
+                gen_w=n(1, A, sd=A ** -0.5), gen_b=n(1, sd=0.1))
+
+
+def make_batch(B, T, D, dec, seed=1, nstates=4):
+    g = torch.Generator().manual_seed(seed)
+    h = torch.randn(B, T, D, generator=g)
+    lens = sorted([int(v) for v in torch.randint(max(1, T // 2), T + 1, (B,), generator=g)], reverse=True)
+    lens[0] = T
+    for b, n in enumerate(lens):
+        h[b, n:] = 0
+    s = [torch.randn(B, dec, generator=g) for _ in range(nstates)]
+    return h, lens, s
+
+
+def worst(a, b, rtol, atol):
+    err = (a.double().cpu() - b.double()).abs()
+    tol = rtol * b.double().abs() + atol
+    return float((err / tol).max())
+
+
+SHAPES = [  # B, T, D, A, dec
+    (4, 50, 64, 32, 48),
+    (16, 97, 512, 256, 256),     # timit-shaped (M1)
+    (32, 400, 640, 300, 320),    # libri-shaped (M2)
+    (3, 750, 640, 300, 320),     # longest utterance after 4x subsampling
+]
+
+
+@pytest.mark.parametrize("B,T,D,A,dec", SHAPES)
+@pytest.mark.parametrize("cluster", [0, 1, 2])
+def test_loc_steps_match_oracle(cuda, B, T, D, A, dec, cluster):
+    at = _attn()
+    w = make_weights(A, D, dec)
+    h, lens, states = make_batch(B, T, D, dec)
+    keys64 = ao.project_keys(h.double(), w["psi_w"].double(), w["psi_b"].double())
+    w64 = {k: v.double() for k, v in w.items()}
+    prev64 = ao.uniform_alignment(lens, T, torch.float64)
+    wd = {k: v.to(cuda) for k, v in w.items()}
+    hd, kd = h.to(cuda), keys64.float().to(cuda)
+    ld = at.lens_i32(lens, cuda)
+    prev = None
+    for step, s in enumerate(states):
+        a64, c64 = ao.loc_step(s.double(), h.double(), keys64.float().double(), lens, prev64, w64)
+        att, ctx, q = at.step_forward("loc", s.to(cuda), wd["phi"], kd, hd, ld, prev, wd["loc_conv"], wd["loc_proj"],
+                                      wd["gen_w"], wd["gen_b"], 2.0, cluster=cluster, want_q=True)
+        torch.cuda.synchronize()
+        wa = worst(att, a64, 1e-4, 1e-6)
+        wc = worst(ctx, c64, 1e-4, 1e-5 * float(c64.abs().max()))
+        wq = worst(q, torch.tanh(s.double() @ w64["phi"].t()), 1e-4, 1e-6)
+        assert wa <= 1.0 and wc <= 1.0 and wq <= 1.0, "step %d: alpha %.2f ctx %.2f q %.2f (err/tol)" % (step, wa, wc, wq)
+        for b, n in enumerate(lens):
+            assert float(att[b, n:].abs().sum()) == 0.0
+        prev = att                   # feed our own alignment back, as Attention.prev_att does (asr.py:456)
+        prev64 = att.double().cpu()  # and keep the oracle on the same trajectory
+
+
+@pytest.mark.parametrize("B,T,D,A,dec", SHAPES[:3])
+def test_dot_steps_match_oracle(cuda, B, T, D, A, dec):
+    at = _attn()
+    w = make_weights(A, D, dec)
+    h, lens, states = make_batch(B, T, D, dec, seed=5)
+    keys64 = ao.project_keys(h.double(), w["psi_w"].double(), w["psi_b"].double())
+    ld = at.lens_i32(lens, cuda)
+    for s in states[:2]:
+        a64, c64 = ao.dot_step(s.double(), h.double(), keys64.float().double(), lens, {"phi": w["phi"].double()})
+        att, ctx, _ = at.step_forward("dot", s.to(cuda), w["phi"].to(cuda), keys64.float().to(cuda), h.to(cuda), ld,
+                                      None, None, None, None, None, 2.0)
+        wa = worst(att, a64, 1e-4, 1e-6)
+        wc = worst(ctx, c64, 1e-4, 1e-5 * float(c64.abs().max()))
+        assert wa <= 1.0 and wc <= 1.0, "alpha %.2f ctx %.2f (err/tol)" % (wa, wc)
+
+
+def test_shared_memory_rows_for_beam_decode(cuda):
+    """20 hypotheses attending over one utterance (batch stride 0) == the same utterance repeated."""
+    at = _attn()
+    B, T, D, A, dec = 20, 400, 640, 300, 320
+    w = make_weights(A, D, dec)
+    g = torch.Generator().manual_seed(3)
+    h1 = torch.randn(1, T, D, generator=g)
+    s = torch.randn(B, dec, generator=g)
+    prev = torch.softmax(torch.randn(B, T, generator=g), -1)
+    keys1 = ao.project_keys(h1, w["psi_w"], w["psi_b"])
+    a_ref, c_ref = ao.loc_step(s.double(), h1.double().expand(B, T, D), keys1.double().expand(B, T, A), [T] * B,
+                               prev.double(), {k: v.double() for k, v in w.items()})
+    wd = {k: v.to(cuda) for k, v in w.items()}
+    att, ctx, _ = at.step_forward("loc", s.to(cuda), wd["phi"], keys1.to(cuda), h1.to(cuda), at.lens_i32([T] * B, cuda),
+                                  prev.to(cuda), wd["loc_conv"], wd["loc_proj"], wd["gen_w"], wd["gen_b"], 2.0,
+                                  shared_memory=True)
+    wa = worst(att, a_ref, 1e-4, 1e-6)
+    wc = worst(ctx, c_ref, 1e-4, 1e-5 * float(c_ref.abs().max()))
+    assert wa <= 1.0 and wc <= 1.0, "alpha %.2f ctx %.2f (err/tol)" % (wa, wc)
