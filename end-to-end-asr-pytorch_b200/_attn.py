@@ -49,3 +49,45 @@ def step_forward(mode, s, w_phi, keys, h, lens, prev_att, w_conv, w_lproj, w_gen
         B, T, D, A, dec, int(cluster), _lib.stream_ptr())
     _lib.check(rc, "b2asr_attn_step_fwd")
     return att, ctx, q
+
+
+def pgrad_layout(A, C, Kw):
+    """Offsets of (dWl, dWc, dwg, dbg) inside one parameter-gradient slot, and the slot stride."""
+    o_wl, o_wc, o_wg, o_bg = 0, A * C, A * C + C * (2 * Kw + 1), A * C + C * (2 * Kw + 1) + A
+    return o_wl, o_wc, o_wg, o_bg, o_bg + 1
+
+
+def num_slots(B, T, D, A, dec, mode, C, Kw, cluster=0):
+    n = _lib.lib().b2asr_attn_slots(B, T, D, A, dec, MODES[mode], C, Kw, int(cluster))
+    if n <= 0:
+        _lib.check(n, "b2asr_attn_slots")
+    return n
+
+
+def step_backward(mode, w_phi, keys, h, lens, prev_att, w_conv, w_lproj, w_gen, scale, q_saved, att_saved,
+                  d_ctx, d_att, d_keys, pgrad, dec, cluster=0, want_prev=True):
+    """Backward of one step.  Accumulates into d_keys [B,T,A] and pgrad [slots,stride] in place; returns
+    (d_prev_att [B,T] | None, d_zq [B,A], d_s [B,dec])."""
+    B, T, A = keys.shape
+    D = h.shape[-1]
+    loc = mode == "loc"
+    dev = keys.device
+    d_prev = torch.empty(B, T, dtype=torch.float32, device=dev) if (loc and want_prev) else None
+    d_zq = torch.empty(B, A, dtype=torch.float32, device=dev)
+    d_s = torch.empty(B, dec, dtype=torch.float32, device=dev)
+    if loc:
+        C, Kw = w_conv.shape[0], (w_conv.shape[-1] - 1) // 2
+    else:
+        C, Kw = 0, 0
+    d_ctx = d_ctx.contiguous()
+    if d_att is not None:
+        d_att = d_att.contiguous()
+    rc = _lib.lib().b2asr_attn_step_bwd(
+        MODES[mode], _lib.ptr(w_phi), keys.data_ptr(), T * A, h.data_ptr(), T * D, lens.data_ptr(), _lib.ptr(prev_att),
+        _lib.ptr(w_conv) if loc else 0, C, Kw, _lib.ptr(w_lproj) if loc else 0, _lib.ptr(w_gen) if loc else 0,
+        float(scale), q_saved.data_ptr(), att_saved.data_ptr(), d_ctx.data_ptr(), _lib.ptr(d_att),
+        d_keys.data_ptr(), T * A, _lib.ptr(d_prev), d_zq.data_ptr(), d_s.data_ptr(),
+        _lib.ptr(pgrad), pgrad.stride(0) if pgrad is not None else 0,
+        B, T, D, A, dec, int(cluster), _lib.stream_ptr())
+    _lib.check(rc, "b2asr_attn_step_bwd")
+    return d_prev, d_zq, d_s

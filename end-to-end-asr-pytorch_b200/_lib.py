@@ -36,6 +36,13 @@ _SIGNATURES = {
     "b2asr_attn_step_fwd": (c_i, [c_i, c_p, c_i64, c_p, c_p, c_i64, c_p, c_i64, c_p, c_p,
                                   c_p, c_i, c_i, c_p, c_p, c_p, c_f, c_p, c_p, c_p,
                                   c_i, c_i, c_i, c_i, c_i, c_i, c_p]),
+    "b2asr_attn_pgrad_stride": (c_i64, [c_i, c_i, c_i]),
+    "b2asr_attn_slots": (c_i, [c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i]),
+    "b2asr_attn_step_bwd": (c_i, [c_i, c_p, c_p, c_i64, c_p, c_i64, c_p, c_p,
+                                  c_p, c_i, c_i, c_p, c_p, c_f,
+                                  c_p, c_p, c_p, c_p,
+                                  c_p, c_i64, c_p, c_p, c_p, c_p, c_i64,
+                                  c_i, c_i, c_i, c_i, c_i, c_i, c_p]),
 }
 
 

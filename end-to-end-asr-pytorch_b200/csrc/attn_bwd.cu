@@ -1,0 +1,411 @@
+// Kernel group (2b), backward: gradient of one Attention.forward step (reference src/asr.py:410-462;
+// the reference gets it from autograd over ~12 ATen ops).  The forward's tanh activations are NOT
+// stored (T'xA per step per utterance); they are recomputed here from the saved query, the previous
+// alignment and the alignment itself.
+//
+//   given  d_ctx [B,D], d_att [B,T] (what the NEXT step's location conv sent back; may be null)
+//   d_alpha = d_att + h . d_ctx                 de = scale * alpha * (d_alpha - <alpha, d_alpha>)
+//   loc:  u = tanh(K + q + l), l = tanh(Wl f), f = conv(prev_att)
+//         d_pre = de * wg * (1-u^2)             dK += d_pre          dq = sum_t d_pre
+//         d_zl = d_pre * (1-l^2)                dWl += d_zl^T f      df = d_zl Wl
+//         dWc += df (x) prev_att                d_prev_att = flipped conv of df with Wc
+//   dot:  dK += de (x) q, dq = de^T K
+//   d_zq = dq * (1-q^2), d_s = d_zq Wphi
+// Parameter gradients go to one private slot per CTA (summed once per batch on the host side), the
+// encoder-feature gradient dh = alpha (x) d_ctx is deferred to one batched GEMM per batch.
+#include "attn.cuh"
+
+namespace b2asr {
+
+struct BwdExtra { size_t de, al, dfpart, dfo, dfw, dqp, dzq, tmp, total; };
+
+__host__ __device__ inline BwdExtra attn_bwd_extra(const AttnArgs& p) {
+  BwdExtra x; size_t o = 0;
+  const int CP = (p.C + 3) / 4 * 4;
+  const int nwarp = p.NT / 32;
+  auto take = [&](size_t n) { size_t at = o; o += (n + 3) / 4 * 4; return at; };
+  x.de = take(p.chunk_max + 4);
+  x.al = take(p.chunk_max + 4);
+  x.dfpart = take((size_t)nwarp * p.TFK * 16);
+  x.dfo = take((size_t)p.chunk_max * CP);
+  x.dfw = take((size_t)(p.chunk_max + 2 * p.Kw) * CP);
+  x.dqp = take(p.A);
+  x.dzq = take(p.A);
+  x.tmp = take((size_t)(CP / 4) * p.chunk_max);
+  x.total = o;
+  return x;
+}
+
+// sum 16 per-lane values across the warp with 16 shuffles; on return lane L (L even) holds the
+// total of value index ((L>>1)&15 bit-reversed per stage, see idx below) in v[0].
+__device__ __forceinline__ float warp_reduce16(float (&v)[16], int lane, int& idx) {
+  {
+    const bool up = lane & 16;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { const float send = up ? v[i] : v[i + 8]; const float keep = up ? v[i + 8] : v[i]; v[i] = keep + __shfl_xor_sync(kFull, send, 16); }
+  }
+  {
+    const bool up = lane & 8;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { const float send = up ? v[i] : v[i + 4]; const float keep = up ? v[i + 4] : v[i]; v[i] = keep + __shfl_xor_sync(kFull, send, 8); }
+  }
+  {
+    const bool up = lane & 4;
+#pragma unroll
+    for (int i = 0; i < 2; ++i) { const float send = up ? v[i] : v[i + 2]; const float keep = up ? v[i + 2] : v[i]; v[i] = keep + __shfl_xor_sync(kFull, send, 4); }
+  }
+  {
+    const bool up = lane & 2;
+    const float send = up ? v[0] : v[1]; const float keep = up ? v[1] : v[0];
+    v[0] = keep + __shfl_xor_sync(kFull, send, 2);
+  }
+  v[0] += __shfl_xor_sync(kFull, v[0], 1);
+  idx = ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
+  return v[0];
+}
+
+__global__ void __launch_bounds__(512, 1) attn_step_bwd_kernel(AttnArgs p) {
+  extern __shared__ __align__(128) unsigned char smraw[];
+  const BwdExtra X = attn_bwd_extra(p);
+  const AttnSmem L = attn_smem_layout(p, X.total);
+  float* ring = reinterpret_cast<float*>(smraw + L.off_ring);
+  unsigned long long* full = reinterpret_cast<unsigned long long*>(smraw + L.off_bar);
+  float* q_sm = reinterpret_cast<float*>(smraw + L.off_q);
+  float* wcT = reinterpret_cast<float*>(smraw + L.off_wc);
+  float* pa = reinterpret_cast<float*>(smraw + L.off_pa);
+  float* fsm = reinterpret_cast<float*>(smraw + L.off_f);
+  float* dctx = reinterpret_cast<float*>(smraw + L.off_ctxp);
+  float* stat = reinterpret_cast<float*>(smraw + L.off_stat);
+  float* red = reinterpret_cast<float*>(smraw + L.off_red);
+  float* ex = reinterpret_cast<float*>(smraw + L.off_extra);
+  float* de = ex + X.de; float* al = ex + X.al; float* dfpart = ex + X.dfpart; float* dfo = ex + X.dfo;
+  float* dfw = ex + X.dfw; float* dqp = ex + X.dqp; float* dzq = ex + X.dzq; float* tmp = ex + X.tmp;
+
+  const int tid = threadIdx.x, NT = blockDim.x, lane = tid & 31, warp = tid >> 5, nwarp = NT >> 5;
+  const int CS = p.CS;
+  const unsigned r = CS > 1 ? cluster_ctarank() : 0u;
+  const int b = blockIdx.x / CS;
+  const int A = p.A, D = p.D, T = p.T, C = p.C;
+  const int CP = (C + 3) / 4 * 4, CQ = CP / 4;
+  const int KW1 = 2 * p.Kw + 1;
+  const int len = min(T, max(0, p.lens[b]));
+  const int chunk = (len + CS - 1) / CS;
+  const int t0 = min(len, (int)r * chunk), t1 = min(len, t0 + chunk), nf = t1 - t0;
+  const float* Kb = p.keys + (long long)b * p.k_bstride + (long long)t0 * A;
+  const float* Hb = p.h + (long long)b * p.h_bstride + (long long)t0 * D;
+  const int TFK = p.TFK, TFH = p.TFH, NS = p.NS;
+  const int nK = (nf + TFK - 1) / TFK, nH = (nf + TFH - 1) / TFH, ntiles = nK + nH;
+  const unsigned stage_floats = p.stage_bytes / 4;
+  const bool loc = p.mode == 1;
+  float* slot = p.pgrad ? p.pgrad + (long long)blockIdx.x * p.pgrad_stride : nullptr;   // [A*C | C*KW1 | A | 1]
+
+  if (tid == 0) {
+    for (int s = 0; s < NS; ++s) mbar_init(&full[s], 1);
+    mbar_fence_init();
+  }
+  cluster_or_cta_sync(CS);            // #0
+
+  auto issue = [&](int i) {          // thread 0 only; encoder-feature tiles first, then key tiles
+    if (i >= ntiles) return;
+    const int s = i % NS;
+    float* dst = ring + (size_t)s * stage_floats;
+    const float* src; unsigned bytes;
+    if (i < nH) { const int f0 = i * TFH; const int n = min(TFH, nf - f0); src = Hb + (long long)f0 * D; bytes = (unsigned)n * D * 4u; }
+    else { const int f0 = (i - nH) * TFK; const int n = min(TFK, nf - f0); src = Kb + (long long)f0 * A; bytes = (unsigned)n * A * 4u; }
+    mbar_expect_tx(&full[s], bytes);
+    bulk_g2s(dst, src, bytes, &full[s]);
+  };
+  if (tid == 0) for (int i = 0; i < NS; ++i) issue(i);
+
+  // ---- stage small operands; recompute the location features of my frames ---------------------
+  for (int a = tid; a < A; a += NT) q_sm[a] = p.q_saved[(long long)b * A + a];
+  for (int d = tid; d < D; d += NT) dctx[d] = p.d_ctx[(long long)b * D + d];
+  for (int j = tid; j < nf; j += NT) al[j] = p.att_saved[(long long)b * T + t0 + j];
+  if (loc) {
+    for (int i = tid; i < KW1 * CP; i += NT) wcT[i] = 0.f;
+    const int npa = nf + 2 * p.Kw;
+    const float unif = len > 0 ? 1.f / (float)len : 0.f;
+    for (int j = tid; j < npa; j += NT) {
+      const int t = t0 - p.Kw + j;
+      float v = 0.f;
+      if (t >= 0 && t < T) v = p.prev_att ? p.prev_att[(long long)b * T + t] : (t < len ? unif : 0.f);
+      pa[j] = v;
+    }
+    __syncthreads();
+    for (int i = tid; i < C * KW1; i += NT) { const int c = i / KW1, k = i - c * KW1; wcT[k * CP + c] = __ldg(p.Wc + i); }
+    __syncthreads();
+    const float4* w4 = reinterpret_cast<const float4*>(wcT);
+    for (int item = tid; item < nf * CQ; item += NT) {
+      const int cg = item / nf, fl = item - cg * nf;
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int k = 0; k < KW1; ++k) {
+        const float pv = pa[fl + k];
+        const float4 w = w4[k * CQ + cg];
+        acc.x = fmaf(pv, w.x, acc.x); acc.y = fmaf(pv, w.y, acc.y); acc.z = fmaf(pv, w.z, acc.z); acc.w = fmaf(pv, w.w, acc.w);
+      }
+      reinterpret_cast<float4*>(fsm)[fl * CQ + cg] = acc;
+    }
+  }
+  __syncthreads();
+
+  // ---- d_alpha over my frames: external part + h . d_ctx (one warp per frame) -------------------
+  const int ngroups = D / 4;
+  for (int i = 0; i < nH; ++i) {
+    const int s = i % NS;
+    mbar_wait(&full[s], (unsigned)((i / NS) & 1));
+    const float4* ht = reinterpret_cast<const float4*>(ring + (size_t)s * stage_floats);
+    const int f0 = i * TFH, n = min(TFH, nf - f0);
+    for (int j = warp; j < n; j += nwarp) {
+      float acc = 0.f;
+      for (int g = lane; g < ngroups; g += 32) {
+        const float4 hv = ht[(size_t)j * ngroups + g];
+        const float4 dv = reinterpret_cast<const float4*>(dctx)[g];
+        acc = fmaf(hv.x, dv.x, acc); acc = fmaf(hv.y, dv.y, acc); acc = fmaf(hv.z, dv.z, acc); acc = fmaf(hv.w, dv.w, acc);
+      }
+      acc = warp_sum(acc);
+      if (lane == 0) de[f0 + j] = acc + (p.d_att ? p.d_att[(long long)b * T + t0 + f0 + j] : 0.f);
+    }
+    __syncthreads();
+    if (tid == 0) { fence_proxy_async_smem(); issue(i + NS); }
+  }
+
+  // ---- softmax backward: de = scale * alpha * (d_alpha - <alpha, d_alpha>) ------------------------
+  float part = 0.f;
+  for (int j = tid; j < nf; j += NT) part = fmaf(al[j], de[j], part);
+  part = cta_reduce_sum(part, red);
+  if (tid == 0) {
+    if (CS > 1) { for (int rr = 0; rr < CS; ++rr) st_dsmem_f32(dsmem_addr(stat + r, rr), part); }
+    else stat[0] = part;
+  }
+  cluster_or_cta_sync(CS);            // #1
+  float dotsum = 0.f;
+  for (int rr = 0; rr < CS; ++rr) dotsum += stat[rr];
+  float dbg_part = 0.f;
+  for (int j = tid; j < nf; j += NT) { const float v = p.scale * al[j] * (de[j] - dotsum); de[j] = v; dbg_part += v; }
+  dbg_part = cta_reduce_sum(dbg_part, red);     // (also orders the de[] writes before the reads below)
+  if (loc && slot && tid == 0) slot[(long long)A * C + (long long)C * KW1 + A] += dbg_part;
+
+  // ---- main pass over the key tiles: thread a owns attention dimension a -------------------------
+  const bool active = tid < A;
+  float wl[kAttMaxC], dwl[kAttMaxC];
+#pragma unroll
+  for (int c = 0; c < kAttMaxC; ++c) { wl[c] = (active && loc && c < C) ? __ldg(p.Wl + (long long)tid * C + c) : 0.f; dwl[c] = 0.f; }
+  const float qa = active ? q_sm[tid] : 0.f;
+  const float wga = (active && loc) ? __ldg(p.wg + tid) : 0.f;
+  float dq_acc = 0.f, dwg_acc = 0.f;
+  float* dkb = p.d_keys + (long long)b * p.dk_bstride + (long long)t0 * A;
+  for (int i = 0; i < nK; ++i) {
+    const int ti = nH + i, s = ti % NS;
+    mbar_wait(&full[s], (unsigned)((ti / NS) & 1));
+    const float* kt = ring + (size_t)s * stage_floats;
+    const int f0 = i * TFK, n = min(TFK, nf - f0);
+    for (int j = 0; j < n; ++j) {
+      float v[16];
+#pragma unroll
+      for (int c = 0; c < 16; ++c) v[c] = 0.f;
+      if (active) {
+        const float kv = kt[j * A + tid];
+        const float dev = de[f0 + j];
+        float dpre;
+        if (loc) {
+          const float4* f4 = reinterpret_cast<const float4*>(fsm) + (size_t)(f0 + j) * CQ;
+          float fv[kAttMaxC];
+#pragma unroll
+          for (int c4 = 0; c4 < kAttMaxC / 4; ++c4) {
+            float4 t4 = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (c4 < CQ) t4 = f4[c4];
+            fv[4 * c4 + 0] = t4.x; fv[4 * c4 + 1] = t4.y; fv[4 * c4 + 2] = t4.z; fv[4 * c4 + 3] = t4.w;
+          }
+          float zl = 0.f;
+#pragma unroll
+          for (int c = 0; c < kAttMaxC; ++c) zl = fmaf(wl[c], fv[c], zl);
+          const float l = tanh_acc(zl);
+          const float u = tanh_acc(kv + qa + l);
+          dwg_acc = fmaf(dev, u, dwg_acc);
+          dpre = dev * wga * (1.f - u * u);
+          dq_acc += dpre;
+          const float dzl = dpre * (1.f - l * l);
+#pragma unroll
+          for (int c = 0; c < kAttMaxC; ++c) { dwl[c] = fmaf(dzl, fv[c], dwl[c]); v[c] = wl[c] * dzl; }
+        } else {
+          dpre = dev * qa;
+          dq_acc = fmaf(dev, kv, dq_acc);
+        }
+        float* dk = dkb + (long long)(f0 + j) * A + tid;
+        *dk += dpre;
+      }
+      if (loc) {
+        int idx;
+        const float tot = warp_reduce16(v, lane, idx);
+        if ((lane & 1) == 0) dfpart[((size_t)warp * TFK + j) * 16 + idx] = tot;
+      }
+    }
+    __syncthreads();
+    if (loc) {
+      for (int item = tid; item < n * CP; item += NT) {
+        const int j = item / CP, c = item - j * CP;
+        float acc = 0.f;
+        for (int w = 0; w < nwarp; ++w) acc += dfpart[((size_t)w * TFK + j) * 16 + c];
+        dfo[(size_t)(f0 + j) * CP + c] = acc;
+      }
+    }
+    __syncthreads();
+    if (tid == 0) { fence_proxy_async_smem(); issue(ti + NS); }
+  }
+
+  // ---- parameter-gradient slot: dWl rows and dwg (private to this CTA; plain read-modify-write) ---
+  if (loc && slot && active) {
+#pragma unroll
+    for (int c = 0; c < kAttMaxC; ++c) if (c < C) slot[(long long)tid * C + c] += dwl[c];
+    slot[(long long)A * C + (long long)C * KW1 + tid] += dwg_acc;
+  }
+  if (active) dqp[tid] = dq_acc;
+  cluster_or_cta_sync(CS);            // #2: dq partials and df of every CTA are complete
+
+  // ---- dq: slice-reduce over the cluster, through tanh', broadcast for the d_s product --------
+  {
+    const int aper = (A + CS - 1) / CS;
+    const int a0 = (int)r * aper, a1 = min(A, a0 + aper);
+    for (int a = a0 + tid; a < a1; a += NT) {
+      float v = 0.f;
+      if (CS > 1) { for (int rr = 0; rr < CS; ++rr) v += ld_dsmem_f32(dsmem_addr(dqp + a, rr)); }
+      else v = dqp[a];
+      if (p.Wphi) { const float qv = q_sm[a]; v *= (1.f - qv * qv); }
+      if (p.d_zq) p.d_zq[(long long)b * A + a] = v;
+      if (CS > 1) { for (int rr = 0; rr < CS; ++rr) st_dsmem_f32(dsmem_addr(dzq + a, rr), v); }
+      else dzq[a] = v;
+    }
+  }
+
+  // ---- location branch: gather df halo from the neighbours, then dWc and d_prev_att -------------
+  if (loc) {
+    const int nw = nf + 2 * p.Kw;
+    for (int item = tid; item < nw * CP; item += NT) {
+      const int w = item / CP, c = item - w * CP;
+      const int tg = t0 - p.Kw + w;
+      float v = 0.f;
+      if (tg >= 0 && tg < len && chunk > 0) {
+        const int rr = tg / chunk, li = tg - rr * chunk;
+        v = (CS > 1) ? ld_dsmem_f32(dsmem_addr(dfo + (size_t)li * CP + c, (unsigned)rr)) : dfo[(size_t)li * CP + c];
+      }
+      dfw[item] = v;
+    }
+    __syncthreads();
+    if (slot) {                     // dWc[c][k] += sum_j df[j][c] * prev_att[t0+j+k-Kw]
+      float* sWc = slot + (long long)A * C;
+      for (int item = tid; item < C * KW1; item += NT) {
+        const int c = item / KW1, k = item - c * KW1;
+        float acc = 0.f;
+        for (int j = 0; j < nf; ++j) acc = fmaf(dfo[(size_t)j * CP + c], pa[j + k], acc);
+        sWc[item] += acc;
+      }
+    }
+    if (p.d_prev_att) {             // d_prev_att[t0+i] = sum_k sum_c Wc[c][k] * df[t0+i-k+Kw][c]
+      const float4* w4 = reinterpret_cast<const float4*>(wcT);
+      const float4* d4 = reinterpret_cast<const float4*>(dfw);
+      for (int item = tid; item < nf * CQ; item += NT) {
+        const int cg = item / nf, i = item - cg * nf;
+        float acc = 0.f;
+        for (int k = 0; k < KW1; ++k) {
+          const float4 w = w4[k * CQ + cg];
+          const float4 d = d4[(size_t)(i - k + 2 * p.Kw) * CQ + cg];
+          acc = fmaf(w.x, d.x, acc); acc = fmaf(w.y, d.y, acc); acc = fmaf(w.z, d.z, acc); acc = fmaf(w.w, d.w, acc);
+        }
+        tmp[cg * p.chunk_max + i] = acc;
+      }
+      __syncthreads();
+      for (int i = tid; i < nf; i += NT) {
+        float acc = 0.f;
+        for (int cg = 0; cg < CQ; ++cg) acc += tmp[cg * p.chunk_max + i];
+        p.d_prev_att[(long long)b * T + t0 + i] = acc;
+      }
+      for (int t = len + (int)r * NT + tid; t < T; t += CS * NT) p.d_prev_att[(long long)b * T + t] = 0.f;
+    }
+  }
+  cluster_or_cta_sync(CS);            // #3: d_zq broadcast complete (and all df halo reads done)
+
+  // ---- d_s = d_zq Wphi (slice of the decoder dimension per CTA) -----------------------------------
+  if (p.d_s) {
+    const int jper = (p.dec + CS - 1) / CS;
+    const int j0 = (int)r * jper, j1 = min(p.dec, j0 + jper);
+    for (int j = j0 + tid; j < j1; j += NT) {
+      float acc;
+      if (p.Wphi) {
+        acc = 0.f;
+        for (int a = 0; a < A; ++a) acc = fmaf(dzq[a], __ldg(p.Wphi + (long long)a * p.dec + j), acc);
+      } else {
+        acc = dzq[j];
+      }
+      p.d_s[(long long)b * p.dec + j] = acc;
+    }
+  }
+  if (CS > 1) cluster_sync_all();     // #4
+}
+
+int attn_configure(AttnArgs& a, int cluster_hint, size_t extra_floats, size_t* smem_out);
+int attn_launch(void (*kern)(AttnArgs), const AttnArgs& a, size_t smem, cudaStream_t st);
+
+}  // namespace b2asr
+
+using namespace b2asr;
+
+extern "C" int64_t b2asr_attn_pgrad_stride(int A, int C, int Kw) {
+  return (int64_t)A * C + (int64_t)C * (2 * Kw + 1) + A + 1;
+}
+
+extern "C" int b2asr_attn_slots(int B, int T, int D, int A, int dec, int mode, int C, int Kw, int cluster) {
+  AttnArgs a = {};
+  a.mode = mode; a.B = B; a.T = T; a.D = D; a.A = A; a.dec = dec; a.C = C; a.Kw = Kw;
+  size_t smem = 0;
+  if (attn_configure(a, cluster, 0, &smem) != B2ASR_OK) return B2ASR_EUNSUPPORTED;
+  // the backward may settle on fewer ring stages but never on another cluster size
+  return B * a.CS;
+}
+
+extern "C" int b2asr_attn_step_bwd(int mode, const float* Wphi, const float* keys, int64_t k_bstride,
+                                   const float* h, int64_t h_bstride, const int32_t* lens, const float* prev_att,
+                                   const float* Wc, int C, int Kw, const float* Wl, const float* wg, float scale,
+                                   const float* q_saved, const float* att_saved, const float* d_ctx, const float* d_att,
+                                   float* d_keys, int64_t dk_bstride, float* d_prev_att, float* d_zq, float* d_s,
+                                   float* pgrad, int64_t pgrad_stride,
+                                   int B, int T, int D, int A, int dec, int cluster, void* stream) {
+  B2_REQUIRE(keys && h && lens && q_saved && att_saved && d_ctx && d_keys, B2ASR_EINVAL, "attn_step_bwd: null pointer argument");
+  B2_REQUIRE(mode == 0 || mode == 1, B2ASR_EINVAL, "attn_step_bwd: mode %d (0 dot, 1 loc)", mode);
+  B2_REQUIRE(B > 0 && T > 0 && D > 0 && A > 0 && dec > 0, B2ASR_EINVAL, "attn_step_bwd: bad sizes");
+  B2_REQUIRE(mode == 0 || (Wc && Wl && wg), B2ASR_EINVAL, "attn_step_bwd: loc mode needs Wc, Wl, wg");
+  B2_REQUIRE(mode == 0 || pgrad == nullptr || pgrad_stride >= b2asr_attn_pgrad_stride(A, C, Kw), B2ASR_EINVAL,
+             "attn_step_bwd: pgrad_stride too small");
+  B2_REQUIRE(Wphi || A == dec, B2ASR_EINVAL, "attn_step_bwd: proj=False needs A == dec");
+  B2_REQUIRE((((uintptr_t)keys | (uintptr_t)h) & 15) == 0 && (k_bstride % 4 == 0) && (h_bstride % 4 == 0), B2ASR_EINVAL,
+             "attn_step_bwd: keys/h must be 16-byte aligned");
+  AttnArgs a = {};
+  a.mode = mode; a.Wphi = Wphi; a.keys = keys; a.k_bstride = k_bstride; a.h = h; a.h_bstride = h_bstride;
+  a.lens = lens; a.prev_att = prev_att; a.Wc = Wc; a.C = C; a.Kw = Kw; a.Wl = Wl; a.wg = wg; a.scale = scale;
+  a.q_saved = q_saved; a.att_saved = att_saved; a.d_ctx = d_ctx; a.d_att = d_att;
+  a.d_keys = d_keys; a.dk_bstride = dk_bstride; a.d_prev_att = d_prev_att; a.d_zq = d_zq; a.d_s = d_s;
+  a.pgrad = pgrad; a.pgrad_stride = pgrad_stride;
+  a.B = B; a.T = T; a.D = D; a.A = A; a.dec = dec;
+  // first pass fixes CS/NT/tiles, second pass sizes the ring with the backward's extra arrays
+  size_t smem = 0;
+  int rc = attn_configure(a, cluster, 0, &smem);
+  if (rc != B2ASR_OK) return rc;
+  const int cs = a.CS;
+  if (a.TFK > 32) a.TFK = 32;
+  const BwdExtra X = attn_bwd_extra(a);
+  a.NS = 4;
+  AttnSmem L = attn_smem_layout(a, X.total);
+  while (L.total > 227 * 1024 && a.NS > 2) { a.NS--; L = attn_smem_layout(a, X.total); }
+  BwdExtra X2 = X;
+  while (L.total > 227 * 1024 && a.TFK > 2 && a.TFH > 1) {     // long slices: shrink the ring tiles
+    a.stage_bytes = (unsigned)align_up((size_t)a.stage_bytes / 2, 128);
+    const unsigned rk = (unsigned)A * 4u, rh = (unsigned)D * 4u;
+    a.TFK = (int)(a.stage_bytes / rk); if (a.TFK > 32) a.TFK = 32; if (a.TFK < 1) a.TFK = 1;
+    a.TFH = (int)(a.stage_bytes / rh); if (a.TFH < 1) a.TFH = 1;
+    const unsigned need = (rk * a.TFK > rh * a.TFH) ? rk * a.TFK : rh * a.TFH;
+    if (a.stage_bytes < need) a.stage_bytes = (unsigned)align_up((size_t)need, 128);
+    X2 = attn_bwd_extra(a);
+    L = attn_smem_layout(a, X2.total);
+  }
+  B2_REQUIRE(L.total <= 227 * 1024, B2ASR_EUNSUPPORTED, "attn_step_bwd: needs %zu bytes of shared memory (T=%d, cluster %d)", L.total, T, cs);
+  return attn_launch(attn_step_bwd_kernel, a, L.total, (cudaStream_t)stream);
+}

@@ -105,6 +105,30 @@ int b2asr_attn_step_fwd(int mode, const float* s, int64_t s_stride, const float*
                         float scale, float* att, float* ctx, float* q_out,
                         int B, int T, int D, int A, int dec, int cluster, void* stream);
 
+/* ------------------------------------------------------------------------
+ * Backward of one attention step (the reference obtains it from autograd over
+ * the ops of src/asr.py:422-457).  Activations are recomputed from q_saved
+ * (q_out of the forward), prev_att and att_saved (the forward's att).
+ *
+ *   d_ctx [B,D], d_att [B,T] or NULL   upstream gradients of ctx / att
+ *   d_keys [B,T,A]   accumulated IN PLACE (+=), batch stride dk_bstride
+ *   d_prev_att [B,T] out or NULL (loc: gradient w.r.t. prev_att)
+ *   d_zq [B,A] out or NULL: gradient w.r.t. the pre-tanh query phi(s)
+ *   d_s  [B,dec] out or NULL: gradient w.r.t. the decoder state
+ *   pgrad [b2asr_attn_slots(), pgrad_stride] accumulated IN PLACE, one private
+ *        slot per CTA laid out [dWl A*C | dWc C*(2Kw+1) | dwg A | dbg 1];
+ *        the caller zeroes it once per batch and sums the slots at the end.
+ * ---------------------------------------------------------------------- */
+int64_t b2asr_attn_pgrad_stride(int A, int C, int Kw);
+int b2asr_attn_slots(int B, int T, int D, int A, int dec, int mode, int C, int Kw, int cluster);
+int b2asr_attn_step_bwd(int mode, const float* Wphi, const float* keys, int64_t k_bstride,
+                        const float* h, int64_t h_bstride, const int32_t* lens, const float* prev_att,
+                        const float* Wc, int C, int Kw, const float* Wl, const float* wg, float scale,
+                        const float* q_saved, const float* att_saved, const float* d_ctx, const float* d_att,
+                        float* d_keys, int64_t dk_bstride, float* d_prev_att, float* d_zq, float* d_s,
+                        float* pgrad, int64_t pgrad_stride,
+                        int B, int T, int D, int A, int dec, int cluster, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

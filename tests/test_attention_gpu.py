@@ -117,3 +117,65 @@ def test_shared_memory_rows_for_beam_decode(cuda):
     wa = worst(att, a_ref, 1e-4, 1e-6)
     wc = worst(ctx, c_ref, 1e-4, 1e-5 * float(c_ref.abs().max()))
     assert wa <= 1.0 and wc <= 1.0, "alpha %.2f ctx %.2f (err/tol)" % (wa, wc)
+
+
+def rel(a, b):
+    """max |a-b| / max|b| : gradients are compared relative to the tensor's own scale."""
+    return float((a.double().cpu() - b.double()).abs().max() / b.double().abs().max().clamp_min(1e-30))
+
+
+@pytest.mark.parametrize("B,T,D,A,dec", SHAPES)
+@pytest.mark.parametrize("mode", ["loc", "dot"])
+@pytest.mark.parametrize("cluster", [0, 1])
+def test_step_backward_matches_autograd_of_oracle(cuda, B, T, D, A, dec, mode, cluster):
+    """Kernel backward vs float64 autograd through the oracle step; every gradient within 1e-4 of its
+    tensor's max magnitude."""
+    at = _attn()
+    w = make_weights(A, D, dec)
+    h, lens, states = make_batch(B, T, D, dec, seed=11, nstates=1)
+    g = torch.Generator().manual_seed(99)
+    keys = ao.project_keys(h, w["psi_w"], w["psi_b"])
+    prev = torch.softmax(torch.randn(B, T, generator=g), -1) * ao.pad_mask(lens, T).logical_not()
+    prev = prev / prev.sum(-1, keepdim=True)
+    Ga, Gc = torch.randn(B, T, generator=g), torch.randn(B, D, generator=g)
+    # ---- oracle, float64 autograd
+    leaf = {k: v.double().clone().requires_grad_(True) for k, v in w.items() if k not in ("psi_w", "psi_b")}
+    s64 = states[0].double().clone().requires_grad_(True)
+    k64 = keys.double().clone().requires_grad_(True)
+    p64 = prev.double().clone().requires_grad_(True)
+    if mode == "loc":
+        a64, c64 = ao.loc_step(s64, h.double(), k64, lens, p64, leaf)
+    else:
+        a64, c64 = ao.dot_step(s64, h.double(), k64, lens, leaf)
+    mask = ao.pad_mask(lens, T).logical_not().double()
+    ((a64 * Ga.double() * mask).sum() + (c64 * Gc.double()).sum()).backward()
+    # ---- kernel
+    wd = {k: v.to(cuda) for k, v in w.items()}
+    ld = at.lens_i32(lens, cuda)
+    loc = mode == "loc"
+    att, ctx, q = at.step_forward(mode, states[0].to(cuda), wd["phi"], keys.to(cuda), h.to(cuda), ld,
+                                  prev.to(cuda) if loc else None, wd["loc_conv"] if loc else None,
+                                  wd["loc_proj"] if loc else None, wd["gen_w"] if loc else None,
+                                  wd["gen_b"] if loc else None, 2.0, cluster=cluster, want_q=True)
+    C, Kw = (10, 100) if loc else (0, 0)
+    o_wl, o_wc, o_wg, o_bg, stride = at.pgrad_layout(A, C, Kw) if loc else (0, 0, 0, 0, 1)
+    slots = at.num_slots(B, T, D, A, dec, mode, C, Kw, cluster)
+    pgrad = torch.zeros(slots, stride, device=cuda) if loc else None
+    d_keys = torch.zeros(B, T, A, device=cuda)
+    d_prev, d_zq, d_s = at.step_backward(mode, wd["phi"], keys.to(cuda), h.to(cuda), ld, prev.to(cuda) if loc else None,
+                                         wd["loc_conv"] if loc else None, wd["loc_proj"] if loc else None,
+                                         wd["gen_w"] if loc else None, 2.0, q, att, Gc.to(cuda), Ga.to(cuda),
+                                         d_keys, pgrad, dec, cluster=cluster)
+    torch.cuda.synchronize()
+    errs = {"d_s": rel(d_s, s64.grad), "d_keys": rel(d_keys, k64.grad),
+            "d_phi": rel(d_zq.t() @ states[0].to(cuda), leaf["phi"].grad)}
+    if loc:
+        pg = pgrad.sum(0)
+        errs["d_prev"] = rel(d_prev, p64.grad * mask)
+        errs["d_loc_proj"] = rel(pg[o_wl:o_wc].view(A, C), leaf["loc_proj"].grad)
+        errs["d_loc_conv"] = rel(pg[o_wc:o_wg].view(C, 1, 2 * Kw + 1), leaf["loc_conv"].grad)
+        errs["d_gen_w"] = rel(pg[o_wg:o_bg].view(1, A), leaf["gen_w"].grad)
+        # d/d(gen_energy.bias) of a softmax is exactly 0 (shift invariance): absolute check
+        errs["d_gen_b"] = float(pg[o_bg].abs().cpu()) / float(Ga.abs().max()) * 1e-1
+    bad = {k: v for k, v in errs.items() if not v <= 1e-4}
+    assert not bad, "gradient mismatch (err / max|ref|): %s" % errs
