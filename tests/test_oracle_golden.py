@@ -1,0 +1,111 @@
+"""CPU: the oracle restatements (oracle/*.py) against golden vectors produced by the UNMODIFIED
+reference (tools/make_golden.py ran /root/reference in-process and saved inputs + outputs)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import attention_oracle as ao
+from oracle import beam_oracle as bo
+from oracle import ctc_oracle as co
+from oracle import decode_oracle as do
+from oracle import model_oracle as mo
+from oracle import prefix_oracle as po
+
+G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def load(name):
+    return torch.load(os.path.join(G, name), weights_only=False)
+
+
+@pytest.mark.parametrize("name", ["attention_loc.pt", "attention_dot.pt"])
+def test_attention_steps(name):
+    g = load(name)
+    sd = g["state_dict"]
+    w = dict(phi=sd["phi.weight"])
+    if g["mode"] == "loc":
+        w.update(loc_conv=sd["loc_conv.weight"], loc_proj=sd["loc_proj.weight"], gen_w=sd["gen_energy.weight"],
+                 gen_b=sd["gen_energy.bias"])
+    keys = ao.project_keys(g["h"], sd["psi.weight"], sd["psi.bias"])
+    assert torch.allclose(keys, g["keys"], atol=1e-6)
+    prev = ao.uniform_alignment(g["lens"], g["h"].shape[1])
+    for s, a_ref, c_ref in zip(g["states"], g["att"], g["ctx"]):
+        if g["mode"] == "loc":
+            a, c = ao.loc_step(s, g["h"], keys, g["lens"], prev, w)
+            prev = a
+        else:
+            a, c = ao.dot_step(s, g["h"], keys, g["lens"], w)
+        assert torch.allclose(a, a_ref, atol=1e-6, rtol=1e-5)
+        assert torch.allclose(c, c_ref, atol=1e-5, rtol=1e-5)
+
+
+def test_prefix_scorer_is_bit_exact():
+    g = load("prefix.pt")
+    x = g["x"].numpy()
+    assert np.array_equal(po.blank_only_state(x), g["init"])
+    for c in g["calls"]:
+        psi, r = po.extend_prefix(x, c["prefix"], c["r_prev"], c["cands"])
+        assert np.array_equal(psi, c["psi"]) and np.array_equal(r, c["r"])
+    f = g["full"]
+    psi, r = po.extend_prefix_all(x, f["prefix"], f["r_prev"])
+    assert np.array_equal(psi, f["psi"]) and np.array_equal(r, f["r"])
+
+
+def _oracle_model(g):
+    m = mo.OracleModel(g["x"].shape[-1], g["vocab"], g["cfg"])
+    missing = m.load_state_dict(g["state_dict"], strict=True)
+    return m
+
+
+def test_train_step_forward_loss_and_gradients():
+    g = load("trainstep.pt")
+    m = _oracle_model(g)
+    m.train()
+    y = g["y"]
+    ans_len = int(torch.max(torch.sum(y != 0, dim=-1)))
+    ctc_pred, enc_len, att_pred, maps = m.run(g["x"], ans_len, tf_rate=1.0, teacher=y, state_len=g["lens"])
+    assert enc_len == g["enc_len"]
+    assert torch.allclose(ctc_pred, g["ctc_pred"], atol=1e-5)
+    assert torch.allclose(att_pred, g["att_pred"], atol=1e-5)
+    assert torch.allclose(maps[0], g["att_maps"], atol=1e-6)
+    loss, att_loss, ctc_loss = mo.hybrid_loss(ctc_pred, att_pred, y, enc_len, 0.5)
+    assert abs(float(loss) - float(g["loss"])) < 1e-5
+    assert abs(float(att_loss) - float(g["att_loss"])) < 1e-5 and abs(float(ctc_loss) - float(g["ctc_loss"])) < 1e-5
+    loss.backward()
+    for k, p in m.named_parameters():
+        ref = g["grads"][k]
+        assert torch.allclose(p.grad, ref, atol=2e-5 * float(ref.abs().max()) + 1e-7), k
+    assert mo.infer_lengths(g["x"]) == g["lens"]
+
+
+@pytest.mark.parametrize("name", ["beam_joint.pt", "beam_att_only.pt", "beam_ctc.pt"])
+def test_beam_decode_tokens_identical(name):
+    g = load(name)
+    m = _oracle_model(g)
+    m.eval()
+    lm = do.OracleLM(*g["lm_dims"][:3], layers=g["lm_dims"][3])
+    lm.load_state_dict(g["lm_state_dict"])
+    lm.eval()
+    hyps = do.beam_decode(m, lm, g["x"], g["decode_step"], g["state_len"], g["beam"], g["ctc_weight"], g["lm_weight"])
+    assert [h.tokens for h in hyps] == [h["tokens"] for h in g["hyps"]]
+    for h, r in zip(hyps, g["hyps"]):
+        assert abs(float(h.mean_score()) - r["avg"]) < 1e-5
+
+
+def test_ctc_oracle_three_ways_agree():
+    torch.manual_seed(0)
+    B, T, V, L = 3, 14, 6, 4
+    x = torch.randn(B, T, V)
+    y = torch.randint(1, V, (B, L)); y[1, 2] = y[1, 1]
+    tl = torch.tensor([4, 3, 2]); sl = [14, 11, 8]
+    for b in range(B):
+        y[b, tl[b]:] = 0
+    loss, nll, g = co.reference_call(x, y, sl, tl, torch.float64)
+    nll2, g2 = co.graves_batch(x.transpose(0, 1).numpy(), y.numpy(), sl, tl.numpy())
+    assert np.allclose(nll.numpy(), nll2, rtol=1e-10)
+    assert np.allclose(g.transpose(0, 1).numpy(), g2, atol=1e-12)
+    lp = torch.log_softmax(torch.randn(5, 3), -1).numpy()
+    for lab in ([1, 2], [1, 1], [2], []):
+        assert abs(co.brute_force_nll(lp, lab) - co.graves_log_lattice(lp, lab)[0]) < 1e-10
