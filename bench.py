@@ -1,0 +1,323 @@
+#!/usr/bin/env python
+"""Benchmark of the hybrid CTC/attention train step (BASELINE.json metric: utterances/s).
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's sm_100a path
+    python bench.py --impl reference --gpus N --steps K --warmup W   # the reference's CPU path (oracle port)
+
+A step = one pass of Trainer.exec's body (reference src/solver.py:132-182: forward, CE + CTC loss,
+backward, [gradient all-reduce], clip, NaN guard, optimizer step) over one synthetic
+libri_example.yaml-shaped batch (workload M2: B=32/GPU, T<=1600 frames of 120-dim
+fbank+delta, V=31 chars, pBLSTM 5x320 -> T'=400, location attention 300, decoder 320, joint_ctc 0.5,
+tf_rate 1.0, Adadelta).  Prints ONE JSON line (rank 0).
+"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+PKG = "end-to-end-asr-pytorch_b200"
+METRIC = "utterances/sec hybrid CTC-attn train step"
+WORKLOAD = "libri_m2"
+N_BATCHES = 4                      # distinct synthetic batches rotated through the timed steps
+
+
+def pkg(name):
+    return importlib.import_module(PKG + "." + name)
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured"
+    return 6650.0, "fallback"
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks sampler (nvidia-smi during the timed region)
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [v.strip() for v in ln.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+# algorithmic bytes per launch (DESIGN.md "Roofline")
+# ------------------------------------------------------------------------------------------------
+def algorithmic_bytes(kernel, enc_lens, B, Tp, A, D, dec, V, labels, C=10, KW1=201):
+    s = sum(enc_lens)
+    wts = 4 * (A * dec + C * KW1 + C * A + A + 1)
+    if kernel == "b2asr_attn_step_fwd":      # keys + h read once, prev/att rows, state in, ctx out, weights
+        return 4 * s * (A + D + 2) + 4 * B * (dec + D) + wts
+    if kernel == "b2asr_attn_step_bwd":      # keys + h read, dK read-modify-write, 4 alignment-sized rows
+        return 4 * s * (3 * A + D + 4) + 4 * B * (2 * A + D + dec) + wts
+    if kernel == "b2asr_ctc_loss_fwd_bwd":   # every valid logit row read once, every grad row written once
+        return 4 * V * (s + B * Tp) + 8 * sum(labels) + 16 * B
+    return 0
+
+
+# ------------------------------------------------------------------------------------------------
+# reference arm / cpu_baseline: the oracle port of the reference's train step on the host cores
+# ------------------------------------------------------------------------------------------------
+def cpu_train_step_rate(steps, warmup, budget_s, seed=1234):
+    """Times oracle/model_oracle.train_step (restating reference solver.py:132-182 + asr.py:58-112) on a
+    bounded sample of the M2 workload: the first `bs` utterances of the synthetic batch at full length."""
+    import torch
+    from oracle import model_oracle as mo
+    syn = pkg("synthetic")
+    w = syn.WORKLOADS[WORKLOAD]
+    torch.manual_seed(0)
+    model = mo.OracleModel(w["d_in"], w["vocab"], w["cfg"])
+    opt = torch.optim.Adadelta(model.parameters(), lr=1.0, eps=1e-8)
+    x, y, lens = syn.make_batch(WORKLOAD, seed)
+    cores = torch.get_num_threads()
+
+    def run(bs):
+        xs = x[:bs]
+        ys = y[:bs]
+        t0 = time.perf_counter()
+        mo.train_step(model, opt, xs, ys, tf_rate=1.0)
+        return time.perf_counter() - t0
+
+    run(1)                                             # page in / thread pools (untimed)
+    per_utt = run(1)
+    bs = int(max(1, min(w["batch"], budget_s / max(per_utt * (steps + warmup), 1e-6))))
+    for _ in range(warmup):
+        run(bs)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        run(bs)
+    dt = time.perf_counter() - t0
+    sample = "first %d of %d utterances of the %s batch (T=%d frames, full label length), %d steps" % (
+        bs, w["batch"], WORKLOAD, x.shape[1], steps)
+    return bs * steps / dt, dt / steps * 1e3, cores, sample
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    value, ms, cores, sample = cpu_train_step_rate(args.steps, args.warmup, budget_s=150.0)
+    out = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "utterances/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "note": "CPU port of the reference train step (oracle/model_oracle.py); "
+                   "the reference is Python and /root/reference does not travel to the GPU box"},
+        "cpu_baseline": {"value": value, "unit": "utterances/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "utterances/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(out), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# this repo's arm
+# ------------------------------------------------------------------------------------------------
+def run_native(args):
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the hot path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    lib = pkg("_lib")
+    lib.lib()                                          # fail loudly if libb2asr.so is missing
+    asr, solver, syn = pkg("asr"), pkg("solver"), pkg("synthetic")
+    w = syn.WORKLOADS[WORKLOAD]
+    cfg = w["cfg"]
+
+    torch.manual_seed(0)                               # identical weights on every rank
+    ex = torch.zeros(1, 8, w["d_in"])
+    model = asr.Seq2Seq(ex, w["vocab"], cfg).to(dev)
+    model.train()
+    opt = solver.make_optimizer(model, cfg["optimizer"])
+    ts = solver.TrainStep(model, opt, cfg["optimizer"]["joint_ctc"])
+    n_params = sum(p.numel() for p in model.parameters())
+
+    host = []
+    for i in range(N_BATCHES):
+        x, y, lens = syn.make_batch(WORKLOAD, 1234 + rank + 1000 * i)
+        host.append((x.pin_memory(), y.pin_memory(), lens))
+    resident = [(x.to(dev), y.to(dev)) for x, y, _ in host]
+    B = w["batch"]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            fn(i)
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms)
+
+    def step_resident(i):
+        x, y = resident[i % N_BATCHES]
+        ts.step(x, y, tf_rate=1.0)
+
+    d2h = [0]
+
+    def step_e2e(i):
+        xh, yh, _ = host[i % N_BATCHES]
+        x = xh.to(dev, non_blocking=True)
+        y = yh.to(dev, non_blocking=True)
+        out = ts.step(x, y, tf_rate=1.0)
+        float(out["loss"])                             # the step's result crosses back to the host
+        d2h[0] = 4 + 4 + 8 * B + 8                      # loss, grad-norm, B lengths, max label length
+
+    for i in range(args.warmup):
+        step_resident(i)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = lib.LAUNCHES
+    ms_total = timed(step_resident, args.steps)
+    launches = lib.LAUNCHES - l0
+    clocks = sampler.stop() if rank == 0 else None
+    ms_step = ms_total / args.steps
+    value = B * world * args.steps / (ms_total * 1e-3)
+
+    for i in range(min(2, args.warmup)):
+        step_e2e(i)
+    ms_e2e = timed(step_e2e, args.steps)
+    e2e_value = B * world * args.steps / (ms_e2e * 1e-3)
+    h2d = host[0][0].numel() * 4 + host[0][1].numel() * 8
+
+    # ---- per-kernel timing pass (same steps, CUDA events around every launch of libb2asr.so) -------
+    lib.profile_start()
+    prof_steps = min(args.steps, 3)
+    for i in range(prof_steps):
+        step_resident(i)
+    prof = lib.profile_stop()
+    roofline = None
+    kernels = {}
+    if prof:
+        peak, how = measured_peaks()
+        att = cfg["attention"]
+        D = int(cfg["encoder"]["dim"].split("_")[-1]) * 2
+        for name, (calls, tot_ms) in prof.items():
+            per = tot_ms / max(calls, 1)
+            # algorithmic bytes use the first batches' actual lengths (averaged over the profiled steps)
+            ab = 0.0
+            for i in range(prof_steps):
+                _, yb, lens = host[i % N_BATCHES]
+                enc = syn.encoder_lengths(WORKLOAD, lens)
+                labels = [int(v) for v in (yb != 0).sum(-1)]
+                ab += algorithmic_bytes(name, enc, B, max(enc), att["dim"], D, cfg["decoder"]["dim"], w["vocab"], labels)
+            ab /= prof_steps
+            kernels[name] = {"calls_per_step": calls / prof_steps, "avg_us": per * 1e3,
+                             "ms_per_step": tot_ms / prof_steps, "alg_bytes_per_launch": ab,
+                             "achieved_gbs": (ab / (per * 1e-3) / 1e9) if per > 0 else None}
+        top = max(kernels, key=lambda k: kernels[k]["ms_per_step"])
+        k = kernels[top]
+        roofline = {"kernel": top, "bound": "hbm", "achieved": k["achieved_gbs"], "peak": peak, "unit": "GB/s",
+                    "frac": k["achieved_gbs"] / peak, "traffic": None, "peak_source": how,
+                    "share_of_step": k["ms_per_step"] / ms_step,
+                    "note": "M2 keys+features (48 MB) are L2-resident across decoder steps; see DESIGN.md"}
+
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        v, ms, cores, sample = cpu_train_step_rate(steps=2, warmup=0, budget_s=20.0)
+        cpu_baseline = {"value": v, "unit": "utterances/s", "cores": cores, "kind": "port", "sample": sample}
+
+    if rank == 0:
+        out = {
+            "metric": METRIC, "value": value, "unit": "utterances/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "batch_per_gpu": B, "global_batch": B * world, "frames": w["t_hi"],
+                       "feature_dim": w["d_in"], "vocab": w["vocab"], "params": n_params,
+                       "parallelism": "dp%d" % world,
+                       "l2": "inputs larger than L2: %d distinct batches rotate and one step touches >1 GB of "
+                             "activations (126 MB L2)" % N_BATCHES},
+            "clocks": clocks, "gpu_launches": launches,
+            "e2e": {"value": e2e_value, "unit": "utterances/s", "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h[0], "ms_per_step": ms_e2e / args.steps},
+            "roofline": roofline, "kernels": kernels, "cpu_baseline": cpu_baseline,
+        }
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_native(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -41,13 +41,12 @@ def step_forward(mode, s, w_phi, keys, h, lens, prev_att, w_conv, w_lproj, w_gen
         w_gen = w_gen.contiguous()
     else:
         C, Kw = 0, 0
-    rc = _lib.lib().b2asr_attn_step_fwd(
+    _lib.call("b2asr_attn_step_fwd", 1, _lib.lib().b2asr_attn_step_fwd,
         MODES[mode], s.data_ptr(), s.stride(0), _lib.ptr(w_phi), keys.data_ptr(), kb, h.data_ptr(), hb,
         lens.data_ptr(), _lib.ptr(prev_att), _lib.ptr(w_conv) if loc else 0, C, Kw,
         _lib.ptr(w_lproj) if loc else 0, _lib.ptr(w_gen) if loc else 0,
         _lib.ptr(b_gen) if loc else 0, float(scale), att.data_ptr(), ctx.data_ptr(), _lib.ptr(q),
         B, T, D, A, dec, int(cluster), _lib.stream_ptr())
-    _lib.check(rc, "b2asr_attn_step_fwd")
     return att, ctx, q
 
 
@@ -82,12 +81,11 @@ def step_backward(mode, w_phi, keys, h, lens, prev_att, w_conv, w_lproj, w_gen, 
     d_ctx = d_ctx.contiguous()
     if d_att is not None:
         d_att = d_att.contiguous()
-    rc = _lib.lib().b2asr_attn_step_bwd(
+    _lib.call("b2asr_attn_step_bwd", 1, _lib.lib().b2asr_attn_step_bwd,
         MODES[mode], _lib.ptr(w_phi), keys.data_ptr(), T * A, h.data_ptr(), T * D, lens.data_ptr(), _lib.ptr(prev_att),
         _lib.ptr(w_conv) if loc else 0, C, Kw, _lib.ptr(w_lproj) if loc else 0, _lib.ptr(w_gen) if loc else 0,
         float(scale), q_saved.data_ptr(), att_saved.data_ptr(), d_ctx.data_ptr(), _lib.ptr(d_att),
         d_keys.data_ptr(), T * A, _lib.ptr(d_prev), d_zq.data_ptr(), d_s.data_ptr(),
         _lib.ptr(pgrad), pgrad.stride(0) if pgrad is not None else 0,
         B, T, D, A, dec, int(cluster), _lib.stream_ptr())
-    _lib.check(rc, "b2asr_attn_step_bwd")
     return d_prev, d_zq, d_s

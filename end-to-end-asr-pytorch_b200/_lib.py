@@ -81,6 +81,40 @@ def check(rc, what):
         raise B2asrError("%s failed (%d): %s" % (what, rc, msg))
 
 
+# ---- launch accounting (bench.py's `gpu_launches`) and optional per-call CUDA-event timing ----------
+LAUNCHES = 0          # kernels of libb2asr.so launched by this process
+_prof = None          # None, or {name: [(start_event, end_event), ...]} while profiling is on
+
+
+def profile_start():
+    global _prof
+    _prof = {}
+
+
+def profile_stop():
+    """-> {name: (calls, total_ms)}; synchronises the device."""
+    global _prof
+    rec, _prof = _prof or {}, None
+    torch.cuda.synchronize()
+    return {k: (len(v), sum(a.elapsed_time(b) for a, b in v)) for k, v in rec.items()}
+
+
+def call(name, n_kernels, fn, *args):
+    """Launch through the C ABI: count the kernels, time them with events on the launching (current)
+    stream when profiling is on, and turn a non-zero return code into an exception."""
+    global LAUNCHES
+    LAUNCHES += n_kernels
+    if _prof is None:
+        rc = fn(*args)
+    else:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        rc = fn(*args)
+        e1.record()
+        _prof.setdefault(name, []).append((e0, e1))
+    check(rc, name)
+
+
 def stream_ptr():
     return torch.cuda.current_stream().cuda_stream
 

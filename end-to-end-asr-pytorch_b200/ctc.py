@@ -55,13 +55,12 @@ class _CTCFunction(torch.autograd.Function):
             sg_b, sg_t = (grad.stride(0), grad.stride(1)) if batch_first else (grad.stride(1), grad.stride(0))
         else:
             sg_b = sg_t = 0
-        rc = L.b2asr_ctc_loss_fwd_bwd(
+        _lib.call("b2asr_ctc_loss_fwd_bwd", 2, L.b2asr_ctc_loss_fwd_bwd,
             x.data_ptr(), sx_t, sx_b, targets.data_ptr(), targets.stride(0),
             in_len.data_ptr(), tgt_len.data_ptr(), T, B, V, Lmax, int(blank),
             int(bool(from_logits)), red, float(prescale),
             nll.data_ptr(), _lib.ptr(loss), _lib.ptr(grad), sg_t, sg_b,
             ws.data_ptr(), ws_bytes, _lib.stream_ptr())
-        _lib.check(rc, "b2asr_ctc_loss_fwd_bwd")
         ctx.red = red
         ctx.prescale = float(prescale)
         ctx.batch_first = batch_first
@@ -80,9 +79,8 @@ class _CTCFunction(torch.autograd.Function):
             g = grad * (g_out.reshape(shape) / ctx.prescale)
         else:
             g_out = g_out.reshape(1).to(torch.float32).contiguous()
-            rc = _lib.lib().b2asr_rescale_if_needed(grad.data_ptr(), grad.numel(), g_out.data_ptr(),
-                                                   ctx.prescale, _lib.stream_ptr())
-            _lib.check(rc, "b2asr_rescale_if_needed")
+            _lib.call("b2asr_rescale_if_needed", 1, _lib.lib().b2asr_rescale_if_needed, grad.data_ptr(),
+                      grad.numel(), g_out.data_ptr(), ctx.prescale, _lib.stream_ptr())
             g = grad
         return g, None, None, None, None, None, None, None, None
 
