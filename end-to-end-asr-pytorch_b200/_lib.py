@@ -23,8 +23,29 @@ c_i64 = ctypes.c_int64
 c_f = ctypes.c_float
 c_sz = ctypes.c_size_t
 
+
+
+class BeamIO(ctypes.Structure):
+    """Mirror of `b2asr_beam_io` (include/b2asr.h); field order and types must match exactly."""
+    _fields_ = [
+        ("x_ctc", c_p), ("T", ctypes.c_int32), ("V", ctypes.c_int32), ("n", ctypes.c_int32), ("K", ctypes.c_int32),
+        ("max_steps", ctypes.c_int32), ("w_att", c_f), ("w_ctc", c_f), ("w_lm", c_f),
+        ("att_logp", c_p), ("lm_logp", c_p),
+        ("valid_in", c_p), ("last_in", c_p), ("r_in", c_p), ("ctc_prob_in", c_p), ("sum_in", c_p),
+        ("valid_out", c_p), ("last_out", c_p), ("r_out", c_p), ("ctc_prob_out", c_p), ("sum_out", c_p),
+        ("parent_out", c_p),
+        ("cand", c_p), ("psi", c_p), ("r_all", c_p), ("topv", c_p), ("topi", c_p), ("step", c_p), ("ticket", c_p),
+        ("hist_parent", c_p), ("hist_tok", c_p), ("hist_score", c_p),
+        ("fin_count", c_p), ("fin_step", c_p), ("fin_row", c_p), ("fin_score", c_p), ("fin_sum", c_p),
+    ]
+
+
 # name -> (restype, argtypes); must list every symbol include/b2asr.h declares.
 _SIGNATURES = {
+    "b2asr_ctc_prefix_init": (c_i, [c_p, c_i, c_i, c_i, c_p, c_p]),
+    "b2asr_ctc_prefix_score": (c_i, [c_p, c_i, c_i, c_i, c_i, c_p, c_p, c_i, c_p, c_p, c_p]),
+    "b2asr_beam_io_size": (c_sz, []),
+    "b2asr_beam_step": (c_i, [ctypes.POINTER(BeamIO), c_p]),
     "b2asr_last_error": (ctypes.c_char_p, []),
     "b2asr_version": (c_i, []),
     "b2asr_arch": (c_i, []),
@@ -69,6 +90,9 @@ def lib():
             fn = getattr(L, name)
             fn.restype = res
             fn.argtypes = args
+        if L.b2asr_beam_io_size() != ctypes.sizeof(BeamIO):
+            raise B2asrError("b2asr_beam_io layout mismatch: library %d bytes, binding %d bytes"
+                             % (L.b2asr_beam_io_size(), ctypes.sizeof(BeamIO)))
         _lib = L
     return _lib
 

@@ -1,0 +1,390 @@
+// Kernel group (3): CTC prefix scorer + joint CTC/attention/RNN-LM beam step for sm_100a.
+//
+// Replaces, for all live hypotheses of one utterance and in ONE launch per decode step,
+//   reference src/asr.py:210-256  (candidate top-k, score fusion, <sos> hack, LM fusion, top-beam,
+//                                  child ranking and pruning),
+//   reference src/ctc.py:65-101   (CTCPrefixScore.cheap_compute: float32 logaddexp recursion over the
+//                                  encoder frames, -1e8 "log zero", the repeated-label rule :87-91),
+//   reference src/postprocess.py:71-106 (Hypothesis.avgScore / addTopk bookkeeping).
+// The recursion over T' frames is inherently sequential (each frame's logaddexp depends on the
+// previous frame's result and re-association would change float32 roundings, hence decoded tokens);
+// the kernel is latency-bound by design.  Parallelism: one CTA per hypothesis, the three dependent
+// chains of every candidate (non-blank state, blank state, cumulative prefix score) on three
+// adjacent lanes exchanging one value per frame by warp shuffle, ten candidates per warp.  Frame
+// data are gathered once into shared memory by the whole CTA; both top-k selections are CTA radix
+// selects followed by a warp-level rank sort; the last CTA to finish ranks the children and
+// gathers the survivors' state, so the step needs no second launch and no host round trip.
+#include "common.cuh"
+
+namespace b2asr {
+
+constexpr float kLogZero = -100000000.0f;     // ctc.py:11
+constexpr float kNegCtc  = -1000000.0f;       // asr.py:225
+constexpr float kNegSos  = -10000000.0f;      // asr.py:229
+constexpr int   kEos     = 1;
+constexpr int   kBeamNT  = 256;
+constexpr int   kCandPerWarp = 10;            // 3 lanes per candidate
+constexpr int   kMaxK    = 32;
+
+// numpy's float32 logaddexp (npy_logaddexpf): x==y -> x+ln2, else max + log1pf(expf(-|x-y|)).
+__device__ __forceinline__ float np_logaddexp(float x, float y) {
+  if (x == y) return __fadd_rn(x, 0.693147180559945309417232121458176568f);
+  const float tmp = __fsub_rn(x, y);
+  if (tmp > 0.f) return __fadd_rn(x, log1pf(expf(-tmp)));
+  if (tmp <= 0.f) return __fadd_rn(y, log1pf(expf(tmp)));
+  return tmp;                                  // NaN
+}
+
+__device__ __forceinline__ unsigned f2key(float f) {   // order-preserving float -> uint
+  const unsigned u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+struct TopkScratch {
+  int hist[256];
+  int sel, need, cnt, minidx;
+  float tv[kMaxK]; int ti[kMaxK];
+};
+
+// CTA-wide top-k (k <= 32) of vals[0..V): results sorted by (value desc, index asc) in outv/outi (shared).
+// Radix select of the k-th largest key (4 passes x 8 bits), collection of everything above it, ties at
+// the threshold taken lowest index first, then a warp-level rank sort of the k survivors.
+__device__ void cta_topk(const float* vals, int V, int k, float* outv, int* outi, TopkScratch* S) {
+  const int tid = threadIdx.x, NT = blockDim.x;
+  if (k > V) k = V;
+  unsigned prefix = 0u, mask = 0u;
+  if (tid == 0) S->need = k;
+  for (int pass = 0; pass < 4; ++pass) {
+    const int shift = 24 - 8 * pass;
+    for (int i = tid; i < 256; i += NT) S->hist[i] = 0;
+    __syncthreads();
+    for (int i = tid; i < V; i += NT) {
+      const unsigned key = f2key(vals[i]);
+      if ((key & mask) == prefix) atomicAdd(&S->hist[(key >> shift) & 255u], 1);
+    }
+    __syncthreads();
+    if (tid == 0) {
+      int need = S->need, cum = 0, b = 255;
+      for (; b > 0; --b) { if (cum + S->hist[b] >= need) break; cum += S->hist[b]; }
+      S->sel = b; S->need = need - cum;
+    }
+    __syncthreads();
+    prefix |= (unsigned)S->sel << shift;
+    mask |= 255u << shift;
+  }
+  const unsigned kth = prefix;
+  const int need = S->need;                    // entries equal to the threshold still to take (>= 1)
+  if (tid == 0) S->cnt = 0;
+  __syncthreads();
+  for (int i = tid; i < V; i += NT) {
+    if (f2key(vals[i]) > kth) { const int pos = atomicAdd(&S->cnt, 1); if (pos < kMaxK) { S->tv[pos] = vals[i]; S->ti[pos] = i; } }
+  }
+  __syncthreads();
+  int last = -1;
+  for (int r = 0; r < need; ++r) {             // usually a single round
+    if (tid == 0) S->minidx = 0x7fffffff;
+    __syncthreads();
+    int best = 0x7fffffff;
+    for (int i = tid; i < V; i += NT) if (i > last && f2key(vals[i]) == kth) { best = i; break; }
+    if (best != 0x7fffffff) atomicMin(&S->minidx, best);
+    __syncthreads();
+    last = S->minidx;
+    if (tid == 0 && last != 0x7fffffff) { const int pos = S->cnt++; if (pos < kMaxK) { S->tv[pos] = vals[last]; S->ti[pos] = last; } }
+    __syncthreads();
+  }
+  // warp-level rank sort
+  if (tid < 32) {
+    const int n = min(S->cnt, k);
+    const float v = tid < n ? S->tv[tid] : -INFINITY;
+    const int ix = tid < n ? S->ti[tid] : 0x7fffffff;
+    int rank = 0;
+#pragma unroll
+    for (int m = 0; m < 32; ++m) {
+      const float vm = __shfl_sync(kFull, v, m);
+      const int im = __shfl_sync(kFull, ix, m);
+      if (m < n && (vm > v || (vm == v && im < ix))) ++rank;
+    }
+    if (tid < n) { outv[rank] = v; outi[rank] = ix; }
+    for (int j = n + tid; j < k; j += 32) { outv[j] = -INFINITY; outi[j] = -1; }
+  }
+  __syncthreads();
+}
+
+// Shared-memory frame tables of one hypothesis, filled by the whole CTA.
+struct PrefixTables { float* xk; float* xb; float* phiD; float* phiS; };   // xk [T][32]
+
+__device__ void prefix_fill_tables(const PrefixTables& tb, const float* x, int T, int V, const float* r_prev,
+                                   const int* cand_sm, int K, int start) {
+  const int tid = threadIdx.x, NT = blockDim.x;
+  for (int i = tid; i < T * 32; i += NT) {
+    const int t = i >> 5, k = i & 31;
+    tb.xk[i] = k < K ? __ldg(x + (long long)t * V + cand_sm[k]) : 0.f;
+  }
+  for (int t = tid; t < T; t += NT) {
+    tb.xb[t] = __ldg(x + (long long)t * V);                     // blank = 0 (ctc.py:12)
+    if (t >= start) {
+      const float pnb = r_prev[2 * (t - 1)], pb = r_prev[2 * (t - 1) + 1];
+      tb.phiD[t] = np_logaddexp(pnb, pb);                        // ctc.py:87-93
+      tb.phiS[t] = np_logaddexp(pnb, kLogZero);                  // candidate repeats the last label
+    }
+  }
+}
+
+// The sequential recursion (ctc.py:85-98).  Executed by warps 0..ceil(K/10)-1; lane = 3*c + role with
+// role 0: r[t,0] (ends in non-blank), 1: r[t,1] (ends in blank), 2: psi.  r rows are written with the
+// caller's strides: element (t,k,j) at r_out[t*st_t + k*st_k + j].
+__device__ void prefix_recursion(const PrefixTables& tb, int T, int K, int prefix_len, int last,
+                                 const int* cand_sm, float* psi_out, float* r_out, long long st_t, long long st_k) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int c = lane / 3, role = lane - 3 * c;
+  const int k = warp * kCandPerWarp + c;
+  const bool on = (c < kCandPerWarp) && (k < K);
+  const int start = max(1, prefix_len);
+  const bool same = on && (cand_sm[k] == last);
+  // rows before start-1 (and the blank column of row start-1) are "log zero" (ctc.py:73)
+  if (on && role < 2) {
+    for (int t = 0; t < min(start, T); ++t) r_out[t * st_t + k * st_k + role] = kLogZero;
+  }
+  float cur = kLogZero;
+  if (on && role != 1 && prefix_len == 0) cur = tb.xk[k];       // r[0,0,:] = x[0,cands]; psi = r[start-1,0,:]
+  if (on && role == 0 && start - 1 < T) r_out[(start - 1) * st_t + k * st_k] = cur;
+  for (int t = start; t < T; ++t) {
+    const float left = __shfl_up_sync(kFull, cur, 1);            // role 1 reads its candidate's r[t-1,0]
+    if (on) {
+      const float phi = same ? tb.phiS[t] : tb.phiD[t];
+      const float xe = tb.xk[t * 32 + k];
+      const float b = role == 0 ? phi : (role == 1 ? left : __fadd_rn(phi, xe));
+      const float add = role == 0 ? xe : (role == 1 ? tb.xb[t] : 0.f);
+      float v = np_logaddexp(cur, b);
+      if (role != 2) v = __fadd_rn(v, add);
+      cur = v;
+      if (role < 2) r_out[t * st_t + k * st_k + role] = v;
+    }
+  }
+  if (on && role == 2) psi_out[k] = cur;
+}
+
+__host__ __device__ inline size_t prefix_smem_floats(int T) { return (size_t)T * 32 + 3 * (size_t)((T + 3) / 4 * 4); }
+
+// ------------------------------------------------------------------------------------------------
+// Stand-alone scorer kernels (API parity with CTCPrefixScore)
+// ------------------------------------------------------------------------------------------------
+__global__ void prefix_init_kernel(const float* x, int T, int V, int blank, float* r) {
+  // sequential fp32 running sum, one thread: bit-exact with ctc.py:21-27
+  if (threadIdx.x == 0 && blockIdx.x == 0) {
+    float acc = 0.f;
+    for (int t = 0; t < T; ++t) {
+      const float xv = x[(long long)t * V + blank];
+      acc = t == 0 ? xv : __fadd_rn(acc, xv);
+      r[2 * t] = kLogZero; r[2 * t + 1] = acc;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kBeamNT) prefix_score_kernel(const float* x, int T, int V, int prefix_len, int last,
+                                                              const float* r_prev, const int* cands, int K,
+                                                              float* psi, float* r_out) {
+  extern __shared__ __align__(16) float smf[];
+  __shared__ int cand_sm[kMaxK];
+  const int Tp = (T + 3) / 4 * 4;
+  PrefixTables tb{smf, smf + (size_t)T * 32, smf + (size_t)T * 32 + Tp, smf + (size_t)T * 32 + 2 * Tp};
+  if (threadIdx.x < kMaxK) cand_sm[threadIdx.x] = threadIdx.x < K ? min(V - 1, max(0, cands[threadIdx.x])) : 0;
+  __syncthreads();
+  prefix_fill_tables(tb, x, T, V, r_prev, cand_sm, K, max(1, prefix_len));
+  __syncthreads();
+  if ((threadIdx.x >> 5) * kCandPerWarp < K) prefix_recursion(tb, T, K, prefix_len, last, cand_sm, psi, r_out, 2, (long long)T * 2);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Fused beam step
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBeamNT) beam_step_kernel(b2asr_beam_io io) {
+  extern __shared__ __align__(16) float smf[];
+  __shared__ TopkScratch S;
+  __shared__ int cand_sm[kMaxK];
+  __shared__ float candv_sm[kMaxK];
+  __shared__ float psi_sm[kMaxK];
+  __shared__ float topv_sm[kMaxK];
+  __shared__ int topi_sm[kMaxK];
+  __shared__ unsigned is_last;
+
+  const int tid = threadIdx.x, NT = blockDim.x;
+  const int row = blockIdx.x, n = io.n, V = io.V, T = io.T, K = io.K;
+  const bool ctc = io.x_ctc != nullptr;
+  const int plen = *io.step;
+  float* val = smf;                                            // [V] attention log-probs, then fused scores
+  const int Vp = (V + 3) / 4 * 4;
+  const bool live = io.valid_in[row] != 0;
+
+  if (live) {
+    const float* att = io.att_logp + (long long)row * V;
+    for (int i = tid; i < V; i += NT) val[i] = att[i];
+    __syncthreads();
+    if (ctc) {
+      // ---- CTC candidates: top-K of the attention log-probs (asr.py:215-216) -----------------------
+      cta_topk(val, V, K, candv_sm, cand_sm, &S);
+      const int Tp = (T + 3) / 4 * 4;
+      float* base = smf + Vp;
+      PrefixTables tb{base, base + (size_t)T * 32, base + (size_t)T * 32 + Tp, base + (size_t)T * 32 + 2 * Tp};
+      const float* r_prev = io.r_in + (long long)row * T * 2;
+      prefix_fill_tables(tb, io.x_ctc, T, V, r_prev, cand_sm, K, max(1, plen));
+      __syncthreads();
+      // ---- prefix scores of prefix+[c] (ctc.py:65-101) ------------------------------------------------
+      if ((tid >> 5) * kCandPerWarp < K)
+        prefix_recursion(tb, T, K, plen, (int)io.last_in[row], cand_sm, psi_sm,
+                         io.r_all + (long long)row * T * K * 2, (long long)K * 2, 2);
+      __syncthreads();
+      // ---- fusion (asr.py:222-229): separate fp32 multiply and add roundings, as torch does -----------
+      const float neg = __fmul_rn(io.w_ctc, kNegCtc);
+      for (int i = tid; i < V; i += NT) val[i] = __fadd_rn(__fmul_rn(io.w_att, val[i]), neg);
+      __syncthreads();
+      if (tid < K) {
+        const float ctc_char = __fsub_rn(psi_sm[tid], io.ctc_prob_in[row]);      // asr.py:222
+        val[cand_sm[tid]] = __fadd_rn(__fmul_rn(io.w_att, candv_sm[tid]), __fmul_rn(io.w_ctc, ctc_char));
+        io.cand[row * K + tid] = cand_sm[tid];
+        io.psi[row * K + tid] = psi_sm[tid];
+      }
+      __syncthreads();
+      if (tid == 0) val[0] = kNegSos;                                           // asr.py:229
+      __syncthreads();
+    }
+    if (io.lm_logp != nullptr && io.w_lm > 0.f) {                               // asr.py:232-235
+      const float* lm = io.lm_logp + (long long)row * V;
+      for (int i = tid; i < V; i += NT) val[i] = __fadd_rn(val[i], __fmul_rn(io.w_lm, lm[i]));
+      __syncthreads();
+    }
+    // ---- top-`beam` of the fused scores (asr.py:238) ---------------------------------------------------
+    cta_topk(val, V, n, topv_sm, topi_sm, &S);
+    if (tid < n) { io.topv[row * n + tid] = topv_sm[tid]; io.topi[row * n + tid] = topi_sm[tid]; }
+  }
+
+  // ---- the last CTA to arrive prunes (asr.py:240-253, postprocess.py:71-106) ---------------------------
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) is_last = (atomicAdd(io.ticket, 1u) == (unsigned)n - 1u);
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+
+  float* avg = smf;                                            // [n*n] mean score of every child (or -inf)
+  int* slotk = reinterpret_cast<int*>(smf + n * n);            // [n*n] candidate slot of the child's token
+  const float cnt = (float)(plen + 1);
+  const int nc = n * n;
+  for (int c = tid; c < nc; c += NT) {
+    const int r = c / n;
+    float a = -INFINITY; int sk = -2;                           // -2: no child here; -1: child, token not a CTC candidate
+    if (io.valid_in[r]) {
+      const int tok = __ldcg(io.topi + c);
+      if (tok >= 0 && tok != kEos) {
+        a = __fdiv_rn(__fadd_rn(io.sum_in[r], __ldcg(io.topv + c)), cnt);      // postprocess.py:71-74
+        sk = -1;
+        if (ctc) for (int j = 0; j < K; ++j) if (__ldcg(io.cand + r * K + j) == tok) { sk = j; break; }
+      }
+    }
+    avg[c] = a; slotk[c] = sk;
+  }
+  int* slot_child = slotk + nc;                                // [n] child index occupying each survivor slot
+  for (int j = tid; j < n; j += NT) slot_child[j] = -1;
+  __syncthreads();
+  for (int c = tid; c < nc; c += NT) {
+    if (slotk[c] == -2) continue;
+    const float a = avg[c];
+    int rank = 0;                                              // stable descending order (asr.py:251)
+    for (int m = 0; m < nc; ++m)
+      if (slotk[m] != -2 && (avg[m] > a || (avg[m] == a && m < c))) ++rank;
+    if (rank < n) slot_child[rank] = c;
+  }
+  __syncthreads();
+  const long long hoff = (long long)min(plen, io.max_steps - 1) * n;
+  for (int j = tid; j < n; j += NT) {
+    const int c = slot_child[j];
+    if (c >= 0) {
+      const int r = c / n;
+      const float tv = __ldcg(io.topv + c);
+      const int tok = __ldcg(io.topi + c);
+      io.valid_out[j] = 1; io.last_out[j] = tok; io.parent_out[j] = r;
+      io.sum_out[j] = __fadd_rn(io.sum_in[r], tv);
+      io.ctc_prob_out[j] = (ctc && slotk[c] >= 0) ? __ldcg(io.psi + r * K + slotk[c]) : 0.f;
+      io.hist_parent[hoff + j] = r; io.hist_tok[hoff + j] = tok; io.hist_score[hoff + j] = tv;
+    } else {
+      io.valid_out[j] = 0; io.last_out[j] = 0; io.parent_out[j] = 0; io.sum_out[j] = 0.f; io.ctc_prob_out[j] = 0.f;
+      io.hist_parent[hoff + j] = -1; io.hist_tok[hoff + j] = -1; io.hist_score[hoff + j] = 0.f;
+    }
+  }
+  if (ctc) {                                                   // survivors inherit r[cand slot] (postprocess.py:95-97)
+    for (int i = tid; i < n * T * 2; i += NT) {
+      const int j = i / (T * 2), rem = i - j * (T * 2), t = rem >> 1, z = rem & 1;
+      const int c = slot_child[j];
+      float v = kLogZero;
+      if (c >= 0 && slotk[c] >= 0) v = __ldcg(io.r_all + (((long long)(c / n) * T + t) * K + slotk[c]) * 2 + z);
+      io.r_out[i] = v;
+    }
+  }
+  if (tid == 0) {                                              // <eos> finalises its parent, in row order (asr.py:244-245)
+    int f = *io.fin_count;
+    for (int r = 0; r < n; ++r) {
+      if (!io.valid_in[r]) continue;
+      for (int k2 = 0; k2 < n; ++k2) {
+        if (__ldcg(io.topi + r * n + k2) == kEos) {
+          const float tv = __ldcg(io.topv + r * n + k2);
+          if (f < io.max_steps * n) { io.fin_step[f] = plen; io.fin_row[f] = r; io.fin_score[f] = tv; io.fin_sum[f] = __fadd_rn(io.sum_in[r], tv); ++f; }
+          break;
+        }
+      }
+    }
+    *io.fin_count = f;
+    *io.step = plen + 1;
+    *io.ticket = 0u;
+  }
+}
+
+}  // namespace b2asr
+
+using namespace b2asr;
+
+extern "C" size_t b2asr_beam_io_size(void) { return sizeof(b2asr_beam_io); }
+
+extern "C" int b2asr_ctc_prefix_init(const float* x, int T, int V, int blank, float* r_out, void* stream) {
+  B2_REQUIRE(x && r_out, B2ASR_EINVAL, "ctc_prefix_init: null pointer argument");
+  B2_REQUIRE(T > 0 && V > 0 && blank >= 0 && blank < V, B2ASR_EINVAL, "ctc_prefix_init: bad sizes T=%d V=%d blank=%d", T, V, blank);
+  prefix_init_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(x, T, V, blank, r_out);
+  B2_CUDA_TRY(cudaGetLastError());
+  return B2ASR_OK;
+}
+
+extern "C" int b2asr_ctc_prefix_score(const float* x, int T, int V, int prefix_len, int last,
+                                      const float* r_prev, const int32_t* cands, int K,
+                                      float* psi, float* r_out, void* stream) {
+  B2_REQUIRE(x && r_prev && cands && psi && r_out, B2ASR_EINVAL, "ctc_prefix_score: null pointer argument");
+  B2_REQUIRE(T > 0 && V > 0 && prefix_len >= 0, B2ASR_EINVAL, "ctc_prefix_score: bad sizes T=%d V=%d", T, V);
+  B2_REQUIRE(K >= 1 && K <= kMaxK, B2ASR_EUNSUPPORTED, "ctc_prefix_score: K=%d candidates per call (1..%d)", K, kMaxK);
+  const size_t smem = prefix_smem_floats(T) * sizeof(float);
+  B2_REQUIRE(smem <= 200 * 1024, B2ASR_EUNSUPPORTED, "ctc_prefix_score: T=%d frames need %zu bytes of shared memory", T, smem);
+  B2_CUDA_TRY(cudaFuncSetAttribute(prefix_score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  prefix_score_kernel<<<1, kBeamNT, smem, (cudaStream_t)stream>>>(x, T, V, prefix_len, last, r_prev, cands, K, psi, r_out);
+  B2_CUDA_TRY(cudaGetLastError());
+  return B2ASR_OK;
+}
+
+extern "C" int b2asr_beam_step(const b2asr_beam_io* io, void* stream) {
+  B2_REQUIRE(io != nullptr, B2ASR_EINVAL, "beam_step: null io");
+  const b2asr_beam_io& a = *io;
+  B2_REQUIRE(a.att_logp && a.valid_in && a.last_in && a.sum_in && a.valid_out && a.last_out && a.sum_out && a.parent_out &&
+             a.topv && a.topi && a.step && a.ticket && a.hist_parent && a.hist_tok && a.hist_score && a.fin_count &&
+             a.fin_step && a.fin_row && a.fin_score && a.fin_sum && a.ctc_prob_out, B2ASR_EINVAL, "beam_step: null pointer argument");
+  B2_REQUIRE(a.n >= 1 && a.n <= kMaxK && a.V >= a.n && a.max_steps >= 1, B2ASR_EUNSUPPORTED, "beam_step: beam %d (1..%d), V=%d", a.n, kMaxK, a.V);
+  size_t floats = (size_t)((a.V + 3) / 4 * 4);
+  if (a.x_ctc) {
+    B2_REQUIRE(a.K >= 1 && a.K <= kMaxK && a.K <= a.V && a.T > 0, B2ASR_EUNSUPPORTED, "beam_step: K=%d CTC candidates (1..%d), T=%d", a.K, kMaxK, a.T);
+    B2_REQUIRE(a.r_in && a.r_out && a.ctc_prob_in && a.cand && a.psi && a.r_all, B2ASR_EINVAL, "beam_step: joint CTC needs r_in/r_out/ctc_prob_in/cand/psi/r_all");
+    floats += prefix_smem_floats(a.T);
+  }
+  const size_t prune = (size_t)2 * a.n * a.n + a.n;
+  if (floats < prune) floats = prune;
+  const size_t smem = floats * sizeof(float);
+  B2_REQUIRE(smem <= 200 * 1024, B2ASR_EUNSUPPORTED, "beam_step: V=%d, T=%d need %zu bytes of shared memory", a.V, a.T, smem);
+  B2_CUDA_TRY(cudaFuncSetAttribute(beam_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  beam_step_kernel<<<a.n, kBeamNT, smem, (cudaStream_t)stream>>>(a);
+  B2_CUDA_TRY(cudaGetLastError());
+  return B2ASR_OK;
+}

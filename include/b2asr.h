@@ -129,6 +129,77 @@ int b2asr_attn_step_bwd(int mode, const float* Wphi, const float* keys, int64_t 
                         float* pgrad, int64_t pgrad_stride,
                         int B, int T, int D, int A, int dec, int cluster, void* stream);
 
+/* ------------------------------------------------------------------------
+ * Kernel group (3): CTC prefix scorer and the joint CTC/attention/RNN-LM beam
+ * step.
+ *
+ * b2asr_ctc_prefix_init  == CTCPrefixScore.init_state, reference src/ctc.py:19-27:
+ *     r[t,1] = running fp32 sum of x[0..t, blank] (sequential order), r[t,0] = -1e8.
+ * b2asr_ctc_prefix_score == CTCPrefixScore.cheap_compute, src/ctc.py:65-101
+ *     (full_compute, src/ctc.py:29-63, is the same call with cands = 0..V-1 in
+ *     chunks of <= 32): float32 logaddexp recursion over frames in increasing t,
+ *     -1e8 "log zero" sentinel, repeated-label rule of ctc.py:87-91.
+ *   x [T,V] log-posteriors (row stride V); prefix_len = len(g); last = g[-1] (0 if empty)
+ *   r_prev [T,2]; cands [K] int32, K <= 32; psi [K] out; r_out [K,T,2] out.
+ * ---------------------------------------------------------------------- */
+int b2asr_ctc_prefix_init(const float* x, int T, int V, int blank, float* r_out, void* stream);
+int b2asr_ctc_prefix_score(const float* x, int T, int V, int prefix_len, int last,
+                           const float* r_prev, const int32_t* cands, int K,
+                           float* psi, float* r_out, void* stream);
+
+/* One decode step of Seq2Seq.beam_decode for ALL live hypotheses of one utterance
+ * (reference src/asr.py:210-256 + Hypothesis.addTopk/avgScore, src/postprocess.py:71-106),
+ * one launch, device-resident state, no host synchronisation:
+ *   per row (hypothesis): top-K CTC candidates of the attention log-probs (asr.py:215),
+ *   prefix scores of row.prefix+[c] (ctc.py:65-101), fused = (1-w)*att + w*scatter(ctc,-1e6),
+ *   fused[0] = -1e7 (asr.py:222-229), fused += w_lm*lm (asr.py:235), top-`beam` (asr.py:238);
+ *   then, by the last CTA to finish: <eos>(=1) finalises its parent, all other picks become
+ *   children ranked by mean score (fp32 left-to-right sum / count), stable in (row, rank)
+ *   order, best `beam` survive (asr.py:251-252); survivors' CTC state is gathered.
+ * Rows are fixed at n = beam; `valid` marks live ones (step 0: only row 0).
+ * All arrays are device memory owned by the caller; `in`/`out` state must not alias. */
+typedef struct b2asr_beam_io {
+  /* utterance constants */
+  const float* x_ctc;      /* [T,V] CTC log-posteriors (asr.py:180) or NULL: joint CTC off */
+  int32_t T, V;
+  int32_t n;               /* rows == decode_beam_size, <= 32 */
+  int32_t K;               /* CTC candidates per row = int(1.5*beam) (asr.py:160), <= 32 */
+  int32_t max_steps;       /* capacity of the history arrays */
+  float w_att, w_ctc, w_lm;/* float32(1-ctc_weight), float32(ctc_weight), float32(lm_weight; 0 = off) */
+  /* per step inputs */
+  const float* att_logp;   /* [n,V] log_softmax(char_trans(dec_out)) (asr.py:210) */
+  const float* lm_logp;    /* [n,V] log_softmax(lm_out) (asr.py:235) or NULL */
+  /* state in */
+  const int32_t* valid_in;     /* [n] */
+  const int64_t* last_in;      /* [n] last token of the prefix (0 = <sos>) */
+  const float*   r_in;         /* [n,T,2] CTC prefix state */
+  const float*   ctc_prob_in;  /* [n] cumulative CTC prefix log-prob (root 0) */
+  const float*   sum_in;       /* [n] fp32 left-to-right sum of the prefix's token scores */
+  /* state out */
+  int32_t* valid_out; int64_t* last_out; float* r_out; float* ctc_prob_out; float* sum_out;
+  int64_t* parent_out;     /* [n] row each survivor descends from (gather index for the neural state) */
+  /* scratch */
+  int32_t* cand;           /* [n,K] */
+  float*   psi;            /* [n,K] */
+  float*   r_all;          /* [n,T,K,2] */
+  float*   topv;           /* [n,n] */
+  int32_t* topi;           /* [n,n] */
+  int32_t* step;           /* [1] prefix length of the live rows; the kernel increments it */
+  uint32_t* ticket;        /* [1] zero before the first step; the kernel re-arms it */
+  /* history (for rebuilding token sequences on the host after the last step) */
+  int32_t* hist_parent;    /* [max_steps,n]  -1 = empty slot */
+  int32_t* hist_tok;       /* [max_steps,n] */
+  float*   hist_score;     /* [max_steps,n] fused score of the token */
+  int32_t* fin_count;      /* [1] */
+  int32_t* fin_step;       /* [max_steps*n] step at which the parent was finalised */
+  int32_t* fin_row;        /* [max_steps*n] parent row at that step */
+  float*   fin_score;      /* [max_steps*n] fused score of <eos> */
+  float*   fin_sum;        /* [max_steps*n] fp32 score sum including <eos> */
+} b2asr_beam_io;
+
+size_t b2asr_beam_io_size(void);   /* sizeof(b2asr_beam_io), for binding sanity checks */
+int    b2asr_beam_step(const b2asr_beam_io* io, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
