@@ -119,3 +119,54 @@ class CTCLoss(torch.nn.Module):
     def forward(self, log_probs, targets, input_lengths, target_lengths):
         return ctc_loss(log_probs, targets, input_lengths, target_lengths, self.blank, self.reduction,
                         self.from_logits, self.batch_first, self.grad_prescale)
+
+
+class CTCPrefixScore():
+    """CTC prefix scorer with the reference's interface (src/ctc.py:9-101), computed by the sm_100a
+    kernels of csrc/beam.cu instead of numpy on the host.
+
+    `x` is the [1,T,V] CTC log-posterior tensor (asr.py:180-181) and stays on the device; states and
+    scores are returned as numpy float32 arrays with the reference's shapes (r [T,2]; psi [K],
+    r [K,T,2]) so existing callers keep working.  The device-resident beam search (beam.py) does not
+    go through this class - it keeps the states on the device - but uses the same device code.
+    """
+
+    def __init__(self, x):
+        _lib.require_cuda(x)
+        self.logzero = -100000000.0
+        self.blank = 0
+        self.eos = 1
+        self.x = x.detach()[0].to(torch.float32).contiguous()       # [T,V] on the device
+        self.odim = x.shape[-1]
+        self.input_length = int(self.x.shape[0])
+
+    def init_state(self):
+        """r[t,1] = sum_{i<=t} x[i,blank] (sequential float32 sum), r[t,0] = logzero (ctc.py:19-27)."""
+        r = torch.empty(self.input_length, 2, dtype=torch.float32, device=self.x.device)
+        _lib.call("b2asr_ctc_prefix_init", 1, _lib.lib().b2asr_ctc_prefix_init, self.x.data_ptr(),
+                  self.input_length, self.odim, self.blank, r.data_ptr(), _lib.stream_ptr())
+        return r.cpu().numpy()
+
+    def _score(self, g, r_prev, candidates):
+        dev = self.x.device
+        T = self.input_length
+        cands = [int(c) for c in candidates]
+        rp = torch.as_tensor(r_prev, dtype=torch.float32).to(dev).contiguous()
+        last = int(g[-1]) if len(g) > 0 else 0
+        psi = torch.empty(len(cands), dtype=torch.float32, device=dev)
+        r = torch.empty(len(cands), T, 2, dtype=torch.float32, device=dev)
+        cd = torch.as_tensor(cands, dtype=torch.int32).to(dev)
+        for k0 in range(0, len(cands), 32):                         # <= 32 candidates per launch
+            k1 = min(len(cands), k0 + 32)
+            _lib.call("b2asr_ctc_prefix_score", 1, _lib.lib().b2asr_ctc_prefix_score, self.x.data_ptr(), T, self.odim,
+                      len(g), last, rp.data_ptr(), cd[k0:k1].data_ptr(), k1 - k0, psi[k0:k1].data_ptr(),
+                      r[k0:k1].data_ptr(), _lib.stream_ptr())
+        return psi.cpu().numpy(), r.cpu().numpy()
+
+    def cheap_compute(self, g, r_prev, candidates):
+        """Scores of g+[c] for the given candidates only (ctc.py:65-101) -> (psi [K], r [K,T,2])."""
+        return self._score(g, r_prev, candidates)
+
+    def full_compute(self, g, r_prev):
+        """Scores of g+[c] for every c in the vocabulary (ctc.py:29-63) -> (psi [V], r [V,T,2])."""
+        return self._score(g, r_prev, range(self.odim))

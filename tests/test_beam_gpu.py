@@ -1,0 +1,157 @@
+"""GPU parity: kernel (3) -- CTC prefix scorer and the joint beam step -- vs the CPU oracles
+(oracle/prefix_oracle.py restating reference src/ctc.py:19-101, oracle/beam_oracle.py restating
+src/asr.py:201-258 + src/postprocess.py:71-106) and vs the golden vectors the unmodified reference
+produced (tests/golden/prefix.pt, beam_*.pt).
+
+Bars:
+  * decoded token sequences IDENTICAL given identical logits (north_star): oracle and kernel are fed
+    the same attention / LM log-prob tables and the same CTC posteriors;
+  * prefix scores psi and states r: |a-b| <= 1e-5*|b| + 1e-5 (float32 logaddexp: CUDA expf/log1pf
+    differ from glibc's by an ulp here and there; the sequential evaluation order is the same);
+    entries that are the -1e8 "log zero" sentinel must match exactly;
+  * init_state (a sequential fp32 sum): bit-exact.
+"""
+import importlib
+import os
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import beam_oracle as bo
+from oracle import prefix_oracle as po
+
+pytestmark = pytest.mark.gpu
+G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def _m(name):
+    return importlib.import_module("end-to-end-asr-pytorch_b200." + name)
+
+
+def close(a, b, rtol=1e-5, atol=1e-5):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    sentinel = b <= -5e7
+    ok = np.abs(a - b) <= rtol * np.abs(b) + atol
+    return bool(np.all(np.where(sentinel, np.abs(a - b) <= 16.0, ok)))     # fp32 spacing at 1e8 is 8
+
+
+def test_prefix_scorer_matches_reference_golden(cuda):
+    g = torch.load(os.path.join(G, "prefix.pt"), weights_only=False)
+    sc = _m("ctc").CTCPrefixScore(g["x"][None].to(cuda))
+    assert np.array_equal(sc.init_state(), g["init"])
+    for c in g["calls"]:
+        psi, r = sc.cheap_compute(c["prefix"], c["r_prev"], c["cands"])
+        assert psi.shape == c["psi"].shape and r.shape == c["r"].shape
+        assert close(psi, c["psi"]) and close(r, c["r"])
+    f = g["full"]
+    psi, r = sc.full_compute(f["prefix"], f["r_prev"])
+    assert close(psi, f["psi"]) and close(r, f["r"])
+
+
+@pytest.mark.parametrize("T,V,K", [(40, 31, 12), (400, 5000, 30), (750, 5000, 30), (97, 63, 32)])
+def test_prefix_scorer_chain_matches_oracle(cuda, T, V, K):
+    g = torch.Generator().manual_seed(T + V)
+    x = F.log_softmax(torch.randn(T, V, generator=g) * 3, dim=-1)
+    sc = _m("ctc").CTCPrefixScore(x[None].to(cuda))
+    xn = x.numpy()
+    r_or = po.blank_only_state(xn)
+    r_gpu = sc.init_state()
+    assert np.array_equal(r_or, r_gpu)
+    prefix = []
+    for step in range(5):
+        cands = [int(c) for c in torch.randperm(V, generator=g)[:K]]
+        if prefix and step % 2 == 0:
+            cands[3] = prefix[-1]                       # repeated-label rule (ctc.py:87-91)
+        psi_o, ro = po.extend_prefix(xn, prefix, r_or, cands)
+        psi_g, rg = sc.cheap_compute(prefix, r_gpu, cands)
+        assert close(psi_g, psi_o), (step, np.abs(psi_g - psi_o).max())
+        assert close(rg, ro), step
+        pick = 3 if (prefix and step % 2 == 0) else 1
+        prefix = prefix + [cands[pick]]
+        r_or, r_gpu = ro[pick], rg[pick]
+
+
+def _table_search(cuda, V, T, n, steps, ctc_w, lm_w, seed, M=8, eos_boost=0.0, sharp=2.0):
+    """Run oracle and kernel on identical log-prob tables: logp = table[step][last_token % M]."""
+    g = torch.Generator().manual_seed(seed)
+    x_ctc = F.log_softmax(torch.randn(T, V, generator=g) * sharp, dim=-1) if ctc_w > 0 else None
+    logits = torch.randn(steps, M, V, generator=g) * sharp
+    logits[:, :, 1] += eos_boost
+    att = F.log_softmax(logits, dim=-1)
+    lm = F.log_softmax(torch.randn(steps, M, V, generator=g) * sharp, dim=-1) if lm_w > 0 else None
+    beam = _m("beam")
+    bs = beam.BeamSearch(V, n, steps, cuda, x_ctc=x_ctc, ctc_weight=ctc_w, lm_weight=lm_w)
+    att_d = att.to(cuda)
+    lm_d = lm.to(cuda) if lm is not None else None
+    for t in range(steps):
+        idx = bs.last_tokens % M
+        bs.step(att_d[t].index_select(0, idx).contiguous(),
+                lm_d[t].index_select(0, idx).contiguous() if lm_d is not None else None)
+    got = bs.results()
+
+    def step_fn(entry):
+        t = len(entry.tokens)
+        last = entry.tokens[-1] if entry.tokens else 0
+        return att[t][last % M], (lm[t][last % M] if lm is not None else None), None
+
+    want = bo.joint_beam_search(step_fn, None, steps, n, None if x_ctc is None else x_ctc.numpy(), ctc_w, lm_w)
+    return got, want
+
+
+CASES = [
+    # V,    T,   n, steps, ctc_w, lm_w, eos_boost
+    (40, 30, 4, 8, 0.5, 0.0, 0.0),
+    (40, 30, 4, 8, 0.5, 0.5, 3.0),       # <eos> often inside the top-k: finals + children from one parent
+    (31, 60, 5, 12, 0.3, 0.0, 1.0),
+    (63, 97, 8, 10, 0.0, 0.0, 2.0),      # joint CTC off (attention-only decoding)
+    (63, 97, 8, 10, 0.0, 0.4, 2.0),
+    (5000, 400, 20, 12, 0.5, 0.5, 4.0),  # M4 shape: beam 20, K=30, V=5000, T'=400
+    (5000, 400, 20, 12, 0.5, 0.0, 0.0),
+    (40, 30, 1, 8, 0.5, 0.0, 2.0),       # beam 1 returns at the first <eos> (asr.py:246-247)
+    (40, 30, 1, 6, 0.0, 0.0, -5.0),      # beam 1, never finishes
+]
+
+
+@pytest.mark.parametrize("V,T,n,steps,ctc_w,lm_w,eos_boost", CASES)
+def test_beam_search_tokens_identical_to_oracle(cuda, V, T, n, steps, ctc_w, lm_w, eos_boost):
+    got, want = _table_search(cuda, V, T, n, steps, ctc_w, lm_w, seed=V + 7 * n + steps, eos_boost=eos_boost)
+    assert [h.outIndex for h in got] == [[int(t) for t in e.tokens] for e in want]
+    for h, e in zip(got, want):
+        a, b = float(h.avgScore()), float(e.mean_score())
+        assert abs(a - b) <= 1e-5 * abs(b) + 1e-5
+        sa = np.array([float(s) for s in h.output_scores]); sb = np.array([float(s) for s in e.scores])
+        assert np.all(np.abs(sa - sb) <= 1e-5 * np.abs(sb) + 1e-5)
+
+
+def _load_model(g, cuda):
+    asr, rnnlm = _m("asr"), _m("rnnlm")
+    model = asr.Seq2Seq(g["x"], g["vocab"], g["cfg"])
+    model.load_state_dict(g["state_dict"], strict=True)
+    model.eval()
+    model.joint_ctc = g["ctc_weight"] > 0
+    model.ctc_weight = g["ctc_weight"]
+    model.decode_lm_weight = g["lm_weight"]
+    lm = rnnlm.RNN_LM(*g["lm_dims"][:3], layers=g["lm_dims"][3])
+    lm.load_state_dict(g["lm_state_dict"])
+    lm.eval()
+    model.rnn_lm = lm
+    return model.to(cuda)
+
+
+@pytest.mark.parametrize("name", ["beam_joint.pt", "beam_att_only.pt", "beam_ctc.pt"])
+@pytest.mark.parametrize("graph", [False, True])
+def test_full_beam_decode_matches_reference_golden(cuda, name, graph):
+    """Whole Seq2Seq.beam_decode on the tiny reference model: tokens identical to what the unmodified
+    reference decoded, mean scores within 1e-4 (the neural parts run batched over the beam here)."""
+    g = torch.load(os.path.join(G, name), weights_only=False)
+    model = _load_model(g, cuda)
+    beam = _m("beam")
+    with torch.no_grad():
+        hyps = beam.beam_decode(model, g["x"].to(cuda), g["decode_step"], g["state_len"], g["beam"], use_graph=graph)
+    assert [h.outIndex for h in hyps] == [r["tokens"] for r in g["hyps"]]
+    for h, r in zip(hyps, g["hyps"]):
+        assert abs(float(h.avgScore()) - r["avg"]) <= 1e-4 * abs(r["avg"]) + 1e-5
+    again = model.beam_decode(g["x"].to(cuda), g["decode_step"], g["state_len"], g["beam"])     # module API
+    assert [h.outIndex for h in again] == [r["tokens"] for r in g["hyps"]]
