@@ -13,6 +13,7 @@ tf_rate 1.0, Adadelta).  Prints ONE JSON line (rank 0).
 import argparse
 import importlib
 import json
+import math
 import os
 import subprocess
 import sys
@@ -162,6 +163,84 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------------------------------------
+# joint beam decode leg (BASELINE.json metric part 2: beam-decode RTF; SURVEY.md section 8d workload M4)
+# ------------------------------------------------------------------------------------------------
+DEC = dict(workload="libri_m2s", beam=20, ctc_weight=0.5, lm_weight=0.5, ratio=0.1, lm=(650, 650, 2), frames=1600)
+
+
+def decode_leg(dev, rank, world, n_utt, dist):
+    """Each rank decodes its own `n_utt` synthetic 16-s utterances (utterance-sharded, no collective):
+    shipped libri_example.yaml-shaped model (VGGBiRNN, V=5000) + RNN_LM(650,650,2), beam 20,
+    decode_ctc_weight 0.5, decode_lm_weight 0.5, max_decode_step_ratio 0.1 -> 160 steps."""
+    import torch
+    asr, rnnlm, syn = pkg("asr"), pkg("rnnlm"), pkg("synthetic")
+    lib = pkg("_lib")
+    w = syn.WORKLOADS[DEC["workload"]]
+    torch.manual_seed(0)
+    model = asr.Seq2Seq(torch.zeros(1, 8, w["d_in"]), w["vocab"], w["cfg"]).to(dev).eval()
+    model.joint_ctc, model.ctc_weight, model.decode_lm_weight = True, DEC["ctc_weight"], DEC["lm_weight"]
+    model.rnn_lm = rnnlm.RNN_LM(DEC["lm"][0], DEC["lm"][1], w["vocab"], layers=DEC["lm"][2]).to(dev).eval()
+    g = torch.Generator().manual_seed(4321 + rank)
+    utts = [torch.randn(1, DEC["frames"], w["d_in"], generator=g).pin_memory() for _ in range(n_utt + 1)]
+    steps = int(math.ceil(DEC["frames"] * DEC["ratio"]))
+
+    def one(xh):
+        x = xh.to(dev, non_blocking=True)                          # host features in, token ids out
+        hyps = model.beam_decode(x, steps, [DEC["frames"]], DEC["beam"])
+        return hyps[0].outIndex
+
+    with torch.no_grad():
+        one(utts[-1])                                              # warm-up utterance
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        l0 = lib.LAUNCHES
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for u in range(n_utt):
+            one(utts[u])
+        e1.record()
+        torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    sec = float(ms) * 1e-3
+    audio = n_utt * world * DEC["frames"] * 0.01
+    return {"rtf": sec / audio * world, "rtf_aggregate": sec / audio, "utterances_per_s": n_utt * world / sec,
+            "ms_per_utterance": sec / n_utt * 1e3, "decode_steps": steps, "utterances_per_gpu": n_utt,
+            "beam": DEC["beam"], "ctc_weight": DEC["ctc_weight"], "lm_weight": DEC["lm_weight"], "vocab": w["vocab"],
+            "audio_s_per_utterance": DEC["frames"] * 0.01, "gpu_launches": lib.LAUNCHES - l0,
+            "note": "rtf = per-GPU wall clock / audio seconds (end to end: host features in, token ids out); "
+                    "rtf_aggregate divides by the audio all ranks decoded"}
+
+
+def cpu_decode_rate(n_steps=2):
+    """Oracle port of Seq2Seq.beam_decode (oracle/decode_oracle.py, restating asr.py:155-258 + ctc.py) on the host
+    cores for `n_steps` decode steps of one M4 utterance; RTF extrapolated to the full 160 steps."""
+    import torch
+    from oracle import decode_oracle as do
+    from oracle import model_oracle as mo
+    syn = pkg("synthetic")
+    w = syn.WORKLOADS[DEC["workload"]]
+    torch.manual_seed(0)
+    model = mo.OracleModel(w["d_in"], w["vocab"], w["cfg"]).eval()
+    lm = do.OracleLM(DEC["lm"][0], DEC["lm"][1], w["vocab"], layers=DEC["lm"][2]).eval()
+    x = torch.randn(1, DEC["frames"], w["d_in"], generator=torch.Generator().manual_seed(4321))
+    t0 = time.perf_counter()
+    do.beam_decode(model, lm, x, 1, [DEC["frames"]], DEC["beam"], DEC["ctc_weight"], DEC["lm_weight"])
+    t1 = time.perf_counter()
+    do.beam_decode(model, lm, x, 1 + n_steps, [DEC["frames"]], DEC["beam"], DEC["ctc_weight"], DEC["lm_weight"])
+    t2 = time.perf_counter()
+    per_step = ((t2 - t1) - (t1 - t0)) / n_steps            # steps 2.. carry the full beam; step 1 only the root
+    enc = t1 - t0
+    steps = int(math.ceil(DEC["frames"] * DEC["ratio"]))
+    rtf = (enc + per_step * steps) / (DEC["frames"] * 0.01)
+    return {"rtf": rtf, "ms_per_decode_step": per_step * 1e3, "cores": torch.get_num_threads(), "kind": "port",
+            "sample": "1 utterance: encoder + root step timed once, then %d full-beam decode steps; RTF extrapolated to %d steps"
+                      % (n_steps, steps)}
+
+
+# ------------------------------------------------------------------------------------------------
 # this repo's arm
 # ------------------------------------------------------------------------------------------------
 def run_native(args):
@@ -280,10 +359,18 @@ def run_native(args):
                     "share_of_step": k["ms_per_step"] / ms_step,
                     "note": "M2 keys+features (48 MB) are L2-resident across decoder steps; see DESIGN.md"}
 
+    decode = None
+    if not args.no_decode:
+        del ts, opt, model, resident
+        torch.cuda.empty_cache()
+        decode = decode_leg(dev, rank, world, args.decode_utts, dist)
+
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu:
         v, ms, cores, sample = cpu_train_step_rate(steps=2, warmup=0, budget_s=20.0)
         cpu_baseline = {"value": v, "unit": "utterances/s", "cores": cores, "kind": "port", "sample": sample}
+        if decode is not None:
+            decode["cpu_baseline"] = cpu_decode_rate()
 
     if rank == 0:
         out = {
@@ -298,7 +385,7 @@ def run_native(args):
             "clocks": clocks, "gpu_launches": launches,
             "e2e": {"value": e2e_value, "unit": "utterances/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h[0], "ms_per_step": ms_e2e / args.steps},
-            "roofline": roofline, "kernels": kernels, "cpu_baseline": cpu_baseline,
+            "roofline": roofline, "kernels": kernels, "cpu_baseline": cpu_baseline, "decode": decode,
         }
         print(json.dumps(out), flush=True)
     if world > 1:
@@ -312,6 +399,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-decode", action="store_true", help="skip the beam-decode RTF leg")
+    ap.add_argument("--decode-utts", type=int, default=4, help="utterances per GPU in the decode leg")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
