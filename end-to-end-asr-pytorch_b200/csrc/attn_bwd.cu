@@ -231,8 +231,9 @@ __global__ void __launch_bounds__(512, 1) attn_step_bwd_kernel(AttnArgs p) {
           dpre = dev * qa;
           dq_acc = fmaf(dev, kv, dq_acc);
         }
-        float* dk = dkb + (long long)(f0 + j) * A + tid;
-        *dk += dpre;
+        // fire-and-forget reduction (RED.ADD.F32): one owner per element and launch, so no contention, and
+        // no L2 round trip on the loop's critical path as a load-add-store would put there
+        red_add_f32(dkb + (long long)(f0 + j) * A + tid, dpre);
       }
       if (loc) {
         int idx;

@@ -28,11 +28,11 @@ constexpr int   kMaxK    = 32;
 
 // numpy's float32 logaddexp (npy_logaddexpf): x==y -> x+ln2, else max + log1pf(expf(-|x-y|)).
 __device__ __forceinline__ float np_logaddexp(float x, float y) {
-  if (x == y) return __fadd_rn(x, 0.693147180559945309417232121458176568f);
+  // branch-free form of the same arithmetic: both of numpy's branches compute max + log1pf(expf(-|x-y|))
   const float tmp = __fsub_rn(x, y);
-  if (tmp > 0.f) return __fadd_rn(x, log1pf(expf(-tmp)));
-  if (tmp <= 0.f) return __fadd_rn(y, log1pf(expf(tmp)));
-  return tmp;                                  // NaN
+  const float m = tmp > 0.f ? x : y;
+  const float r = __fadd_rn(m, log1pf(expf(-fabsf(tmp))));
+  return x == y ? __fadd_rn(x, 0.693147180559945309417232121458176568f) : r;
 }
 
 __device__ __forceinline__ unsigned f2key(float f) {   // order-preserving float -> uint
@@ -41,44 +41,48 @@ __device__ __forceinline__ unsigned f2key(float f) {   // order-preserving float
 }
 
 struct TopkScratch {
-  int hist[256];
-  int sel, need, cnt, minidx;
+  int cnt_iter[3];
+  int cnt, minidx;
   float tv[kMaxK]; int ti[kMaxK];
 };
 
+// number of vals whose key >= thr, summed over the CTA (every thread must call)
+__device__ __forceinline__ int cta_count_ge(const float* vals, int V, unsigned thr, int* slot) {
+  int c = 0;
+  for (int i = threadIdx.x; i < V; i += blockDim.x) c += f2key(vals[i]) >= thr;
+  c = __reduce_add_sync(kFull, c);
+  if ((threadIdx.x & 31) == 0 && c) atomicAdd(slot, c);
+  __syncthreads();
+  return *slot;
+}
+
 // CTA-wide top-k (k <= 32) of vals[0..V): results sorted by (value desc, index asc) in outv/outi (shared).
-// Radix select of the k-th largest key (4 passes x 8 bits), collection of everything above it, ties at
-// the threshold taken lowest index first, then a warp-level rank sort of the k survivors.
+// The k-th largest key is found by bisection over its 32 bits (one CTA-wide count per bit), everything
+// above it is collected, ties at the threshold are taken lowest index first, and the k survivors are
+// ordered by a warp-level rank sort.
 __device__ void cta_topk(const float* vals, int V, int k, float* outv, int* outi, TopkScratch* S) {
   const int tid = threadIdx.x, NT = blockDim.x;
   if (k > V) k = V;
-  unsigned prefix = 0u, mask = 0u;
-  if (tid == 0) S->need = k;
-  for (int pass = 0; pass < 4; ++pass) {
-    const int shift = 24 - 8 * pass;
-    for (int i = tid; i < 256; i += NT) S->hist[i] = 0;
-    __syncthreads();
-    for (int i = tid; i < V; i += NT) {
-      const unsigned key = f2key(vals[i]);
-      if ((key & mask) == prefix) atomicAdd(&S->hist[(key >> shift) & 255u], 1);
-    }
-    __syncthreads();
-    if (tid == 0) {
-      int need = S->need, cum = 0, b = 255;
-      for (; b > 0; --b) { if (cum + S->hist[b] >= need) break; cum += S->hist[b]; }
-      S->sel = b; S->need = need - cum;
-    }
-    __syncthreads();
-    prefix |= (unsigned)S->sel << shift;
-    mask |= 255u << shift;
+  unsigned prefix = 0u;
+  if (tid == 0) { S->cnt_iter[0] = 0; S->cnt_iter[1] = 0; S->cnt_iter[2] = 0; }
+  __syncthreads();
+  for (int it = 0; it < 32; ++it) {
+    const unsigned trial = prefix | (0x80000000u >> it);
+    const int c = cta_count_ge(vals, V, trial, &S->cnt_iter[it % 3]);
+    if (c >= k) prefix = trial;                 // the k-th largest key has this bit set
+    // re-arm the slot of iteration it+2: its last readers (iteration it-1) all passed the barrier above,
+    // and nobody adds to it before the next barrier
+    if (tid == 0) S->cnt_iter[(it + 2) % 3] = 0;
   }
+  __syncthreads();
   const unsigned kth = prefix;
-  const int need = S->need;                    // entries equal to the threshold still to take (>= 1)
   if (tid == 0) S->cnt = 0;
   __syncthreads();
   for (int i = tid; i < V; i += NT) {
     if (f2key(vals[i]) > kth) { const int pos = atomicAdd(&S->cnt, 1); if (pos < kMaxK) { S->tv[pos] = vals[i]; S->ti[pos] = i; } }
   }
+  __syncthreads();
+  const int need = k - S->cnt;                 // entries equal to the threshold still to take (>= 1)
   __syncthreads();
   int last = -1;
   for (int r = 0; r < need; ++r) {             // usually a single round
@@ -116,7 +120,9 @@ struct PrefixTables { float* xk; float* xb; float* phiD; float* phiS; };   // xk
 __device__ void prefix_fill_tables(const PrefixTables& tb, const float* x, int T, int V, const float* r_prev,
                                    const int* cand_sm, int K, int start) {
   const int tid = threadIdx.x, NT = blockDim.x;
-  for (int i = tid; i < T * 32; i += NT) {
+  const int first = start == 1 ? 0 : start;        // row 0 is read only for the empty prefix (start == 1)
+#pragma unroll 8
+  for (int i = first * 32 + tid; i < T * 32; i += NT) {
     const int t = i >> 5, k = i & 31;
     tb.xk[i] = k < K ? __ldg(x + (long long)t * V + cand_sm[k]) : 0.f;
   }
@@ -320,17 +326,20 @@ __global__ void __launch_bounds__(kBeamNT) beam_step_kernel(b2asr_beam_io io) {
       io.r_out[i] = v;
     }
   }
+  __syncthreads();
+  int* eos_at = slot_child;                                    // reuse: [n] child index holding <eos> per row, or -1
+  for (int j = tid; j < n; j += NT) eos_at[j] = -1;
+  __syncthreads();
+  for (int c = tid; c < nc; c += NT)
+    if (io.valid_in[c / n] && __ldcg(io.topi + c) == kEos) eos_at[c / n] = c;   // top-k indices are unique per row
+  __syncthreads();
   if (tid == 0) {                                              // <eos> finalises its parent, in row order (asr.py:244-245)
     int f = *io.fin_count;
     for (int r = 0; r < n; ++r) {
-      if (!io.valid_in[r]) continue;
-      for (int k2 = 0; k2 < n; ++k2) {
-        if (__ldcg(io.topi + r * n + k2) == kEos) {
-          const float tv = __ldcg(io.topv + r * n + k2);
-          if (f < io.max_steps * n) { io.fin_step[f] = plen; io.fin_row[f] = r; io.fin_score[f] = tv; io.fin_sum[f] = __fadd_rn(io.sum_in[r], tv); ++f; }
-          break;
-        }
-      }
+      const int c = eos_at[r];
+      if (c < 0) continue;
+      const float tv = __ldcg(io.topv + c);
+      if (f < io.max_steps * n) { io.fin_step[f] = plen; io.fin_row[f] = r; io.fin_score[f] = tv; io.fin_sum[f] = __fadd_rn(io.sum_in[r], tv); ++f; }
     }
     *io.fin_count = f;
     *io.step = plen + 1;

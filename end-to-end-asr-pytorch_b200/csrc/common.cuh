@@ -119,6 +119,10 @@ __device__ __forceinline__ void fence_proxy_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
 
+__device__ __forceinline__ void red_add_f32(float* gaddr, float v) {
+  asm volatile("red.global.add.f32 [%0], %1;" ::"l"(gaddr), "f"(v) : "memory");
+}
+
 // accurate tanh from one ex2 and one reciprocal: 1 - 2/(1+e^{2x}); abs error ~1e-7
 __device__ __forceinline__ float tanh_acc(float x) {
   const float xc = fminf(fmaxf(x, -15.f), 15.f);
