@@ -1,7 +1,7 @@
 """Kernel group (2a): key projection K = tanh(h psi^T + b), once per batch (reference asr.py:412-419).
 
-Forward runs on the tcgen05 kernel when csrc provides b2asr_attn_keys (3xTF32 split for fp32-class
-accuracy); backward is two plain library GEMMs around the tanh derivative.
+Forward runs on the tcgen05 kernel b2asr_attn_keys (3xTF32 split for fp32-class accuracy); backward is
+two plain library GEMMs around the tanh derivative (cuBLAS, as SURVEY.md section 2 scopes dense GEMMs).
 """
 import torch
 import torch.nn.functional as F
@@ -28,11 +28,16 @@ class _KeysFunction(torch.autograd.Function):
 
 
 def _forward(h, w, b):
-    L = _lib.lib()
-    if hasattr(L, "b2asr_attn_keys"):
-        from . import _keys_native
-        return _keys_native.forward(h, w, b)
-    return torch.tanh(F.linear(h, w, b))                   # library GEMM until the tcgen05 kernel lands
+    """tcgen05 kernel (csrc/keys.cu): h [..., D] contiguous -> keys [..., A]."""
+    h = h.contiguous()
+    w = w.contiguous()
+    b = b.contiguous()
+    D, A = h.shape[-1], w.shape[0]
+    M = h.numel() // D
+    out = torch.empty(h.shape[:-1] + (A,), dtype=torch.float32, device=h.device)
+    _lib.call("b2asr_attn_keys", 1, _lib.lib().b2asr_attn_keys, h.data_ptr(), w.data_ptr(), b.data_ptr(),
+              out.data_ptr(), M, D, A, _lib.stream_ptr())
+    return out
 
 
 def project(h, w, b):

@@ -18,6 +18,7 @@ back once and the `Hypothesis` list the reference returns is rebuilt from it.
   beam_decode    the Seq2Seq.beam_decode body
 """
 import math
+import os
 
 import numpy as np
 import torch
@@ -177,11 +178,15 @@ class BeamSearch:
         return outs[:self.n]
 
 
-def beam_decode(model, audio_feature, decode_step, state_len, decode_beam_size, use_graph=True):
+def beam_decode(model, audio_feature, decode_step, state_len, decode_beam_size, use_graph=None):
     """Seq2Seq.beam_decode (asr.py:155-258) for one utterance; returns the top `decode_beam_size`
     Hypothesis objects sorted by mean score."""
     assert audio_feature.shape[0] == 1
     assert model.training is False
+    if use_graph is None:
+        # measured on B200 (profiles/): the step is GPU-bound, replay saves nothing over eager launches and
+        # capture + instantiation costs 0.1-0.5 s per utterance shape, so graphs are opt-in
+        use_graph = os.environ.get('B2ASR_DECODE_GRAPH', '0') == '1'
     if not audio_feature.is_cuda:
         raise RuntimeError('beam_decode runs on the sm_100a kernels only (no CPU path); move the model and input to a CUDA device')
     n = int(decode_beam_size)

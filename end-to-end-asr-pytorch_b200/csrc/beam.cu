@@ -46,30 +46,39 @@ struct TopkScratch {
   float tv[kMaxK]; int ti[kMaxK];
 };
 
-// number of vals whose key >= thr, summed over the CTA (every thread must call)
-__device__ __forceinline__ int cta_count_ge(const float* vals, int V, unsigned thr, int* slot) {
-  int c = 0;
-  for (int i = threadIdx.x; i < V; i += blockDim.x) c += f2key(vals[i]) >= thr;
-  c = __reduce_add_sync(kFull, c);
-  if ((threadIdx.x & 31) == 0 && c) atomicAdd(slot, c);
-  __syncthreads();
-  return *slot;
-}
+constexpr int kKeysPerThread = 24;            // register-resident keys: V <= 24*256 = 6144, else the shared-memory loop
 
 // CTA-wide top-k (k <= 32) of vals[0..V): results sorted by (value desc, index asc) in outv/outi (shared).
-// The k-th largest key is found by bisection over its 32 bits (one CTA-wide count per bit), everything
-// above it is collected, ties at the threshold are taken lowest index first, and the k survivors are
-// ordered by a warp-level rank sort.
+// The k-th largest key is found by bisection over its 32 bits (one CTA-wide count per bit; the keys
+// stay in registers), everything above it is collected, ties at the threshold are taken lowest index
+// first, and the k survivors are ordered by a warp-level rank sort.
 __device__ void cta_topk(const float* vals, int V, int k, float* outv, int* outi, TopkScratch* S) {
   const int tid = threadIdx.x, NT = blockDim.x;
   if (k > V) k = V;
+  const bool in_regs = V <= kKeysPerThread * NT;
+  unsigned keys[kKeysPerThread];
+#pragma unroll
+  for (int j = 0; j < kKeysPerThread; ++j) {
+    const int i = tid + j * NT;
+    keys[j] = (in_regs && i < V) ? f2key(vals[i]) : 0u;       // key 0 never reaches a threshold (>= 1)
+  }
   unsigned prefix = 0u;
   if (tid == 0) { S->cnt_iter[0] = 0; S->cnt_iter[1] = 0; S->cnt_iter[2] = 0; }
   __syncthreads();
   for (int it = 0; it < 32; ++it) {
     const unsigned trial = prefix | (0x80000000u >> it);
-    const int c = cta_count_ge(vals, V, trial, &S->cnt_iter[it % 3]);
-    if (c >= k) prefix = trial;                 // the k-th largest key has this bit set
+    int c = 0;
+    if (in_regs) {
+#pragma unroll
+      for (int j = 0; j < kKeysPerThread; ++j) c += keys[j] >= trial;
+    } else {
+      for (int i = tid; i < V; i += NT) c += f2key(vals[i]) >= trial;
+    }
+    c = __reduce_add_sync(kFull, c);
+    int* slot = &S->cnt_iter[it % 3];
+    if ((tid & 31) == 0 && c) atomicAdd(slot, c);
+    __syncthreads();
+    if (*slot >= k) prefix = trial;             // the k-th largest key has this bit set
     // re-arm the slot of iteration it+2: its last readers (iteration it-1) all passed the barrier above,
     // and nobody adds to it before the next barrier
     if (tid == 0) S->cnt_iter[(it + 2) % 3] = 0;

@@ -81,6 +81,17 @@ int b2asr_ctc_loss_fwd_bwd(const float* x, int64_t sx_t, int64_t sx_b,
 int b2asr_rescale_if_needed(float* buf, int64_t n, const float* upstream, float assumed, void* stream);
 
 /* ------------------------------------------------------------------------
+ * Kernel group (2a): key projection, reference src/asr.py:419
+ *     self.comp_listener_feature = torch.tanh(self.psi(listener_feature))
+ * out[m,a] = tanh( sum_d h[m,d] * W[a,d] + bias[a] ),  h [M,D] (M = B*T' rows, contiguous), W [A,D]
+ * (psi.weight), bias [A] (psi.bias), out [M,A].  tcgen05 tensor cores, error-compensated TF32
+ * (hi/lo operand split, three MMAs per k-step, fp32 accumulation in tensor memory) so the result
+ * meets the 1e-4 fp32 parity bar.  D % 4 == 0; h and W 16-byte aligned.
+ * ---------------------------------------------------------------------- */
+int b2asr_attn_keys(const float* h, const float* W, const float* bias, float* out,
+                    int M, int D, int A, void* stream);
+
+/* ------------------------------------------------------------------------
  * Kernel group (2b): one decoder step of Attention.forward, reference
  * src/asr.py:410-462 (query projection :422, location conv + projection :452,
  * tanh energy :453, mask + softmax(scale*e) :454-455, context bmm :457; dot
