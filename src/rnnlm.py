@@ -1,0 +1,6 @@
+"""Drop-in shim: `from src.rnnlm import ...` (the import path of the reference's src/rnnlm.py) resolves to the
+B200-native mirror in end-to-end-asr-pytorch_b200/rnnlm.py."""
+import importlib as _importlib
+
+_impl = _importlib.import_module("end-to-end-asr-pytorch_b200.rnnlm")
+globals().update({_k: _v for _k, _v in vars(_impl).items() if not _k.startswith("__")})
