@@ -240,8 +240,17 @@ class Trainer(Solver):
     def exec(self):
         ''' Training End-to-end ASR system (solver.py:118-198)'''
         self.verbose('Training set total ' + str(len(self.train_set)) + ' batches.')
+        # data parallel (new; SURVEY.md section 8e): every rank walks the SAME shuffled order (main.py seeds all ranks
+        # alike) and takes batch i when i mod world == rank; a trailing partial group is dropped so that all ranks
+        # enter the same number of gradient all-reduces
+        rank, world = _dist()
+        usable = (len(self.train_set) // world) * world
         while self.step < self.max_step:
-            for x, y in self.train_set:
+            for i, (x, y) in enumerate(self.train_set):
+                if i >= usable:
+                    break
+                if i % world != rank:
+                    continue
                 self.progress('Training step - ' + str(self.step))
                 tf_rate = self.tf_start - self.step * (self.tf_start - self.tf_end) / self.max_step
                 assert len(x.shape) == 4, 'Bucketing should cause acoustic feature to have shape 1xBxTxD'

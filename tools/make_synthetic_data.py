@@ -10,18 +10,24 @@ import sys
 import numpy as np
 
 
+TIMIT_PHONES = ("h# b bcl d dcl g gcl p pcl t tcl k kcl dx q jh ch s sh z zh f th v dh m n ng em en eng nx l r w y hh hv el "
+                "iy ih eh ey ae aa aw ay ah ao oy ow uh uw ux er ax ix axr ax-h pau epi").split()
+
+
 def mapping(vocab, unit):
+    """token -> index with <sos>=0, <eos>=1 (postprocess.py:11-22 auto-detects the unit from the symbols:
+    '#' (TIMIT's h#) -> phone, fewer than 50 symbols -> char)."""
     m = {'<sos>': 0, '<eos>': 1}
     for i in range(2, vocab):
-        m[('p%d#' % i) if unit == 'phone' else chr(ord('a') + (i - 2) % 26) * (1 + (i - 2) // 26)] = i
+        m[TIMIT_PHONES[i - 2] if unit == 'phone' else chr(ord('a') + (i - 2) % 26) * (1 + (i - 2) // 26)] = i
     return m
 
 
-def utterances(n, d, vocab, t_lo, t_hi, rng):
+def utterances(n, d, vocab, t_lo, t_hi, rng, l_div=(32, 12)):
     out = []
     for _ in range(n):
         T = int(rng.integers(t_lo, t_hi + 1))
-        L = int(rng.integers(max(2, T // 32), max(3, T // 12)))
+        L = int(rng.integers(max(2, T // l_div[0]), max(3, T // l_div[1])))
         y = [0] + [int(v) for v in rng.integers(2, vocab, L)] + [1]
         # weakly label-dependent features so that a few training steps move the loss
         x = rng.standard_normal((T, d)).astype(np.float32)
@@ -36,7 +42,7 @@ def make_timit(root, n=48, d=39, vocab=40, seed=0):
     rng = np.random.default_rng(seed)
     pickle.dump(mapping(vocab, 'phone'), open(os.path.join(root, 'mapping.pkl'), 'wb'))
     for s, k in (('train', n), ('dev', max(4, n // 6)), ('test', max(4, n // 6))):
-        u = utterances(k, d, vocab, 60, 160, rng)
+        u = utterances(k, d, vocab, 300, 500, rng, l_div=(8, 6))   # >30 labels: greedy dev decoding runs 30 extra steps
         pickle.dump([x for x, _ in u], open(os.path.join(root, s + '_x.pkl'), 'wb'))
         pickle.dump([y for _, y in u], open(os.path.join(root, s + '_y.pkl'), 'wb'))
 
