@@ -5,20 +5,22 @@
 // log2-space over the blank-interleaved label lattice, ATen gradient convention
 // (softmax - occupancy), see DESIGN.md section "CTC".
 //
-// Two launches per call:
+// Three launches per call (two when only the loss is wanted):
 //   ctc_rows_kernel     wide, HBM-bound.  One pass over the [T,B,V] logits: row log-sum-exp,
 //                       grad row = prescale*scale_b*softmax (rows past in_len zeroed) and the
 //                       per-frame table of the log2-probs the lattice will need
 //                       (whole vocabulary when V is small, gathered at the label string
 //                       otherwise) -> 1 read + 1 write of the big tensors.
-//   ctc_lattice_kernel  narrow, latency-bound.  One 2-CTA cluster per utterance: CTA 0 walks
-//                       alpha forward in time, CTA 1 walks beta backward; they meet in the
-//                       middle (one cluster barrier), after which each side finishes the
-//                       other's half, emitting occupancies as sparse corrections onto grad.
-//                       Label states are striped across the warps of a CTA, K consecutive
+//   ctc_lattice_kernel  narrow, latency-bound.  One 2-CTA cluster per utterance: CTA 0 walks alpha forward in
+//                       time over all frames, CTA 1 walks beta backward; every renormalised row goes to
+//                       the workspace.  Label states are striped across the warps of a CTA, K consecutive
 //                       states per thread; neighbours travel by warp shuffle and a one-float
-//                       shared-memory hand-off per warp boundary.  Values are renormalised
-//                       every chunk so fp32 keeps ~1e-6 relative accuracy at T=3000.
+//                       shared-memory hand-off per warp boundary.  Values are renormalised every chunk
+//                       so fp32 keeps ~1e-6 relative accuracy at T=3000.
+//   ctc_occupancy_kernel wide.  One CTA per (utterance, frame): occupancies from the stored alpha/beta rows,
+//                       subtracted from the gradient row as sparse fire-and-forget reductions.  (An
+//                       earlier version emitted them from inside the lattice walk after a meet-in-the-
+//                       middle; ncu showed the walk paying ~340 warp-instructions per step for it.)
 #include "common.cuh"
 
 namespace b2asr {
@@ -36,6 +38,8 @@ struct CtcArgs {
   float* tab; int W; int tab_gather;      // table row width (multiple of 4); 1 = gathered at labels
   float* scr; int Spad;                   // [B][2][T][Spad] stored lattice rows (global state coords)
   double* cs;                             // [B][2][T] renormalisation offsets per stored row
+  double* logp2; int* feasible;           // [B] log2 P(l|x) and whether any alignment exists
+  int* chain;                             // [B][Lmax] bits 0..29: 1 + next position with the same class (0 = none); bit 30: not the first of its class
   int RB, NST;                            // ring: rows per stage, stages
   int pair;                               // 1 = 2-CTA cluster per utterance (meet in the middle)
 };
@@ -187,27 +191,28 @@ __device__ __forceinline__ float lse3_log2(float a, float b, float c) {
 }
 
 struct LatticeSmem {
-  float* tabring; float* othring; float* obuf; int* nxt; int* labs; int* prv; float* xch; float* wred; float* bsum;
+  float* tabring; int* labs; float* xch; float* wred; float* fin;
 };
 
-__host__ __device__ inline size_t lattice_smem_bytes(int W, int Spad, int Lmax, int RB, int NST, bool want_grad) {
+__host__ __device__ inline size_t lattice_smem_bytes(int W, int Lmax, int RB, int NST) {
   size_t f = (size_t)NST * RB * W;                 // tabring
-  if (want_grad) f += (size_t)NST * RB * Spad;     // othring
-  f += 2 * (size_t)Spad;                            // obuf
-  f += (size_t)Spad;                                // nxt (int)
-  f += 2 * (size_t)((Lmax + 4) / 4 * 4);            // labs, prv (int)
-  f += 64 + 32 + 64;                                // xch, wred, bsum
+  f += (size_t)((Lmax + 4) / 4 * 4);               // labs (int)
+  f += 64 + 32 + 4;                                // xch, wred, fin
   return f * 4;
 }
 
 template <int K>
 constexpr int lattice_max_threads() { return K <= 4 ? 1024 : 512; }
 
-template <int K>
-__global__ void __launch_bounds__(lattice_max_threads<K>(), 1) ctc_lattice_kernel(CtcArgs p) {
+// One direction of the lattice walk per CTA (pair mode: cluster rank 0 = alpha forward in time, rank 1 = beta
+// backward) over ALL frames of the utterance.  Every row (renormalised log2 values in global state
+// coordinates) and its float64 offset go to the workspace; the occupancies are formed afterwards by
+// ctc_occupancy_kernel, which is wide (one CTA per frame) instead of riding on this latency-bound walk.
+template <int K, bool GRAD, bool ONEWARP>
+__global__ void __launch_bounds__(ONEWARP ? 32 : lattice_max_threads<K>(), 1) ctc_lattice_kernel(CtcArgs p) {
   extern __shared__ __align__(16) unsigned char smraw[];
   const int tid = threadIdx.x, nthr = blockDim.x, lane = tid & 31, warp = tid >> 5, nwarp = nthr >> 5;
-  const bool want_grad = p.grad != nullptr;
+  constexpr bool want_grad = GRAD;
   const int b = p.pair ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
   const int T = (int)min((long long)p.T, max(0ll, p.in_len[b]));
   const int L = (int)min((long long)p.Lmax, max(0ll, p.tgt_len[b]));
@@ -218,320 +223,182 @@ __global__ void __launch_bounds__(lattice_max_threads<K>(), 1) ctc_lattice_kerne
   {
     float* f = reinterpret_cast<float*>(smraw);
     sm.tabring = f; f += (size_t)NST * RB * W;
-    sm.othring = f; if (want_grad) f += (size_t)NST * RB * Spad;
-    sm.obuf = f; f += 2 * (size_t)Spad;
-    sm.nxt = reinterpret_cast<int*>(f); f += Spad;
     sm.labs = reinterpret_cast<int*>(f); f += (p.Lmax + 4) / 4 * 4;
-    sm.prv = reinterpret_cast<int*>(f); f += (p.Lmax + 4) / 4 * 4;
     sm.xch = f; f += 64;
     sm.wred = f; f += 32;
-    sm.bsum = f;
+    sm.fin = f;
   }
-
-  // ---- labels + same-label chains (so each (t,class) gets exactly one correction) ----------
   const long long* lab_g = p.targets + (long long)b * p.tgt_stride;
   for (int i = tid; i < L; i += nthr) sm.labs[i] = (int)min((long long)p.V - 1, max(0ll, lab_g[i]));
-  for (int i = tid; i < Spad; i += nthr) sm.nxt[i] = -1;
   __syncthreads();
-  // prv[i] = nearest earlier label position with the same class (-1: i heads its chain);
-  // nxt[2i+1] = next lattice state with the same class (-1: end of chain).
-  for (int i = tid; i < L; i += nthr) {
-    const int c = sm.labs[i];
-    int j = i - 1;
-    while (j >= 0 && sm.labs[j] != c) --j;
-    sm.prv[i] = j;
-  }
-  __syncthreads();
-  for (int i = tid; i < L; i += nthr) {
-    const int pj = sm.prv[i];
-    if (pj >= 0) sm.nxt[2 * pj + 1] = 2 * i + 1;       // one writer per slot: a label has at most one successor
-  }
-  __syncthreads();
-  unsigned headmask = 0;                                // bit kk: my state kk is the head of its class chain
 
-  const float gs = row_scale(p, L);
-  const int mid = T / 2;
+  // same-class chains of the label string, for the occupancy pass (encoding at CtcArgs::chain): the first position
+  // of a class sums the occupancies of the whole chain, so each (frame, class) receives exactly ONE reduction
+  // and the gradient is bit-reproducible.
+  if (want_grad && (!p.pair || cluster_ctarank() == 0)) {
+    int* ch = p.chain + (long long)b * p.Lmax;
+    for (int i = tid; i < L; i += nthr) {
+      const int c = sm.labs[i];
+      int nx = -1, first = 1;
+      for (int j = i + 1; j < L; ++j) if (sm.labs[j] == c) { nx = j; break; }
+      for (int j = i - 1; j >= 0; --j) if (sm.labs[j] == c) { first = 0; break; }
+      ch[i] = (nx + 1) | (first ? 0 : 0x40000000);
+    }
+  }
+
   const int npass = (p.pair || !want_grad) ? 1 : 2;
-  double logP = 0.0;
-  bool feasible = true;
-
   for (int pass = 0; pass < npass; ++pass) {
     const int dir = p.pair ? (int)cluster_ctarank() : pass;
-    int n1;                                            // steps [0,n1) are stored, [n1,T) are emitted
-    if (!want_grad) n1 = T;
-    else if (p.pair) n1 = dir == 0 ? mid : T - mid;
-    else n1 = pass == 0 ? T : 0;
 
     // ---- per-thread static description of my K local states ---------------------------------
-    int sglob[K], tix[K], cls[K];
+    // local state jl = tid*K + kk is global state s = jl (forward) or S-1-jl (backward); rows are stored in
+    // LOCAL coordinates so that a thread's K values leave as aligned vector stores.
+    int tix[K];
     bool valid[K], skip[K];
-    headmask = 0;
 #pragma unroll
     for (int kk = 0; kk < K; ++kk) {
       const int jl = tid * K + kk;
       valid[kk] = jl < S;
       const int s = dir ? (S - 1 - jl) : jl;
-      sglob[kk] = s;
       const bool is_lab = valid[kk] && (s & 1);
       const int li = (s - 1) >> 1;
-      cls[kk] = is_lab ? sm.labs[li] : p.blank;
-      tix[kk] = p.tab_gather ? (is_lab ? li + 1 : 0) : cls[kk];
+      const int cls = is_lab ? sm.labs[li] : p.blank;
+      tix[kk] = valid[kk] ? (p.tab_gather ? (is_lab ? li + 1 : 0) : cls) : (W - 1);   // padding states read a finite slot
       skip[kk] = false;
       if (is_lab && jl >= 2) {
         const int li2 = dir ? li + 1 : li - 1;
-        skip[kk] = sm.labs[li2] != cls[kk];
+        skip[kk] = sm.labs[li2] != cls;
       }
-      if (is_lab && sm.prv[li] < 0) headmask |= 1u << kk;
     }
 
     float a[K];
 #pragma unroll
     for (int kk = 0; kk < K; ++kk) a[kk] = kNeg;
     double C = 0.0;
-    int pend_k = -1;                                    // emission waiting for its barrier
     float xshift = 0.f;                                 // renormalisation applied after xch was written
     float drift = 0.f;                                  // running estimate of the best path's per-frame slope
+    float* srow = p.scr + ((long long)b * 2 + dir) * p.T * Spad + (long long)tid * K;
+    double* crow = p.cs + ((long long)b * 2 + dir) * p.T;
 
-    for (int phase = 0; phase < 2; ++phase) {
-      const int ks = phase == 0 ? 0 : n1;
-      const int ke = phase == 0 ? n1 : T;
-      if (phase == 1) {
-        if (!want_grad) break;
-        __threadfence();
-        if (p.pair) cluster_sync_all(); else __syncthreads();
-      }
-      const int nsteps = ke - ks;
-      if (nsteps <= 0) continue;
-      const int nchunks = (nsteps + RB - 1) / RB;
-      const int wq = W >> 2, sq = Spad >> 2;
-
-      auto issue = [&](int c) {
-        if (c < nchunks) {
-          const int st = c % NST;
-          const int k0 = ks + c * RB;
-          const int rows = min(RB, ke - k0);
-          float* tdst = sm.tabring + (size_t)st * RB * W;
-          for (int i = tid; i < rows * wq; i += nthr) {
-            const int r = i / wq, q = i - r * wq;
-            const int k = k0 + r;
-            const int t = dir ? (T - 1 - k) : k;
-            cp_async16(tdst + (size_t)r * W + 4 * q, p.tab + ((long long)b * p.T + t) * W + 4 * q);
-          }
-          if (phase == 1) {
-            float* odst = sm.othring + (size_t)st * RB * Spad;
-            for (int i = tid; i < rows * sq; i += nthr) {
-              const int r = i / sq, q = i - r * sq;
-              const int k = k0 + r;
-              const int ko = T - 1 - k;
-              cp_async16(odst + (size_t)r * Spad + 4 * q,
-                         p.scr + (((long long)b * 2 + (1 - dir)) * p.T + ko) * Spad + 4 * q);
-            }
-          }
-        }
-        cp_async_commit();
-      };
-
-      for (int c = 0; c < NST - 1; ++c) issue(c);
-
-      for (int c = 0; c < nchunks; ++c) {
-        // wait for stage c (all but the NST-2 most recent groups), make it CTA-visible
-        if (NST == 2) cp_async_wait<0>(); else if (NST == 3) cp_async_wait<1>(); else cp_async_wait<2>();
-        __syncthreads();
-        issue(c + NST - 1);
-
+    const int nchunks = (T + RB - 1) / RB;
+    const int wq = W >> 2;
+    auto issue = [&](int c) {
+      if (c < nchunks) {
         const int st = c % NST;
-        const int k0 = ks + c * RB;
-        const int rows = min(RB, ke - k0);
-        for (int r = 0; r < rows; ++r) {
+        const int k0 = c * RB;
+        const int rows = min(RB, T - k0);
+        float* tdst = sm.tabring + (size_t)st * RB * W;
+        for (int i = tid; i < rows * wq; i += nthr) {
+          const int r = i / wq, q = i - r * wq;
           const int k = k0 + r;
           const int t = dir ? (T - 1 - k) : k;
-          const float* trow = sm.tabring + ((size_t)st * RB + r) * W;
+          cp_async16(tdst + (size_t)r * W + 4 * q, p.tab + ((long long)b * p.T + t) * W + 4 * q);
+        }
+      }
+      cp_async_commit();
+    };
+    for (int c = 0; c < NST - 1; ++c) issue(c);
 
-          // ---- finish the previous step's emission (its obuf/bsum are visible now) ----------
-          if (pend_k >= 0) {
-            const int tp = dir ? (T - 1 - pend_k) : pend_k;
-            const float* ob = sm.obuf + (size_t)(pend_k & 1) * Spad;
-            float* grow = p.grad + (long long)tp * p.sg_t + (long long)b * p.sg_b;
+    // CTA-wide barrier, or nothing when one warp holds the whole lattice (its lanes are in lock step through
+    // the shuffles, and __syncwarp orders the shared-memory ring reads)
+    auto sync_all = [&]() { if (ONEWARP) __syncwarp(); else __syncthreads(); };
+
+    int k = 0;
+    for (int c = 0; c < nchunks; ++c) {
+      if (NST == 2) cp_async_wait<0>(); else if (NST == 3) cp_async_wait<1>(); else cp_async_wait<2>();
+      sync_all();
+      issue(c + NST - 1);
+      const int rows = min(RB, T - c * RB);
+      const float* trow = sm.tabring + (size_t)(c % NST) * RB * W;
+      float part = 0.f;                                    // offsets added inside this chunk (fp32: <= RB terms)
+      for (int r = 0; r < rows; ++r, ++k, trow += W) {
+        float lp[K];
 #pragma unroll
-            for (int kk = 1; kk < K; kk += 2) {
-              if (headmask & (1u << kk)) {
-                float sum = ob[sglob[kk]];
-                int nx = sm.nxt[sglob[kk]];
-                while (nx >= 0) { sum += ob[nx]; nx = sm.nxt[nx]; }
-                atomicAdd(grow + cls[kk], -gs * sum);
-              }
-            }
-            if (tid == 0) {
-              float bs = 0.f;
-              for (int w = 0; w < nwarp; ++w) bs += sm.bsum[(pend_k & 1) * 32 + w];
-              atomicAdd(grow + p.blank, -gs * bs);
-            }
-            pend_k = -1;
+        for (int kk = 0; kk < K; ++kk) lp[kk] = trow[tix[kk]];
+        // per-frame offset (table max + learned slope): keeps the best path near 0, where fp32 is dense
+        const float rmax = trow[W - 1] + drift;
+        part += rmax;
+        if (k == 0) {
+#pragma unroll
+          for (int kk = 0; kk < K; ++kk) {
+            const int jl = tid * K + kk;
+            a[kk] = (jl < 2 && valid[kk]) ? fmaxf(lp[kk] - rmax, kNeg) : kNeg;
           }
-
-          // ---- lattice step ---------------------------------------------------------------
-          float lp[K];
+        } else {
+          float l1 = __shfl_up_sync(kFull, a[K - 1], 1);
+          if (ONEWARP) { if (lane == 0) l1 = kNeg; }
+          else if (lane == 0) l1 = warp > 0 ? fmaxf(sm.xch[((k - 1) & 1) * 32 + warp - 1] - xshift, kNeg) : kNeg;
+          xshift = 0.f;
 #pragma unroll
-          for (int kk = 0; kk < K; ++kk) lp[kk] = valid[kk] ? trow[tix[kk]] : 0.f;
-          // per-frame offset (table max + learned slope): keeps the best path near 0, where fp32 is dense
-          const float rmax = trow[W - 1] + drift;
-          C += (double)rmax;
-          if (k == 0) {
-#pragma unroll
-            for (int kk = 0; kk < K; ++kk) {
-              const int jl = tid * K + kk;
-              a[kk] = (jl < 2 && valid[kk]) ? fmaxf(lp[kk] - rmax, kNeg) : kNeg;
-            }
-          } else {
-            float l1 = __shfl_up_sync(kFull, a[K - 1], 1);
-            if (lane == 0) l1 = warp > 0 ? fmaxf(sm.xch[((k - 1) & 1) * 32 + warp - 1] - xshift, kNeg) : kNeg;
-            xshift = 0.f;
-#pragma unroll
-            for (int kk = K - 1; kk >= 0; --kk) {
-              const float p0 = a[kk];
-              const float p1 = kk > 0 ? a[kk - 1] : l1;
-              float v;
-              if (kk & 1) {
-                const float p2 = kk > 1 ? a[kk - 2] : l1;   // kk==1: two back is the left neighbour
-                v = lse3_log2(p0, p1, skip[kk] ? p2 : kNeg);
-              } else {
-                v = lse2_log2(p0, p1);
-              }
-              a[kk] = fmaxf(v + (lp[kk] - rmax), kNeg);
-            }
-          }
-          if (lane == 31) sm.xch[(k & 1) * 32 + warp] = a[K - 1];
-
-          if (phase == 0) {
-            if (want_grad) {
-              float* srow = p.scr + (((long long)b * 2 + dir) * p.T + k) * Spad;
-#pragma unroll
-              for (int kk = 0; kk < K; ++kk) if (valid[kk]) srow[sglob[kk]] = a[kk];
-              if (tid == 0) p.cs[((long long)b * 2 + dir) * p.T + k] = C;
-            }
-          } else {
-            const float* orow = sm.othring + ((size_t)st * RB + r) * Spad;
-            const double Co = p.cs[((long long)b * 2 + (1 - dir)) * p.T + (T - 1 - k)];
-            float e[K];
-#pragma unroll
-            for (int kk = 0; kk < K; ++kk) e[kk] = valid[kk] ? (a[kk] + orow[sglob[kk]] - lp[kk]) : kNeg;
-            if (k == n1) {
-              // meeting point: log2 P = C + Co + log2 sum_s 2^(e_s)   (block reduction, once)
-              float mx = kNeg;
-#pragma unroll
-              for (int kk = 0; kk < K; ++kk) mx = fmaxf(mx, e[kk]);
-              mx = warp_max(mx);
-              if (lane == 0) sm.wred[warp] = mx;
-              __syncthreads();
-              mx = sm.wred[0];
-              for (int w = 1; w < nwarp; ++w) mx = fmaxf(mx, sm.wred[w]);
-              __syncthreads();
-              float sx = 0.f;
-#pragma unroll
-              for (int kk = 0; kk < K; ++kk) sx += valid[kk] ? ex2(e[kk] - mx) : 0.f;
-              sx = warp_sum(sx);
-              if (lane == 0) sm.wred[warp] = sx;
-              __syncthreads();
-              sx = 0.f;
-              for (int w = 0; w < nwarp; ++w) sx += sm.wred[w];
-              __syncthreads();
-              feasible = mx > -1.0e29f;
-              logP = C + Co + (double)mx + (double)log2f(sx);
-              if (tid == 0 && (dir == 0 || !p.pair)) {
-                p.nll[b] = feasible ? (float)(-logP * (double)kLn2) : INFINITY;
-              }
-            }
-            if (feasible) {
-              const float cst = (float)(C + Co - logP);
-              float* ob = sm.obuf + (size_t)(k & 1) * Spad;
-              float bsum = 0.f;
-#pragma unroll
-              for (int kk = 0; kk < K; ++kk) {
-                const float o = valid[kk] ? ex2(fminf(e[kk] + cst, 0.f)) : 0.f;
-                if (kk & 1) { if (valid[kk]) ob[sglob[kk]] = o; }
-                else bsum += o;
-              }
-              bsum = warp_sum(bsum);
-              if (lane == 0) sm.bsum[(k & 1) * 32 + warp] = bsum;
-              pend_k = k;
+          for (int kk = K - 1; kk >= 0; --kk) {
+            const float p0 = a[kk];
+            const float p1 = kk > 0 ? a[kk - 1] : l1;
+            float v;
+            if (kk & 1) {
+              const float p2 = kk > 1 ? a[kk - 2] : l1;   // kk==1: two back is the left neighbour
+              v = lse3_log2(p0, p1, skip[kk] ? p2 : kNeg);
             } else {
-              float* grow = p.grad + (long long)t * p.sg_t + (long long)b * p.sg_b;
-              for (int v = tid; v < p.V; v += nthr) grow[v] = __int_as_float(0x7fc00000);
+              v = lse2_log2(p0, p1);
             }
-          }
-
-          // renormalise at the end of every chunk: block max -> subtract, remember in C
-          const bool last_in_chunk = (r == rows - 1);
-          if (last_in_chunk) {
-            float mx = kNeg;
-#pragma unroll
-            for (int kk = 0; kk < K; ++kk) mx = fmaxf(mx, valid[kk] ? a[kk] : kNeg);
-            mx = warp_max(mx);
-            if (lane == 0) sm.wred[warp] = mx;
-          }
-          __syncthreads();
-          if (last_in_chunk) {
-            float mx = sm.wred[0];
-            for (int w = 1; w < nwarp; ++w) mx = fmaxf(mx, sm.wred[w]);
-            if (mx > -1.0e29f) {
-#pragma unroll
-              for (int kk = 0; kk < K; ++kk) a[kk] = fmaxf(a[kk] - mx, kNeg);
-              C += (double)mx;
-              xshift = mx;                              // the hand-off slot still holds the unshifted value
-              drift += mx / (float)rows;                // what the offsets failed to absorb over this chunk
-            }
+            a[kk] = fmaxf(v + (lp[kk] - rmax), kNeg);
           }
         }
-      }
-      cp_async_wait<0>();
-    }  // phase
-
-    // ---- flush the last pending emission of this pass ------------------------------------------
-    if (pend_k >= 0) {
-      const int tp = dir ? (T - 1 - pend_k) : pend_k;
-      const float* ob = sm.obuf + (size_t)(pend_k & 1) * Spad;
-      float* grow = p.grad + (long long)tp * p.sg_t + (long long)b * p.sg_b;
+        if (!ONEWARP && lane == 31) sm.xch[(k & 1) * 32 + warp] = a[K - 1];
+        if (want_grad) {
 #pragma unroll
-      for (int kk = 1; kk < K; kk += 2) {
-        if (headmask & (1u << kk)) {
-          float sum = ob[sglob[kk]];
-          int nx = sm.nxt[sglob[kk]];
-          while (nx >= 0) { sum += ob[nx]; nx = sm.nxt[nx]; }
-          atomicAdd(grow + cls[kk], -gs * sum);
+          for (int kk = 0; kk < K; kk += 2) *reinterpret_cast<float2*>(srow + kk) = make_float2(a[kk], a[kk + 1]);
+          if (tid == 0) crow[k] = C + (double)part;
+          srow += Spad;
         }
+        if (!ONEWARP && r + 1 < rows) __syncthreads();     // hand-off slot of this step visible to the next
       }
-      if (tid == 0) {
-        float bs = 0.f;
-        for (int w = 0; w < nwarp; ++w) bs += sm.bsum[(pend_k & 1) * 32 + w];
-        atomicAdd(grow + p.blank, -gs * bs);
+      C += (double)part;
+      // renormalise at the end of every chunk: block max -> subtract, remember in C
+      float mx = kNeg;
+#pragma unroll
+      for (int kk = 0; kk < K; ++kk) mx = fmaxf(mx, valid[kk] ? a[kk] : kNeg);
+      mx = warp_max(mx);
+      if (!ONEWARP) {
+        if (lane == 0) sm.wred[warp] = mx;
+        __syncthreads();
+        mx = sm.wred[0];
+        for (int w = 1; w < nwarp; ++w) mx = fmaxf(mx, sm.wred[w]);
       }
-      pend_k = -1;
+      if (mx > -1.0e29f) {
+#pragma unroll
+        for (int kk = 0; kk < K; ++kk) a[kk] = fmaxf(a[kk] - mx, kNeg);
+        C += (double)mx;
+        xshift = mx;                                      // the hand-off slot still holds the unshifted value
+        drift += mx / (float)rows;                        // what the offsets failed to absorb over this chunk
+      }
     }
+    cp_async_wait<0>();
 
-    // ---- loss-only: read log P off the last forward row ------------------------------------------
-    if (!want_grad) {
+    // ---- forward direction: log P = C + log2(2^a[S-1] + 2^a[S-2]) off the last row ---------------
+    if (dir == 0) {
       __syncthreads();
 #pragma unroll
       for (int kk = 0; kk < K; ++kk) {
         const int jl = tid * K + kk;
-        if (valid[kk] && jl >= S - 2) sm.obuf[jl - (S - 2) + 1] = a[kk];   // slots 1 (S-2) and 2 (S-1)
+        if (valid[kk] && jl >= S - 2) sm.fin[jl - (S - 2) + 1] = a[kk];   // slots 1 (S-2) and 2 (S-1)
       }
-      if (tid == 0 && S == 1) sm.obuf[1] = kNeg;
+      if (tid == 0 && S == 1) sm.fin[1] = kNeg;
       __syncthreads();
       if (tid == 0) {
-        float r;
+        float r; double lp2 = 0.0; int ok = 0;
         if (T == 0) r = (L == 0) ? 0.f : INFINITY;
         else {
-          const float v = lse2_log2(sm.obuf[1], sm.obuf[2]);
-          r = (v > -1.0e29f) ? (float)(-(C + (double)v) * (double)kLn2) : INFINITY;
+          const float v = lse2_log2(sm.fin[1], sm.fin[2]);
+          ok = v > -1.0e29f;
+          lp2 = C + (double)v;
+          r = ok ? (float)(-lp2 * (double)kLn2) : INFINITY;
         }
         p.nll[b] = r;
+        if (want_grad) { p.logp2[b] = lp2; p.feasible[b] = ok; }
       }
     }
     __syncthreads();
   }  // pass
-
-  if (want_grad && T == 0 && tid == 0 && (!p.pair || cluster_ctarank() == 0)) p.nll[b] = (L == 0) ? 0.f : INFINITY;
 
   // ---- batch reduction by the last CTA to finish (deterministic order) ----------------------
   if (p.loss != nullptr && (!p.pair || cluster_ctarank() == 0)) {
@@ -554,6 +421,62 @@ __global__ void __launch_bounds__(lattice_max_threads<K>(), 1) ctc_lattice_kerne
 }
 
 // --------------------------------------------------------------------------------------
+// Occupancy pass: wide.  One CTA per (utterance, frame): occupancy of every lattice state from the stored
+// alpha / beta rows, o_s = 2^(alpha_t(s) + beta_t(s) - lp_t(s) + C_a + C_b - log2 P), then
+// grad[t,b,class(s)] -= scale_b * o_s.  Blank states are reduced in the CTA (one reduction per row), label
+// states go out as fire-and-forget reductions (a class repeated in the label string just adds twice).
+// --------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) ctc_occupancy_kernel(CtcArgs p) {
+  extern __shared__ __align__(16) float osm[];             // [L] occupancy of the label states
+  __shared__ float wsum[8];
+  const int b = blockIdx.y, t = blockIdx.x;
+  const int T = (int)min((long long)p.T, max(0ll, p.in_len[b]));
+  if (t >= T) return;
+  const int L = (int)min((long long)p.Lmax, max(0ll, p.tgt_len[b]));
+  const int S = 2 * L + 1;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  float* grow = p.grad + (long long)t * p.sg_t + (long long)b * p.sg_b;
+  if (!p.feasible[b]) {                                  // no alignment: NaN on the valid rows, as ATen does
+    for (int v = tid; v < p.V; v += blockDim.x) grow[v] = __int_as_float(0x7fc00000);
+    return;
+  }
+  const float gs = row_scale(p, L);
+  const float* arow = p.scr + (((long long)b * 2 + 0) * p.T + t) * p.Spad;
+  const float* brow = p.scr + (((long long)b * 2 + 1) * p.T + (T - 1 - t)) * p.Spad;
+  const float* trow = p.tab + ((long long)b * p.T + t) * p.W;
+  const long long* lab = p.targets + (long long)b * p.tgt_stride;
+  const int* chain = p.chain + (long long)b * p.Lmax;
+  const float cst = (float)(p.cs[((long long)b * 2 + 0) * p.T + t] + p.cs[((long long)b * 2 + 1) * p.T + (T - 1 - t)] - p.logp2[b]);
+  float bsum = 0.f;
+  for (int s = tid; s < S; s += blockDim.x) {
+    const bool is_lab = s & 1;
+    const int li = (s - 1) >> 1;
+    int cls = p.blank;
+    if (is_lab) cls = (int)min((long long)p.V - 1, max(0ll, lab[li]));
+    const float lp = trow[p.tab_gather ? (is_lab ? li + 1 : 0) : cls];
+    const float e = arow[s] + brow[S - 1 - s] - lp;           // rows are stored in each walk's local coordinates
+    const float o = ex2(fminf(e + cst, 0.f));
+    if (is_lab) osm[li] = o;
+    else bsum += o;
+  }
+  bsum = warp_sum(bsum);
+  if (lane == 0) wsum[warp] = bsum;
+  __syncthreads();
+  for (int i = tid; i < L; i += blockDim.x) {            // the first position of every class sums its chain
+    const int v = chain[i];
+    if (v & 0x40000000) continue;
+    float sum = osm[i];
+    for (int nx = (v & 0x3fffffff) - 1; nx >= 0; nx = (chain[nx] & 0x3fffffff) - 1) sum += osm[nx];
+    red_add_f32(grow + (int)min((long long)p.V - 1, max(0ll, lab[i])), -gs * sum);
+  }
+  if (tid == 0) {
+    float tot = 0.f;
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) tot += wsum[w];
+    red_add_f32(grow + p.blank, -gs * tot);
+  }
+}
+
+// --------------------------------------------------------------------------------------
 // Rescale helper for autograd backward.
 // --------------------------------------------------------------------------------------
 __global__ void rescale_if_needed_kernel(float* buf, long long n, const float* upstream, float assumed) {
@@ -570,7 +493,7 @@ __global__ void rescale_if_needed_kernel(float* buf, long long n, const float* u
 struct CtcPlan {
   int W, tab_gather, Spad, K, nthr, RB, NST, pair;
   size_t smem;
-  size_t off_ticket, off_tab, off_scr, off_cs, total;
+  size_t off_ticket, off_tab, off_scr, off_cs, off_lp, off_feas, off_chain, total;
 };
 
 static int env_int(const char* name, int dflt) {
@@ -597,25 +520,39 @@ static int make_plan(int T, int B, int V, int Lmax, bool want_grad, CtcPlan& pl)
   if (bestK < 0) { set_error("ctc: label length %d too long (max %d)", Lmax, (12 * 1024 - 1) / 2); return B2ASR_EUNSUPPORTED; }
   pl.K = bestK;
   pl.nthr = (int)align_up((size_t)((S + bestK - 1) / bestK), 32);
+  pl.Spad = pl.nthr * pl.K;                                        // one aligned vector store per thread and row
   pl.pair = want_grad ? env_int("B2ASR_CTC_PAIR", 1) : 0;
   pl.NST = 3;
   pl.RB = 8;
   const size_t cap = 200 * 1024;
-  while (pl.RB > 1 && lattice_smem_bytes(pl.W, pl.Spad, Lmax, pl.RB, pl.NST, want_grad) > cap) pl.RB >>= 1;
-  pl.smem = lattice_smem_bytes(pl.W, pl.Spad, Lmax, pl.RB, pl.NST, want_grad);
+  while (pl.RB > 1 && lattice_smem_bytes(pl.W, Lmax, pl.RB, pl.NST) > cap) pl.RB >>= 1;
+  pl.smem = lattice_smem_bytes(pl.W, Lmax, pl.RB, pl.NST);
   if (pl.smem > 227 * 1024) { set_error("ctc: lattice needs %zu bytes of shared memory", pl.smem); return B2ASR_EUNSUPPORTED; }
   size_t off = 0;
   pl.off_ticket = off; off += 256;
   pl.off_tab = off; off += align_up((size_t)B * T * pl.W * sizeof(float), 256);
   pl.off_scr = off; if (want_grad) off += align_up((size_t)B * 2 * T * pl.Spad * sizeof(float), 256);
   pl.off_cs = off; if (want_grad) off += align_up((size_t)B * 2 * T * sizeof(double), 256);
+  pl.off_lp = off; off += align_up((size_t)B * sizeof(double), 256);
+  pl.off_feas = off; off += align_up((size_t)B * sizeof(int), 256);
+  pl.off_chain = off; off += align_up((size_t)B * (Lmax + 1) * sizeof(int), 256);
   pl.total = off;
   return B2ASR_OK;
 }
 
+template <int K, bool GRAD, bool ONEWARP>
+static int launch_lattice_t(const CtcArgs& a, const CtcPlan& pl, cudaStream_t st);
+
 template <int K>
 static int launch_lattice(const CtcArgs& a, const CtcPlan& pl, cudaStream_t st) {
-  B2_CUDA_TRY(cudaFuncSetAttribute(ctc_lattice_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem));
+  const bool grad = a.grad != nullptr, one = pl.nthr == 32;
+  if (grad) return one ? launch_lattice_t<K, true, true>(a, pl, st) : launch_lattice_t<K, true, false>(a, pl, st);
+  return one ? launch_lattice_t<K, false, true>(a, pl, st) : launch_lattice_t<K, false, false>(a, pl, st);
+}
+
+template <int K, bool GRAD, bool ONEWARP>
+static int launch_lattice_t(const CtcArgs& a, const CtcPlan& pl, cudaStream_t st) {
+  B2_CUDA_TRY(cudaFuncSetAttribute(ctc_lattice_kernel<K, GRAD, ONEWARP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(a.pair ? 2 * a.B : a.B);
   cfg.blockDim = dim3(pl.nthr);
@@ -628,7 +565,7 @@ static int launch_lattice(const CtcArgs& a, const CtcPlan& pl, cudaStream_t st) 
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  B2_CUDA_TRY(cudaLaunchKernelEx(&cfg, ctc_lattice_kernel<K>, a));
+  B2_CUDA_TRY(cudaLaunchKernelEx(&cfg, ctc_lattice_kernel<K, GRAD, ONEWARP>, a));
   return B2ASR_OK;
 }
 
@@ -675,6 +612,7 @@ extern "C" int b2asr_ctc_loss_fwd_bwd(const float* x, int64_t sx_t, int64_t sx_b
   a.tab = (float*)(w + pl.off_tab); a.W = pl.W; a.tab_gather = pl.tab_gather;
   a.scr = (float*)(w + pl.off_scr); a.Spad = pl.Spad;
   a.cs = (double*)(w + pl.off_cs);
+  a.logp2 = (double*)(w + pl.off_lp); a.feasible = (int*)(w + pl.off_feas); a.chain = (int*)(w + pl.off_chain);
   a.RB = pl.RB; a.NST = pl.NST; a.pair = pl.pair;
 
   // ---- wide pass --------------------------------------------------------------------------
@@ -704,7 +642,14 @@ extern "C" int b2asr_ctc_loss_fwd_bwd(const float* x, int64_t sx_t, int64_t sx_b
     case 12: rc = launch_lattice<12>(a, pl, st); break;
     default: set_error("ctc: internal: K=%d", pl.K); return B2ASR_EUNSUPPORTED;
   }
-  return rc;
+  if (rc != B2ASR_OK) return rc;
+
+  // ---- occupancy pass (gradient only) ---------------------------------------------------------
+  if (want_grad) {
+    ctc_occupancy_kernel<<<dim3((unsigned)T, (unsigned)B), 256, (size_t)(Lmax + 4) * sizeof(float), st>>>(a);
+    B2_CUDA_TRY(cudaGetLastError());
+  }
+  return B2ASR_OK;
 }
 
 extern "C" int b2asr_rescale_if_needed(float* buf, int64_t n, const float* upstream, float assumed, void* stream) {

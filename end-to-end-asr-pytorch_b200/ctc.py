@@ -55,7 +55,7 @@ class _CTCFunction(torch.autograd.Function):
             sg_b, sg_t = (grad.stride(0), grad.stride(1)) if batch_first else (grad.stride(1), grad.stride(0))
         else:
             sg_b = sg_t = 0
-        _lib.call("b2asr_ctc_loss_fwd_bwd", 2, L.b2asr_ctc_loss_fwd_bwd,
+        _lib.call("b2asr_ctc_loss_fwd_bwd", 3 if want_grad else 2, L.b2asr_ctc_loss_fwd_bwd,
             x.data_ptr(), sx_t, sx_b, targets.data_ptr(), targets.stride(0),
             in_len.data_ptr(), tgt_len.data_ptr(), T, B, V, Lmax, int(blank),
             int(bool(from_logits)), red, float(prescale),
