@@ -37,10 +37,11 @@ struct CtcArgs {
   unsigned* ticket;
   float* tab; int W; int tab_gather;      // table row width (multiple of 4); 1 = gathered at labels
   float* scr; int Spad;                   // [B][2][T][Spad] stored lattice rows (global state coords)
-  double* cs;                             // [B][2][T] renormalisation offsets per stored row
+  float* poff;                            // [B][2][T] offset folded away inside the row's chunk, up to and including the row
+  double* cbase; int nchunk_max;          // [B][2][nchunk_max] offset folded away before each chunk
   double* logp2; int* feasible;           // [B] log2 P(l|x) and whether any alignment exists
   int* chain;                             // [B][Lmax] bits 0..29: 1 + next position with the same class (0 = none); bit 30: not the first of its class
-  int RB, NST;                            // ring: rows per stage, stages
+  int RBlog, NST;                         // ring: log2(rows per stage), stages
   int pair;                               // 1 = 2-CTA cluster per utterance (meet in the middle)
 };
 
@@ -141,18 +142,18 @@ __global__ void __launch_bounds__(256) ctc_rows_kernel(CtcArgs p, int Vpad) {
     }
   }
 
-  // ---- table of log2-probs for the lattice; last slot = a per-frame offset (max entry) ------
+  // ---- table of log2-probs for the lattice, relative to the row's largest entry tm ---------
+  // gathered layout: [0,L) = labels in string order; dense layout: [0,V) = classes.  Both: slot W-2 = blank,
+  // slot W-1 = tm (so the lattice fetches {blank, tm} with one 64-bit broadcast load).
   float* trow = p.tab + ((long long)b * p.T + t) * p.W;
   float tm;
   if (p.tab_gather) {
     const long long* lab = p.targets + (long long)b * p.tgt_stride;
     tm = kNeg;
     for (int i = l; i <= L; i += TPR) {
-      long long c = (i == 0) ? (long long)p.blank : lab[i - 1];
+      long long c = (i == L) ? (long long)p.blank : lab[i];
       c = min((long long)V - 1, max(0ll, c));
-      const float val = fmaxf((cache[c] - lse) * kLog2e, kNeg);
-      trow[i] = val;
-      tm = fmaxf(tm, val);
+      tm = fmaxf(tm, fmaxf((cache[c] - lse) * kLog2e, kNeg));
     }
     tm = warp_max(tm);
     if (TPR == 256) {
@@ -163,11 +164,19 @@ __global__ void __launch_bounds__(256) ctc_rows_kernel(CtcArgs p, int Vpad) {
 #pragma unroll
       for (int w = 1; w < 8; ++w) tm = fmaxf(tm, red[0][w]);
     }
+    if (!(tm > -1.0e29f)) tm = 0.f;
+    for (int i = l; i <= L; i += TPR) {
+      long long c = (i == L) ? (long long)p.blank : lab[i];
+      c = min((long long)V - 1, max(0ll, c));
+      trow[i == L ? p.W - 2 : i] = fmaxf(fmaxf((cache[c] - lse) * kLog2e, kNeg) - tm, kNeg);
+    }
   } else {
-    for (int i = l; i < V; i += TPR) trow[i] = fmaxf((cache[i] - lse) * kLog2e, kNeg);
     tm = fmaxf((m - lse) * kLog2e, kNeg);
+    if (!(tm > -1.0e29f)) tm = 0.f;
+    for (int i = l; i < V; i += TPR) trow[i] = fmaxf(fmaxf((cache[i] - lse) * kLog2e, kNeg) - tm, kNeg);
+    if (l == 0) trow[p.W - 2] = fmaxf(fmaxf((cache[p.blank] - lse) * kLog2e, kNeg) - tm, kNeg);
   }
-  if (l == 0) trow[p.W - 1] = (tm > -1.0e29f) ? tm : 0.f;
+  if (l == 0) trow[p.W - 1] = tm;
 }
 
 // --------------------------------------------------------------------------------------
@@ -190,224 +199,207 @@ __device__ __forceinline__ float lse3_log2(float a, float b, float c) {
   return m + LAT_LG2(1.f + LAT_EX2(lo - m) + LAT_EX2(o - m));
 }
 
-struct LatticeSmem {
-  float* tabring; int* labs; float* xch; float* wred; float* fin;
-};
-
 __host__ __device__ inline size_t lattice_smem_bytes(int W, int Lmax, int RB, int NST) {
-  size_t f = (size_t)NST * RB * W;                 // tabring
-  f += (size_t)((Lmax + 4) / 4 * 4);               // labs (int)
-  f += 64 + 32 + 4;                                // xch, wred, fin
-  return f * 4;
+  size_t f = (size_t)NST * RB * W;                 // table ring
+  f += (size_t)((Lmax + 4) / 4 * 4);               // label string (int)
+  f += 64 + 64 + 4;                                // hand-off slots [2][32], warp maxima [2][32], final pair
+  return f * 4 + 8 * 8;                            // + ring mbarriers
 }
 
 template <int K>
 constexpr int lattice_max_threads() { return K <= 4 ? 1024 : 512; }
 
+__device__ __forceinline__ void bar_sync_n(int nthreads) {
+  asm volatile("bar.sync 0, %0;" ::"r"(nthreads) : "memory");
+}
+// order-preserving float -> int key, so a warp maximum is one redux.sync
+__device__ __forceinline__ int f2ord(float f) {
+  const int i = __float_as_int(f);
+  return i ^ ((i >> 31) & 0x7fffffff);
+}
+__device__ __forceinline__ float ord2f(int k) { return __int_as_float(k ^ ((k >> 31) & 0x7fffffff)); }
+
 // One direction of the lattice walk per CTA (pair mode: cluster rank 0 = alpha forward in time, rank 1 = beta
-// backward) over ALL frames of the utterance.  Every row (renormalised log2 values in global state
-// coordinates) and its float64 offset go to the workspace; the occupancies are formed afterwards by
-// ctc_occupancy_kernel, which is wide (one CTA per frame) instead of riding on this latency-bound walk.
-template <int K, bool GRAD, bool ONEWARP>
-__global__ void __launch_bounds__(ONEWARP ? 32 : lattice_max_threads<K>(), 1) ctc_lattice_kernel(CtcArgs p) {
+// backward) over ALL frames of the utterance.  A thread owns K/2 consecutive (blank, label) state pairs in the
+// walk's LOCAL coordinates (local state j = global state j forward, S-1-j backward: the reversed lattice has the
+// same shape).  Per step and thread: one 64-bit broadcast load {blank, row max}, K/2 label loads, one shuffle,
+// K log-sum-exps, one vector store of the row, one CTA barrier.  Renormalisation never touches the registers:
+// the CTA maximum measured at the end of a chunk is folded into the frame offset of the next chunk's first step.
+template <int K, bool GRAD>
+__global__ void __launch_bounds__(lattice_max_threads<K>(), 1) ctc_lattice_kernel(CtcArgs p) {
   extern __shared__ __align__(16) unsigned char smraw[];
-  const int tid = threadIdx.x, nthr = blockDim.x, lane = tid & 31, warp = tid >> 5, nwarp = nthr >> 5;
-  constexpr bool want_grad = GRAD;
+  constexpr int H = K / 2;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int b = p.pair ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int dir = p.pair ? (int)cluster_ctarank() : 0;
   const int T = (int)min((long long)p.T, max(0ll, p.in_len[b]));
   const int L = (int)min((long long)p.Lmax, max(0ll, p.tgt_len[b]));
   const int S = 2 * L + 1;
-  const int W = p.W, Spad = p.Spad, RB = p.RB, NST = p.NST;
+  const int W = p.W, RB = 1 << p.RBlog, NST = p.NST;
 
-  LatticeSmem sm;
-  {
-    float* f = reinterpret_cast<float*>(smraw);
-    sm.tabring = f; f += (size_t)NST * RB * W;
-    sm.labs = reinterpret_cast<int*>(f); f += (p.Lmax + 4) / 4 * 4;
-    sm.xch = f; f += 64;
-    sm.wred = f; f += 32;
-    sm.fin = f;
-  }
+  float* ring = reinterpret_cast<float*>(smraw);
+  int* labs = reinterpret_cast<int*>(ring + (size_t)NST * RB * W);
+  float* xch = reinterpret_cast<float*>(labs + (p.Lmax + 4) / 4 * 4);
+  int* wred = reinterpret_cast<int*>(xch + 64);
+  float* fin = reinterpret_cast<float*>(wred + 64);
+  unsigned long long* full = reinterpret_cast<unsigned long long*>(fin + 4);
+
+  // warps that hold no state of THIS utterance leave after the set-up; the rest synchronise among themselves
+  const int nact = ((S + K - 1) / K + 31) >> 5;
+  const int nsync = nact * 32;
+
   const long long* lab_g = p.targets + (long long)b * p.tgt_stride;
-  for (int i = tid; i < L; i += nthr) sm.labs[i] = (int)min((long long)p.V - 1, max(0ll, lab_g[i]));
+  for (int i = tid; i < L; i += blockDim.x) labs[i] = (int)min((long long)p.V - 1, max(0ll, lab_g[i]));
+  if (tid < 64) xch[tid] = kNeg;                      // step 0 reads the virtual row before the first frame
+  if (tid == 0) {
+    for (int s = 0; s < NST; ++s) mbar_init(full + s, 1);
+    mbar_fence_init();
+  }
   __syncthreads();
+
+  const int nchunks = (T + RB - 1) >> p.RBlog;
+  const float* tab_b = p.tab + (long long)b * p.T * W;
+  auto issue = [&](int c) {                                  // thread 0: one bulk copy per chunk (rows are contiguous)
+    if (c < nchunks) {
+      const int k0 = c << p.RBlog;
+      const int rows = min(RB, T - k0);
+      const int t_lo = dir ? (T - k0 - rows) : k0;
+      const unsigned bytes = (unsigned)rows * (unsigned)W * 4u;
+      unsigned long long* bar = full + (c % NST);
+      mbar_expect_tx(bar, bytes);
+      bulk_g2s(ring + (size_t)(c % NST) * RB * W, tab_b + (long long)t_lo * W, bytes, bar);
+    }
+  };
+  if (tid == 0) for (int c = 0; c < NST - 1; ++c) issue(c);
 
   // same-class chains of the label string, for the occupancy pass (encoding at CtcArgs::chain): the first position
   // of a class sums the occupancies of the whole chain, so each (frame, class) receives exactly ONE reduction
   // and the gradient is bit-reproducible.
-  if (want_grad && (!p.pair || cluster_ctarank() == 0)) {
+  if (GRAD && dir == 0) {
     int* ch = p.chain + (long long)b * p.Lmax;
-    for (int i = tid; i < L; i += nthr) {
-      const int c = sm.labs[i];
+    for (int i = tid; i < L; i += blockDim.x) {
+      const int c = labs[i];
       int nx = -1, first = 1;
-      for (int j = i + 1; j < L; ++j) if (sm.labs[j] == c) { nx = j; break; }
-      for (int j = i - 1; j >= 0; --j) if (sm.labs[j] == c) { first = 0; break; }
+      for (int j = i + 1; j < L; ++j) if (labs[j] == c) { nx = j; break; }
+      for (int j = i - 1; j >= 0; --j) if (labs[j] == c) { first = 0; break; }
       ch[i] = (nx + 1) | (first ? 0 : 0x40000000);
     }
   }
+  if (warp >= nact) return;
 
-  const int npass = (p.pair || !want_grad) ? 1 : 2;
-  for (int pass = 0; pass < npass; ++pass) {
-    const int dir = p.pair ? (int)cluster_ctarank() : pass;
-
-    // ---- per-thread static description of my K local states ---------------------------------
-    // local state jl = tid*K + kk is global state s = jl (forward) or S-1-jl (backward); rows are stored in
-    // LOCAL coordinates so that a thread's K values leave as aligned vector stores.
-    int tix[K];
-    bool valid[K], skip[K];
+  // ---- static description of my K/2 (blank, label) pairs ----------------------------------------
+  int lix[H];                       // table slot of the label state
+  bool skip[H], vB[H], vL[H];
 #pragma unroll
-    for (int kk = 0; kk < K; ++kk) {
-      const int jl = tid * K + kk;
-      valid[kk] = jl < S;
-      const int s = dir ? (S - 1 - jl) : jl;
-      const bool is_lab = valid[kk] && (s & 1);
-      const int li = (s - 1) >> 1;
-      const int cls = is_lab ? sm.labs[li] : p.blank;
-      tix[kk] = valid[kk] ? (p.tab_gather ? (is_lab ? li + 1 : 0) : cls) : (W - 1);   // padding states read a finite slot
-      skip[kk] = false;
-      if (is_lab && jl >= 2) {
-        const int li2 = dir ? li + 1 : li - 1;
-        skip[kk] = sm.labs[li2] != cls;
+  for (int j = 0; j < H; ++j) {
+    const int lj = tid * H + j;                       // local label index
+    vB[j] = lj <= L;
+    vL[j] = lj < L;
+    const int li = dir ? (L - 1 - lj) : lj;
+    const int cls = vL[j] ? labs[li] : p.blank;
+    lix[j] = vL[j] ? (p.tab_gather ? li : cls) : (W - 2);     // padding states read the blank slot: finite
+    skip[j] = false;
+    if (vL[j] && lj >= 1) skip[j] = labs[dir ? li + 1 : li - 1] != cls;
+  }
+
+  // virtual row before the first frame: all mass on local state 0, so the uniform step yields the first row
+  float aB[H], aL[H];
+#pragma unroll
+  for (int j = 0; j < H; ++j) { aB[j] = kNeg; aL[j] = kNeg; }
+  if (tid == 0) aB[0] = 0.f;
+
+  double C = 0.0;                                     // offsets folded away before the current chunk
+  float shift = 0.f;                                  // CTA maximum of the previous chunk's last row
+  float drift = 0.f;                                  // running estimate of the best path's per-frame slope
+  float* srow = p.scr + ((long long)b * 2 + dir) * p.T * p.Spad + (long long)tid * K;
+  float* prow = p.poff + ((long long)b * 2 + dir) * p.T;
+  double* cb = p.cbase + ((long long)b * 2 + dir) * p.nchunk_max;
+  unsigned xw = (unsigned)warp * 4u;                  // byte offset of my hand-off slot, parity toggles bit 7
+  const unsigned xr = (unsigned)(warp > 0 ? warp - 1 : 0) * 4u;
+  const char* xchb = reinterpret_cast<const char*>(xch);
+
+  int k = 0;
+  for (int c = 0; c < nchunks; ++c) {
+    if (tid == 0) { issue(c + NST - 1); if (GRAD) cb[c] = C; }
+    mbar_wait(full + (c % NST), (unsigned)((c / NST) & 1));
+    const int rows = min(RB, T - (c << p.RBlog));
+    const float* trow = ring + (size_t)(c % NST) * RB * W + (dir ? (size_t)(rows - 1) * W : 0);
+    const int tstep = dir ? -W : W;
+    float part = 0.f;                                 // offsets added inside this chunk (fp32: <= RB terms)
+    float off = drift + shift;                        // first step also absorbs the previous chunk's maximum
+    for (int r = 0; r < rows; ++r, ++k, trow += tstep) {
+      const float2 bt = *reinterpret_cast<const float2*>(trow + W - 2);      // {blank, row max}
+      float el[H];
+#pragma unroll
+      for (int j = 0; j < H; ++j) el[j] = trow[lix[j]] - off;
+      const float eb = bt.x - off;
+      part += bt.y + off;
+      off = drift;
+      float l1 = __shfl_up_sync(kFull, aL[H - 1], 1);
+      if (lane == 0) l1 = warp > 0 ? *reinterpret_cast<const float*>(xchb + ((xw & 128u) ^ 128u) + xr) : kNeg;
+#pragma unroll
+      for (int j = H - 1; j >= 0; --j) {
+        const float pl = j > 0 ? aL[j - 1] : l1;       // label state of the pair to my left (old row)
+        const float nL = lse3_log2(aL[j], aB[j], skip[j] ? pl : kNeg);
+        const float nB = lse2_log2(aB[j], pl);
+        aL[j] = fmaxf(nL + el[j], kNeg);
+        aB[j] = fmaxf(nB + eb, kNeg);
       }
-    }
-
-    float a[K];
-#pragma unroll
-    for (int kk = 0; kk < K; ++kk) a[kk] = kNeg;
-    double C = 0.0;
-    float xshift = 0.f;                                 // renormalisation applied after xch was written
-    float drift = 0.f;                                  // running estimate of the best path's per-frame slope
-    float* srow = p.scr + ((long long)b * 2 + dir) * p.T * Spad + (long long)tid * K;
-    double* crow = p.cs + ((long long)b * 2 + dir) * p.T;
-
-    const int nchunks = (T + RB - 1) / RB;
-    const int wq = W >> 2;
-    auto issue = [&](int c) {
-      if (c < nchunks) {
-        const int st = c % NST;
-        const int k0 = c * RB;
-        const int rows = min(RB, T - k0);
-        float* tdst = sm.tabring + (size_t)st * RB * W;
-        for (int i = tid; i < rows * wq; i += nthr) {
-          const int r = i / wq, q = i - r * wq;
-          const int k = k0 + r;
-          const int t = dir ? (T - 1 - k) : k;
-          cp_async16(tdst + (size_t)r * W + 4 * q, p.tab + ((long long)b * p.T + t) * W + 4 * q);
-        }
-      }
-      cp_async_commit();
-    };
-    for (int c = 0; c < NST - 1; ++c) issue(c);
-
-    // CTA-wide barrier, or nothing when one warp holds the whole lattice (its lanes are in lock step through
-    // the shuffles, and __syncwarp orders the shared-memory ring reads)
-    auto sync_all = [&]() { if (ONEWARP) __syncwarp(); else __syncthreads(); };
-
-    int k = 0;
-    for (int c = 0; c < nchunks; ++c) {
-      if (NST == 2) cp_async_wait<0>(); else if (NST == 3) cp_async_wait<1>(); else cp_async_wait<2>();
-      sync_all();
-      issue(c + NST - 1);
-      const int rows = min(RB, T - c * RB);
-      const float* trow = sm.tabring + (size_t)(c % NST) * RB * W;
-      float part = 0.f;                                    // offsets added inside this chunk (fp32: <= RB terms)
-      for (int r = 0; r < rows; ++r, ++k, trow += W) {
-        float lp[K];
-#pragma unroll
-        for (int kk = 0; kk < K; ++kk) lp[kk] = trow[tix[kk]];
-        // per-frame offset (table max + learned slope): keeps the best path near 0, where fp32 is dense
-        const float rmax = trow[W - 1] + drift;
-        part += rmax;
-        if (k == 0) {
-#pragma unroll
-          for (int kk = 0; kk < K; ++kk) {
-            const int jl = tid * K + kk;
-            a[kk] = (jl < 2 && valid[kk]) ? fmaxf(lp[kk] - rmax, kNeg) : kNeg;
-          }
-        } else {
-          float l1 = __shfl_up_sync(kFull, a[K - 1], 1);
-          if (ONEWARP) { if (lane == 0) l1 = kNeg; }
-          else if (lane == 0) l1 = warp > 0 ? fmaxf(sm.xch[((k - 1) & 1) * 32 + warp - 1] - xshift, kNeg) : kNeg;
-          xshift = 0.f;
-#pragma unroll
-          for (int kk = K - 1; kk >= 0; --kk) {
-            const float p0 = a[kk];
-            const float p1 = kk > 0 ? a[kk - 1] : l1;
-            float v;
-            if (kk & 1) {
-              const float p2 = kk > 1 ? a[kk - 2] : l1;   // kk==1: two back is the left neighbour
-              v = lse3_log2(p0, p1, skip[kk] ? p2 : kNeg);
-            } else {
-              v = lse2_log2(p0, p1);
-            }
-            a[kk] = fmaxf(v + (lp[kk] - rmax), kNeg);
-          }
-        }
-        if (!ONEWARP && lane == 31) sm.xch[(k & 1) * 32 + warp] = a[K - 1];
-        if (want_grad) {
-#pragma unroll
-          for (int kk = 0; kk < K; kk += 2) *reinterpret_cast<float2*>(srow + kk) = make_float2(a[kk], a[kk + 1]);
-          if (tid == 0) crow[k] = C + (double)part;
-          srow += Spad;
-        }
-        if (!ONEWARP && r + 1 < rows) __syncthreads();     // hand-off slot of this step visible to the next
-      }
-      C += (double)part;
-      // renormalise at the end of every chunk: block max -> subtract, remember in C
-      float mx = kNeg;
-#pragma unroll
-      for (int kk = 0; kk < K; ++kk) mx = fmaxf(mx, valid[kk] ? a[kk] : kNeg);
-      mx = warp_max(mx);
-      if (!ONEWARP) {
-        if (lane == 0) sm.wred[warp] = mx;
-        __syncthreads();
-        mx = sm.wred[0];
-        for (int w = 1; w < nwarp; ++w) mx = fmaxf(mx, sm.wred[w]);
-      }
-      if (mx > -1.0e29f) {
-#pragma unroll
-        for (int kk = 0; kk < K; ++kk) a[kk] = fmaxf(a[kk] - mx, kNeg);
-        C += (double)mx;
-        xshift = mx;                                      // the hand-off slot still holds the unshifted value
-        drift += mx / (float)rows;                        // what the offsets failed to absorb over this chunk
-      }
-    }
-    cp_async_wait<0>();
-
-    // ---- forward direction: log P = C + log2(2^a[S-1] + 2^a[S-2]) off the last row ---------------
-    if (dir == 0) {
-      __syncthreads();
-#pragma unroll
-      for (int kk = 0; kk < K; ++kk) {
-        const int jl = tid * K + kk;
-        if (valid[kk] && jl >= S - 2) sm.fin[jl - (S - 2) + 1] = a[kk];   // slots 1 (S-2) and 2 (S-1)
-      }
-      if (tid == 0 && S == 1) sm.fin[1] = kNeg;
-      __syncthreads();
-      if (tid == 0) {
-        float r; double lp2 = 0.0; int ok = 0;
-        if (T == 0) r = (L == 0) ? 0.f : INFINITY;
+      if (lane == 31) *reinterpret_cast<float*>(const_cast<char*>(xchb) + xw) = aL[H - 1];
+      xw ^= 128u;
+      if (GRAD) {
+        if (K == 2) *reinterpret_cast<float2*>(srow) = make_float2(aB[0], aL[0]);
         else {
-          const float v = lse2_log2(sm.fin[1], sm.fin[2]);
-          ok = v > -1.0e29f;
-          lp2 = C + (double)v;
-          r = ok ? (float)(-lp2 * (double)kLn2) : INFINITY;
+#pragma unroll
+          for (int j = 0; j < H; j += 2) *reinterpret_cast<float4*>(srow + 2 * j) = make_float4(aB[j], aL[j], aB[j + 1], aL[j + 1]);
         }
-        p.nll[b] = r;
-        if (want_grad) { p.logp2[b] = lp2; p.feasible[b] = ok; }
+        srow += p.Spad;
+        if (tid == 0) prow[k] = part;
       }
+      if (r + 1 == rows) {                            // publish my warp's maximum before the chunk's last barrier
+        float mx = kNeg;
+#pragma unroll
+        for (int j = 0; j < H; ++j) mx = fmaxf(mx, fmaxf(vB[j] ? aB[j] : kNeg, vL[j] ? aL[j] : kNeg));
+        const int km = __reduce_max_sync(kFull, f2ord(mx));
+        if (lane == 0) wred[(c & 1) * 32 + warp] = km;
+      }
+      bar_sync_n(nsync);
     }
-    __syncthreads();
-  }  // pass
+    C += (double)part;
+    const int km = __reduce_max_sync(kFull, lane < nact ? wred[(c & 1) * 32 + lane] : f2ord(kNeg));
+    const float mx = ord2f(km);
+    shift = 0.f;
+    if (mx > -1.0e29f) { shift = mx; drift += mx / (float)rows; }
+  }
+  // the last chunk's maximum was measured but never subtracted: the stored rows do not include it either
+  // ---- forward direction: log P = C + log2(2^a[S-1] + 2^a[S-2]) off the last row ---------------
+  if (dir == 0) {
+#pragma unroll
+    for (int j = 0; j < H; ++j) {
+      const int lj = tid * H + j;
+      if (lj == L) fin[2] = aB[j];
+      if (lj == L - 1) fin[1] = aL[j];
+    }
+    if (tid == 0 && L == 0) fin[1] = kNeg;
+    bar_sync_n(nsync);
+    if (tid == 0) {
+      float r; double lp2 = 0.0; int ok = 0;
+      if (T == 0) r = (L == 0) ? 0.f : INFINITY;
+      else {
+        const float v = lse2_log2(fin[1], fin[2]);
+        ok = v > -1.0e29f;
+        lp2 = C + (double)v;
+        r = ok ? (float)(-lp2 * (double)kLn2) : INFINITY;
+      }
+      p.nll[b] = r;
+      if (GRAD) { p.logp2[b] = lp2; p.feasible[b] = ok; }
+    }
+  }
 
   // ---- batch reduction by the last CTA to finish (deterministic order) ----------------------
-  if (p.loss != nullptr && (!p.pair || cluster_ctarank() == 0)) {
-    __shared__ unsigned is_last;
+  if (p.loss != nullptr && dir == 0 && tid == 0) {
     __threadfence();
-    __syncthreads();
-    if (tid == 0) is_last = (atomicAdd(p.ticket, 1u) == (unsigned)p.B - 1u);
-    __syncthreads();
-    if (is_last && tid == 0) {
+    if (atomicAdd(p.ticket, 1u) == (unsigned)p.B - 1u) {
       __threadfence();
       float acc = 0.f;
       for (int i = 0; i < p.B; ++i) {
@@ -446,14 +438,17 @@ __global__ void __launch_bounds__(256) ctc_occupancy_kernel(CtcArgs p) {
   const float* trow = p.tab + ((long long)b * p.T + t) * p.W;
   const long long* lab = p.targets + (long long)b * p.tgt_stride;
   const int* chain = p.chain + (long long)b * p.Lmax;
-  const float cst = (float)(p.cs[((long long)b * 2 + 0) * p.T + t] + p.cs[((long long)b * 2 + 1) * p.T + (T - 1 - t)] - p.logp2[b]);
+  const int kb = T - 1 - t;                                // the backward walk's step index of this frame
+  const double ca = p.cbase[((long long)b * 2 + 0) * p.nchunk_max + (t >> p.RBlog)] + (double)p.poff[((long long)b * 2 + 0) * p.T + t];
+  const double cbk = p.cbase[((long long)b * 2 + 1) * p.nchunk_max + (kb >> p.RBlog)] + (double)p.poff[((long long)b * 2 + 1) * p.T + kb];
+  const float cst = (float)(ca + cbk - p.logp2[b] - (double)trow[p.W - 1]);   // table entries are relative to the row max
   float bsum = 0.f;
   for (int s = tid; s < S; s += blockDim.x) {
     const bool is_lab = s & 1;
     const int li = (s - 1) >> 1;
     int cls = p.blank;
     if (is_lab) cls = (int)min((long long)p.V - 1, max(0ll, lab[li]));
-    const float lp = trow[p.tab_gather ? (is_lab ? li + 1 : 0) : cls];
+    const float lp = trow[is_lab ? (p.tab_gather ? li : cls) : p.W - 2];
     const float e = arow[s] + brow[S - 1 - s] - lp;           // rows are stored in each walk's local coordinates
     const float o = ex2(fminf(e + cst, 0.f));
     if (is_lab) osm[li] = o;
@@ -491,9 +486,9 @@ __global__ void rescale_if_needed_kernel(float* buf, long long n, const float* u
 // Host side: plan + launch.
 // --------------------------------------------------------------------------------------
 struct CtcPlan {
-  int W, tab_gather, Spad, K, nthr, RB, NST, pair;
+  int W, tab_gather, Spad, K, nthr, RBlog, NST, pair, nchunk_max;
   size_t smem;
-  size_t off_ticket, off_tab, off_scr, off_cs, off_lp, off_feas, off_chain, total;
+  size_t off_ticket, off_tab, off_scr, off_poff, off_cbase, off_lp, off_feas, off_chain, total;
 };
 
 static int env_int(const char* name, int dflt) {
@@ -504,35 +499,36 @@ static int env_int(const char* name, int dflt) {
 static int make_plan(int T, int B, int V, int Lmax, bool want_grad, CtcPlan& pl) {
   const int S = 2 * Lmax + 1;
   pl.tab_gather = (V > 2 * (Lmax + 1)) ? 1 : 0;
-  pl.W = (int)align_up((size_t)(pl.tab_gather ? Lmax + 1 : V) + 1, 4);   // +1: per-frame offset slot
+  pl.W = (int)align_up((size_t)(pl.tab_gather ? Lmax : V) + 2, 4);       // + blank slot + per-frame offset slot
   pl.Spad = (int)align_up((size_t)S, 4);
-  // K (even) states per thread: balance MUFU work over the 4 SM sub-partitions
-  int bestK = -1; long bestCost = 0;
-  for (int K = 2; K <= 12; K += 2) {
-    const int thr = (S + K - 1) / K;
-    const int nw = (thr + 31) / 32;
-    if (nw * 32 > (K <= 4 ? 1024 : 512)) continue;
-    const long cost = (long)((nw + 3) / 4) * K * 20 + (nw > 1 ? 60 : 0) + nw * 4;
-    if (bestK < 0 || cost < bestCost) { bestK = K; bestCost = cost; }
+  // K (even) states per thread.  The walk is bound by per-warp issue latency, not by throughput, so the best
+  // split is the finest one: K=2 while the lattice fits 1024 threads, then 4, 8, 12.
+  int bestK = -1;
+  for (int K : {2, 4, 8, 12}) {
+    if ((S + K - 1) / K <= (K <= 4 ? 1024 : 512)) { bestK = K; break; }
   }
   const int forcedK = env_int("B2ASR_CTC_K", 0);
-  if (forcedK >= 2 && forcedK <= 12 && forcedK % 2 == 0 && (S + forcedK - 1) / forcedK <= (forcedK <= 4 ? 1024 : 512)) bestK = forcedK;
-  if (bestK < 0) { set_error("ctc: label length %d too long (max %d)", Lmax, (12 * 1024 - 1) / 2); return B2ASR_EUNSUPPORTED; }
+  if ((forcedK == 2 || forcedK == 4 || forcedK == 8 || forcedK == 12) && forcedK > bestK && bestK > 0) bestK = forcedK;
+  if (bestK < 0) { set_error("ctc: label length %d too long (max %d)", Lmax, (12 * 512 - 1) / 2); return B2ASR_EUNSUPPORTED; }
   pl.K = bestK;
   pl.nthr = (int)align_up((size_t)((S + bestK - 1) / bestK), 32);
   pl.Spad = pl.nthr * pl.K;                                        // one aligned vector store per thread and row
-  pl.pair = want_grad ? env_int("B2ASR_CTC_PAIR", 1) : 0;
-  pl.NST = 3;
-  pl.RB = 8;
-  const size_t cap = 200 * 1024;
-  while (pl.RB > 1 && lattice_smem_bytes(pl.W, Lmax, pl.RB, pl.NST) > cap) pl.RB >>= 1;
-  pl.smem = lattice_smem_bytes(pl.W, Lmax, pl.RB, pl.NST);
+  pl.pair = want_grad ? 1 : 0;
+  // table ring: NST stages of 2^RBlog rows, each stage one bulk copy; ~64 rows in flight hide the copy latency
+  pl.NST = 4;
+  pl.RBlog = 4;
+  const size_t cap = 160 * 1024;
+  while (pl.RBlog > 0 && lattice_smem_bytes(pl.W, Lmax, 1 << pl.RBlog, pl.NST) > cap) --pl.RBlog;
+  if (lattice_smem_bytes(pl.W, Lmax, 1 << pl.RBlog, pl.NST) > cap) pl.NST = 2;
+  pl.smem = lattice_smem_bytes(pl.W, Lmax, 1 << pl.RBlog, pl.NST);
   if (pl.smem > 227 * 1024) { set_error("ctc: lattice needs %zu bytes of shared memory", pl.smem); return B2ASR_EUNSUPPORTED; }
+  pl.nchunk_max = (T + (1 << pl.RBlog) - 1) >> pl.RBlog;
   size_t off = 0;
   pl.off_ticket = off; off += 256;
   pl.off_tab = off; off += align_up((size_t)B * T * pl.W * sizeof(float), 256);
   pl.off_scr = off; if (want_grad) off += align_up((size_t)B * 2 * T * pl.Spad * sizeof(float), 256);
-  pl.off_cs = off; if (want_grad) off += align_up((size_t)B * 2 * T * sizeof(double), 256);
+  pl.off_poff = off; if (want_grad) off += align_up((size_t)B * 2 * T * sizeof(float), 256);
+  pl.off_cbase = off; if (want_grad) off += align_up((size_t)B * 2 * pl.nchunk_max * sizeof(double), 256);
   pl.off_lp = off; off += align_up((size_t)B * sizeof(double), 256);
   pl.off_feas = off; off += align_up((size_t)B * sizeof(int), 256);
   pl.off_chain = off; off += align_up((size_t)B * (Lmax + 1) * sizeof(int), 256);
@@ -540,19 +536,9 @@ static int make_plan(int T, int B, int V, int Lmax, bool want_grad, CtcPlan& pl)
   return B2ASR_OK;
 }
 
-template <int K, bool GRAD, bool ONEWARP>
-static int launch_lattice_t(const CtcArgs& a, const CtcPlan& pl, cudaStream_t st);
-
-template <int K>
-static int launch_lattice(const CtcArgs& a, const CtcPlan& pl, cudaStream_t st) {
-  const bool grad = a.grad != nullptr, one = pl.nthr == 32;
-  if (grad) return one ? launch_lattice_t<K, true, true>(a, pl, st) : launch_lattice_t<K, true, false>(a, pl, st);
-  return one ? launch_lattice_t<K, false, true>(a, pl, st) : launch_lattice_t<K, false, false>(a, pl, st);
-}
-
-template <int K, bool GRAD, bool ONEWARP>
+template <int K, bool GRAD>
 static int launch_lattice_t(const CtcArgs& a, const CtcPlan& pl, cudaStream_t st) {
-  B2_CUDA_TRY(cudaFuncSetAttribute(ctc_lattice_kernel<K, GRAD, ONEWARP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem));
+  B2_CUDA_TRY(cudaFuncSetAttribute(ctc_lattice_kernel<K, GRAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(a.pair ? 2 * a.B : a.B);
   cfg.blockDim = dim3(pl.nthr);
@@ -565,8 +551,13 @@ static int launch_lattice_t(const CtcArgs& a, const CtcPlan& pl, cudaStream_t st
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  B2_CUDA_TRY(cudaLaunchKernelEx(&cfg, ctc_lattice_kernel<K, GRAD, ONEWARP>, a));
+  B2_CUDA_TRY(cudaLaunchKernelEx(&cfg, ctc_lattice_kernel<K, GRAD>, a));
   return B2ASR_OK;
+}
+
+template <int K>
+static int launch_lattice(const CtcArgs& a, const CtcPlan& pl, cudaStream_t st) {
+  return a.grad != nullptr ? launch_lattice_t<K, true>(a, pl, st) : launch_lattice_t<K, false>(a, pl, st);
 }
 
 }  // namespace b2asr
@@ -611,9 +602,9 @@ extern "C" int b2asr_ctc_loss_fwd_bwd(const float* x, int64_t sx_t, int64_t sx_b
   a.ticket = (unsigned*)(w + pl.off_ticket);
   a.tab = (float*)(w + pl.off_tab); a.W = pl.W; a.tab_gather = pl.tab_gather;
   a.scr = (float*)(w + pl.off_scr); a.Spad = pl.Spad;
-  a.cs = (double*)(w + pl.off_cs);
+  a.poff = (float*)(w + pl.off_poff); a.cbase = (double*)(w + pl.off_cbase); a.nchunk_max = pl.nchunk_max;
   a.logp2 = (double*)(w + pl.off_lp); a.feasible = (int*)(w + pl.off_feas); a.chain = (int*)(w + pl.off_chain);
-  a.RB = pl.RB; a.NST = pl.NST; a.pair = pl.pair;
+  a.RBlog = pl.RBlog; a.NST = pl.NST; a.pair = pl.pair;
 
   // ---- wide pass --------------------------------------------------------------------------
   const long long rows = (long long)T * B;
@@ -636,9 +627,7 @@ extern "C" int b2asr_ctc_loss_fwd_bwd(const float* x, int64_t sx_t, int64_t sx_b
   switch (pl.K) {
     case 2: rc = launch_lattice<2>(a, pl, st); break;
     case 4: rc = launch_lattice<4>(a, pl, st); break;
-    case 6: rc = launch_lattice<6>(a, pl, st); break;
     case 8: rc = launch_lattice<8>(a, pl, st); break;
-    case 10: rc = launch_lattice<10>(a, pl, st); break;
     case 12: rc = launch_lattice<12>(a, pl, st); break;
     default: set_error("ctc: internal: K=%d", pl.K); return B2ASR_EUNSUPPORTED;
   }
