@@ -40,6 +40,7 @@ struct CtcArgs {
   float* poff;                            // [B][2][T] offset folded away inside the row's chunk, up to and including the row
   double* cbase; int nchunk_max;          // [B][2][nchunk_max] offset folded away before each chunk
   double* logp2; int* feasible;           // [B] log2 P(l|x) and whether any alignment exists
+  int* cls;                               // [B][Lmax] label classes clamped to [0,V)
   int* chain;                             // [B][Lmax] bits 0..29: 1 + next position with the same class (0 = none); bit 30: not the first of its class
   int RBlog, NST;                         // ring: log2(rows per stage), stages
   int pair;                               // 1 = 2-CTA cluster per utterance (meet in the middle)
@@ -277,12 +278,14 @@ __global__ void __launch_bounds__(lattice_max_threads<K>(), 1) ctc_lattice_kerne
   // and the gradient is bit-reproducible.
   if (GRAD && dir == 0) {
     int* ch = p.chain + (long long)b * p.Lmax;
+    int* cl = p.cls + (long long)b * p.Lmax;
     for (int i = tid; i < L; i += blockDim.x) {
       const int c = labs[i];
       int nx = -1, first = 1;
       for (int j = i + 1; j < L; ++j) if (labs[j] == c) { nx = j; break; }
       for (int j = i - 1; j >= 0; --j) if (labs[j] == c) { first = 0; break; }
       ch[i] = (nx + 1) | (first ? 0 : 0x40000000);
+      cl[i] = c;
     }
   }
   if (warp >= nact) return;
@@ -413,62 +416,71 @@ __global__ void __launch_bounds__(lattice_max_threads<K>(), 1) ctc_lattice_kerne
 }
 
 // --------------------------------------------------------------------------------------
-// Occupancy pass: wide.  One CTA per (utterance, frame): occupancy of every lattice state from the stored
+// Occupancy pass: wide.  One WARP per (utterance, frame), FPC consecutive frames of one utterance per CTA (they
+// share the label classes and chains in shared memory): occupancy of every lattice state from the stored
 // alpha / beta rows, o_s = 2^(alpha_t(s) + beta_t(s) - lp_t(s) + C_a + C_b - log2 P), then
-// grad[t,b,class(s)] -= scale_b * o_s.  Blank states are reduced in the CTA (one reduction per row), label
-// states go out as fire-and-forget reductions (a class repeated in the label string just adds twice).
+// grad[t,b,class(s)] -= scale_b * o_s.  Blank states are reduced in the warp (one reduction per row); label
+// states are staged in shared memory and the first position of every class sums its chain, so each
+// (frame, class) receives exactly one fire-and-forget reduction (bit-reproducible gradient).
 // --------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) ctc_occupancy_kernel(CtcArgs p) {
-  extern __shared__ __align__(16) float osm[];             // [L] occupancy of the label states
-  __shared__ float wsum[8];
-  const int b = blockIdx.y, t = blockIdx.x;
+__global__ void __launch_bounds__(256) ctc_occupancy_kernel(CtcArgs p, int FPC) {
+  extern __shared__ __align__(16) int osm_i[];             // cls[Lp] | chain[Lp] | occ[FPC][Lp]
+  const int b = blockIdx.y;
   const int T = (int)min((long long)p.T, max(0ll, p.in_len[b]));
-  if (t >= T) return;
+  const int t0 = blockIdx.x * FPC;
+  if (t0 >= T) return;
   const int L = (int)min((long long)p.Lmax, max(0ll, p.tgt_len[b]));
   const int S = 2 * L + 1;
+  const int Lp = (p.Lmax + 4) / 4 * 4;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  int* cls = osm_i;
+  int* chn = osm_i + Lp;
+  float* occ = reinterpret_cast<float*>(osm_i + 2 * Lp) + (size_t)warp * Lp;
+  const bool feasible = p.feasible[b] != 0;
+  if (feasible) {
+    const int* cg = p.cls + (long long)b * p.Lmax;
+    const int* hg = p.chain + (long long)b * p.Lmax;
+    for (int i = tid; i < L; i += blockDim.x) { cls[i] = cg[i]; chn[i] = hg[i]; }
+  }
+  __syncthreads();
+  const int t = t0 + warp;
+  if (t >= T) return;
   float* grow = p.grad + (long long)t * p.sg_t + (long long)b * p.sg_b;
-  if (!p.feasible[b]) {                                  // no alignment: NaN on the valid rows, as ATen does
-    for (int v = tid; v < p.V; v += blockDim.x) grow[v] = __int_as_float(0x7fc00000);
+  if (!feasible) {                                       // no alignment: NaN on the valid rows, as ATen does
+    for (int v = lane; v < p.V; v += 32) grow[v] = __int_as_float(0x7fc00000);
     return;
   }
   const float gs = row_scale(p, L);
-  const float* arow = p.scr + (((long long)b * 2 + 0) * p.T + t) * p.Spad;
-  const float* brow = p.scr + (((long long)b * 2 + 1) * p.T + (T - 1 - t)) * p.Spad;
-  const float* trow = p.tab + ((long long)b * p.T + t) * p.W;
-  const long long* lab = p.targets + (long long)b * p.tgt_stride;
-  const int* chain = p.chain + (long long)b * p.Lmax;
   const int kb = T - 1 - t;                                // the backward walk's step index of this frame
+  const float* arow = p.scr + (((long long)b * 2 + 0) * p.T + t) * p.Spad;
+  const float* brow = p.scr + (((long long)b * 2 + 1) * p.T + kb) * p.Spad;
+  const float* trow = p.tab + ((long long)b * p.T + t) * p.W;
   const double ca = p.cbase[((long long)b * 2 + 0) * p.nchunk_max + (t >> p.RBlog)] + (double)p.poff[((long long)b * 2 + 0) * p.T + t];
   const double cbk = p.cbase[((long long)b * 2 + 1) * p.nchunk_max + (kb >> p.RBlog)] + (double)p.poff[((long long)b * 2 + 1) * p.T + kb];
   const float cst = (float)(ca + cbk - p.logp2[b] - (double)trow[p.W - 1]);   // table entries are relative to the row max
+  const float cb = cst - trow[p.W - 2];
+  // rows are stored in each walk's local coordinates: alpha state s at arow[s], beta state s at brow[S-1-s]
   float bsum = 0.f;
-  for (int s = tid; s < S; s += blockDim.x) {
-    const bool is_lab = s & 1;
-    const int li = (s - 1) >> 1;
-    int cls = p.blank;
-    if (is_lab) cls = (int)min((long long)p.V - 1, max(0ll, lab[li]));
-    const float lp = trow[is_lab ? (p.tab_gather ? li : cls) : p.W - 2];
-    const float e = arow[s] + brow[S - 1 - s] - lp;           // rows are stored in each walk's local coordinates
-    const float o = ex2(fminf(e + cst, 0.f));
-    if (is_lab) osm[li] = o;
-    else bsum += o;
+  for (int i = lane; i <= L; i += 32) {                   // pair i = blank state 2i and label state 2i+1
+    const float2 av = *reinterpret_cast<const float2*>(arow + 2 * i);
+    const float bb = brow[2 * (L - i)];
+    bsum += ex2(fminf(av.x + bb + cb, 0.f));
+    if (i < L) {
+      const float bl = brow[2 * (L - i) - 1];
+      const float lp = trow[p.tab_gather ? i : cls[i]];
+      occ[i] = ex2(fminf(av.y + bl - lp + cst, 0.f));
+    }
   }
   bsum = warp_sum(bsum);
-  if (lane == 0) wsum[warp] = bsum;
-  __syncthreads();
-  for (int i = tid; i < L; i += blockDim.x) {            // the first position of every class sums its chain
-    const int v = chain[i];
+  __syncwarp();
+  for (int i = lane; i < L; i += 32) {                    // the first position of every class sums its chain
+    const int v = chn[i];
     if (v & 0x40000000) continue;
-    float sum = osm[i];
-    for (int nx = (v & 0x3fffffff) - 1; nx >= 0; nx = (chain[nx] & 0x3fffffff) - 1) sum += osm[nx];
-    red_add_f32(grow + (int)min((long long)p.V - 1, max(0ll, lab[i])), -gs * sum);
+    float sum = occ[i];
+    for (int nx = (v & 0x3fffffff) - 1; nx >= 0; nx = (chn[nx] & 0x3fffffff) - 1) sum += occ[nx];
+    red_add_f32(grow + cls[i], -gs * sum);
   }
-  if (tid == 0) {
-    float tot = 0.f;
-    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) tot += wsum[w];
-    red_add_f32(grow + p.blank, -gs * tot);
-  }
+  if (lane == 0) red_add_f32(grow + p.blank, -gs * bsum);
 }
 
 // --------------------------------------------------------------------------------------
@@ -488,7 +500,7 @@ __global__ void rescale_if_needed_kernel(float* buf, long long n, const float* u
 struct CtcPlan {
   int W, tab_gather, Spad, K, nthr, RBlog, NST, pair, nchunk_max;
   size_t smem;
-  size_t off_ticket, off_tab, off_scr, off_poff, off_cbase, off_lp, off_feas, off_chain, total;
+  size_t off_ticket, off_tab, off_scr, off_poff, off_cbase, off_lp, off_feas, off_chain, off_cls, total;
 };
 
 static int env_int(const char* name, int dflt) {
@@ -532,6 +544,7 @@ static int make_plan(int T, int B, int V, int Lmax, bool want_grad, CtcPlan& pl)
   pl.off_lp = off; off += align_up((size_t)B * sizeof(double), 256);
   pl.off_feas = off; off += align_up((size_t)B * sizeof(int), 256);
   pl.off_chain = off; off += align_up((size_t)B * (Lmax + 1) * sizeof(int), 256);
+  pl.off_cls = off; off += align_up((size_t)B * (Lmax + 1) * sizeof(int), 256);
   pl.total = off;
   return B2ASR_OK;
 }
@@ -603,7 +616,7 @@ extern "C" int b2asr_ctc_loss_fwd_bwd(const float* x, int64_t sx_t, int64_t sx_b
   a.tab = (float*)(w + pl.off_tab); a.W = pl.W; a.tab_gather = pl.tab_gather;
   a.scr = (float*)(w + pl.off_scr); a.Spad = pl.Spad;
   a.poff = (float*)(w + pl.off_poff); a.cbase = (double*)(w + pl.off_cbase); a.nchunk_max = pl.nchunk_max;
-  a.logp2 = (double*)(w + pl.off_lp); a.feasible = (int*)(w + pl.off_feas); a.chain = (int*)(w + pl.off_chain);
+  a.logp2 = (double*)(w + pl.off_lp); a.feasible = (int*)(w + pl.off_feas); a.chain = (int*)(w + pl.off_chain); a.cls = (int*)(w + pl.off_cls);
   a.RBlog = pl.RBlog; a.NST = pl.NST; a.pair = pl.pair;
 
   // ---- wide pass --------------------------------------------------------------------------
@@ -635,7 +648,14 @@ extern "C" int b2asr_ctc_loss_fwd_bwd(const float* x, int64_t sx_t, int64_t sx_b
 
   // ---- occupancy pass (gradient only) ---------------------------------------------------------
   if (want_grad) {
-    ctc_occupancy_kernel<<<dim3((unsigned)T, (unsigned)B), 256, (size_t)(Lmax + 4) * sizeof(float), st>>>(a);
+    const int Lp = (Lmax + 4) / 4 * 4;
+    int FPC = 8;
+    while (FPC > 1 && (size_t)(FPC + 2) * Lp * 4 > 96 * 1024) FPC >>= 1;
+    const size_t osm = (size_t)(FPC + 2) * Lp * 4;
+    B2_REQUIRE(osm <= 200 * 1024, B2ASR_EUNSUPPORTED, "ctc: label length %d too long for the occupancy pass", Lmax);
+    if (osm > 48 * 1024)
+      B2_CUDA_TRY(cudaFuncSetAttribute(ctc_occupancy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)osm));
+    ctc_occupancy_kernel<<<dim3((unsigned)((T + FPC - 1) / FPC), (unsigned)B), 32 * FPC, osm, st>>>(a, FPC);
     B2_CUDA_TRY(cudaGetLastError());
   }
   return B2ASR_OK;
