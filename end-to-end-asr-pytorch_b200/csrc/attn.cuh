@@ -37,7 +37,11 @@ struct AttnArgs {
   float* d_zq;                                  // [B,A] out: grad wrt phi(s) pre-activation
   float* d_s;                                   // [B,dec] out or nullptr
   float* pgrad; long long pgrad_stride;         // [B*CS, pgrad_stride] per-CTA parameter-gradient slots
+  long long* trace;                             // debug: clock64 stamps of CTA 0's phases (nullptr = off)
 };
+
+#define B2_TRACE(p, slot) do { if ((p).trace && blockIdx.x == 0 && threadIdx.x == 0) (p).trace[slot] = clock64(); } while (0)
+long long* attn_trace_buffer();                // device buffer when B2ASR_ATT_TRACE is set, else nullptr
 
 // shared-memory carve-up, identical arithmetic on host (size) and device (pointers)
 struct AttnSmem {

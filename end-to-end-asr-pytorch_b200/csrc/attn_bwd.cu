@@ -17,21 +17,20 @@
 
 namespace b2asr {
 
-struct BwdExtra { size_t de, al, dfpart, dfo, dfw, dqp, dzq, tmp, total; };
+struct BwdExtra { size_t de, al, wls, dfo, dfw, dqp, dzq, tmp, total; };
 
 __host__ __device__ inline BwdExtra attn_bwd_extra(const AttnArgs& p) {
   BwdExtra x; size_t o = 0;
   const int CP = (p.C + 3) / 4 * 4;
-  const int nwarp = p.NT / 32;
   auto take = [&](size_t n) { size_t at = o; o += (n + 3) / 4 * 4; return at; };
   x.de = take(p.chunk_max + 4);
   x.al = take(p.chunk_max + 4);
-  x.dfpart = take((size_t)nwarp * p.TFK * 16);
+  x.wls = take((size_t)p.A * CP);                        // Wl as [A][CP] for the df pass
   x.dfo = take((size_t)p.chunk_max * CP);
   x.dfw = take((size_t)(p.chunk_max + 2 * p.Kw) * CP);
   x.dqp = take(p.A);
   x.dzq = take(p.A);
-  x.tmp = take((size_t)(CP / 4) * p.chunk_max);
+  { const size_t t1 = (size_t)(CP / 4) * p.chunk_max, t2 = 4 * (size_t)((p.dec + p.CS - 1) / p.CS); x.tmp = take(t1 > t2 ? t1 : t2); }
   x.total = o;
   return x;
 }
@@ -64,6 +63,7 @@ __device__ __forceinline__ float warp_reduce16(float (&v)[16], int lane, int& id
   return v[0];
 }
 
+template <int CPT>
 __global__ void __launch_bounds__(512, 1) attn_step_bwd_kernel(AttnArgs p) {
   extern __shared__ __align__(128) unsigned char smraw[];
   const BwdExtra X = attn_bwd_extra(p);
@@ -78,7 +78,7 @@ __global__ void __launch_bounds__(512, 1) attn_step_bwd_kernel(AttnArgs p) {
   float* stat = reinterpret_cast<float*>(smraw + L.off_stat);
   float* red = reinterpret_cast<float*>(smraw + L.off_red);
   float* ex = reinterpret_cast<float*>(smraw + L.off_extra);
-  float* de = ex + X.de; float* al = ex + X.al; float* dfpart = ex + X.dfpart; float* dfo = ex + X.dfo;
+  float* de = ex + X.de; float* al = ex + X.al; float* wls = ex + X.wls; float* dfo = ex + X.dfo;
   float* dfw = ex + X.dfw; float* dqp = ex + X.dqp; float* dzq = ex + X.dzq; float* tmp = ex + X.tmp;
 
   const int tid = threadIdx.x, NT = blockDim.x, lane = tid & 31, warp = tid >> 5, nwarp = NT >> 5;
@@ -99,12 +99,11 @@ __global__ void __launch_bounds__(512, 1) attn_step_bwd_kernel(AttnArgs p) {
   const bool loc = p.mode == 1;
   float* slot = p.pgrad ? p.pgrad + (long long)blockIdx.x * p.pgrad_stride : nullptr;   // [A*C | C*KW1 | A | 1]
 
+  B2_TRACE(p, 16);
   if (tid == 0) {
     for (int s = 0; s < NS; ++s) mbar_init(&full[s], 1);
     mbar_fence_init();
   }
-  cluster_or_cta_sync(CS);            // #0
-
   auto issue = [&](int i) {          // thread 0 only; encoder-feature tiles first, then key tiles
     if (i >= ntiles) return;
     const int s = i % NS;
@@ -116,13 +115,13 @@ __global__ void __launch_bounds__(512, 1) attn_step_bwd_kernel(AttnArgs p) {
     bulk_g2s(dst, src, bytes, &full[s]);
   };
   if (tid == 0) for (int i = 0; i < NS; ++i) issue(i);
+  B2_TRACE(p, 17);
 
-  // ---- stage small operands; recompute the location features of my frames ---------------------
+  // ---- stage small operands (every global load issued before the one barrier that publishes them) ----------
   for (int a = tid; a < A; a += NT) q_sm[a] = p.q_saved[(long long)b * A + a];
   for (int d = tid; d < D; d += NT) dctx[d] = p.d_ctx[(long long)b * D + d];
   for (int j = tid; j < nf; j += NT) al[j] = p.att_saved[(long long)b * T + t0 + j];
   if (loc) {
-    for (int i = tid; i < KW1 * CP; i += NT) wcT[i] = 0.f;
     const int npa = nf + 2 * p.Kw;
     const float unif = len > 0 ? 1.f / (float)len : 0.f;
     for (int j = tid; j < npa; j += NT) {
@@ -131,13 +130,22 @@ __global__ void __launch_bounds__(512, 1) attn_step_bwd_kernel(AttnArgs p) {
       if (t >= 0 && t < T) v = p.prev_att ? p.prev_att[(long long)b * T + t] : (t < len ? unif : 0.f);
       pa[j] = v;
     }
-    __syncthreads();
+#pragma unroll 8
     for (int i = tid; i < C * KW1; i += NT) { const int c = i / KW1, k = i - c * KW1; wcT[k * CP + c] = __ldg(p.Wc + i); }
-    __syncthreads();
+    for (int i = tid; i < KW1 * (CP - C); i += NT) { const int k = i / (CP - C), c = C + i - k * (CP - C); wcT[k * CP + c] = 0.f; }
+#pragma unroll 4
+    for (int i = tid; i < A * C; i += NT) { const int a = i / C, c = i - a * C; wls[a * CP + c] = __ldg(p.Wl + i); }
+    for (int i = tid; i < A * (CP - C); i += NT) { const int a = i / (CP - C), c = C + i - a * (CP - C); wls[a * CP + c] = 0.f; }
+  }
+  cluster_or_cta_sync(CS);            // #0: operands staged; every CTA of the cluster is running (DSMEM is legal)
+
+  // ---- recompute the location features of my frames ------------------------------------------------
+  if (loc) {
     const float4* w4 = reinterpret_cast<const float4*>(wcT);
     for (int item = tid; item < nf * CQ; item += NT) {
       const int cg = item / nf, fl = item - cg * nf;
       float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
       for (int k = 0; k < KW1; ++k) {
         const float pv = pa[fl + k];
         const float4 w = w4[k * CQ + cg];
@@ -147,6 +155,7 @@ __global__ void __launch_bounds__(512, 1) attn_step_bwd_kernel(AttnArgs p) {
     }
   }
   __syncthreads();
+  B2_TRACE(p, 18);
 
   // ---- d_alpha over my frames: external part + h . d_ctx (one warp per frame) -------------------
   const int ngroups = D / 4;
@@ -169,6 +178,7 @@ __global__ void __launch_bounds__(512, 1) attn_step_bwd_kernel(AttnArgs p) {
     if (tid == 0) { fence_proxy_async_smem(); issue(i + NS); }
   }
 
+  B2_TRACE(p, 19);
   // ---- softmax backward: de = scale * alpha * (d_alpha - <alpha, d_alpha>) ------------------------
   float part = 0.f;
   for (int j = tid; j < nf; j += NT) part = fmaf(al[j], de[j], part);
@@ -183,85 +193,111 @@ __global__ void __launch_bounds__(512, 1) attn_step_bwd_kernel(AttnArgs p) {
   float dbg_part = 0.f;
   for (int j = tid; j < nf; j += NT) { const float v = p.scale * al[j] * (de[j] - dotsum); de[j] = v; dbg_part += v; }
   dbg_part = cta_reduce_sum(dbg_part, red);     // (also orders the de[] writes before the reads below)
-  if (loc && slot && tid == 0) slot[(long long)A * C + (long long)C * KW1 + A] += dbg_part;
+  if (loc && slot && tid == 0) red_add_f32(slot + (long long)A * C + (long long)C * KW1 + A, dbg_part);
 
+  B2_TRACE(p, 20);
   // ---- main pass over the key tiles: thread a owns attention dimension a -------------------------
+  // Two frames per iteration (two independent recompute chains).  d_zl overwrites the key value it was computed
+  // from in the ring stage; after the tile, df[t][c] = sum_a d_zl[t][a] Wl[a][c] is formed by one warp per
+  // (frame, 4 channels) with lanes striding a -- 6 shuffles per 4 outputs instead of 16 per frame and warp.
   const bool active = tid < A;
-  float wl[kAttMaxC], dwl[kAttMaxC];
+  float wl[CPT], dwl[CPT];
 #pragma unroll
-  for (int c = 0; c < kAttMaxC; ++c) { wl[c] = (active && loc && c < C) ? __ldg(p.Wl + (long long)tid * C + c) : 0.f; dwl[c] = 0.f; }
+  for (int c = 0; c < CPT; ++c) { wl[c] = (active && loc && c < C) ? wls[tid * CP + (c < CP ? c : 0)] : 0.f; dwl[c] = 0.f; }
   const float qa = active ? q_sm[tid] : 0.f;
   const float wga = (active && loc) ? __ldg(p.wg + tid) : 0.f;
   float dq_acc = 0.f, dwg_acc = 0.f;
+  const int kcol = active ? tid : 0;
   float* dkb = p.d_keys + (long long)b * p.dk_bstride + (long long)t0 * A;
   for (int i = 0; i < nK; ++i) {
     const int ti = nH + i, s = ti % NS;
     mbar_wait(&full[s], (unsigned)((ti / NS) & 1));
-    const float* kt = ring + (size_t)s * stage_floats;
+    float* kt = ring + (size_t)s * stage_floats;
     const int f0 = i * TFK, n = min(TFK, nf - f0);
-    for (int j = 0; j < n; ++j) {
-      float v[16];
+    for (int j = 0; j < n; j += 2) {
 #pragma unroll
-      for (int c = 0; c < 16; ++c) v[c] = 0.f;
-      if (active) {
-        const float kv = kt[j * A + tid];
-        const float dev = de[f0 + j];
-        float dpre;
-        if (loc) {
-          const float4* f4 = reinterpret_cast<const float4*>(fsm) + (size_t)(f0 + j) * CQ;
-          float fv[kAttMaxC];
+      for (int u = 0; u < 2; ++u) {
+        const int jj = j + u;
+        if (jj < n) {                                     // uniform
+          const float kv = kt[jj * A + kcol];
+          const float dev = de[f0 + jj];
+          float dpre, dzl = 0.f;
+          if (loc) {
+            const float4* f4 = reinterpret_cast<const float4*>(fsm) + (size_t)(f0 + jj) * CQ;
+            float fv[CPT];
 #pragma unroll
-          for (int c4 = 0; c4 < kAttMaxC / 4; ++c4) {
-            float4 t4 = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (c4 < CQ) t4 = f4[c4];
-            fv[4 * c4 + 0] = t4.x; fv[4 * c4 + 1] = t4.y; fv[4 * c4 + 2] = t4.z; fv[4 * c4 + 3] = t4.w;
+            for (int c4 = 0; c4 < CPT / 4; ++c4) {
+              float4 t4 = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (c4 < CQ) t4 = f4[c4];
+              fv[4 * c4 + 0] = t4.x; fv[4 * c4 + 1] = t4.y; fv[4 * c4 + 2] = t4.z; fv[4 * c4 + 3] = t4.w;
+            }
+            float zl = 0.f;
+#pragma unroll
+            for (int c = 0; c < CPT; ++c) zl = fmaf(wl[c], fv[c], zl);
+            const float l = tanh_fast(zl);
+            const float uu = tanh_fast(kv + qa + l);
+            dwg_acc = fmaf(dev, uu, dwg_acc);
+            dpre = dev * wga * (1.f - uu * uu);
+            dq_acc += dpre;
+            dzl = dpre * (1.f - l * l);
+#pragma unroll
+            for (int c = 0; c < CPT; ++c) dwl[c] = fmaf(dzl, fv[c], dwl[c]);
+          } else {
+            dpre = dev * qa;
+            dq_acc = fmaf(dev, kv, dq_acc);
           }
-          float zl = 0.f;
-#pragma unroll
-          for (int c = 0; c < kAttMaxC; ++c) zl = fmaf(wl[c], fv[c], zl);
-          const float l = tanh_acc(zl);
-          const float u = tanh_acc(kv + qa + l);
-          dwg_acc = fmaf(dev, u, dwg_acc);
-          dpre = dev * wga * (1.f - u * u);
-          dq_acc += dpre;
-          const float dzl = dpre * (1.f - l * l);
-#pragma unroll
-          for (int c = 0; c < kAttMaxC; ++c) { dwl[c] = fmaf(dzl, fv[c], dwl[c]); v[c] = wl[c] * dzl; }
-        } else {
-          dpre = dev * qa;
-          dq_acc = fmaf(dev, kv, dq_acc);
+          if (active) {
+            // fire-and-forget reduction (RED.ADD.F32): one owner per element and launch, so no contention, and
+            // no L2 round trip on the loop's critical path as a load-add-store would put there
+            red_add_f32(dkb + (long long)(f0 + jj) * A + tid, dpre);
+            if (loc) kt[jj * A + tid] = dzl;
+          }
         }
-        // fire-and-forget reduction (RED.ADD.F32): one owner per element and launch, so no contention, and
-        // no L2 round trip on the loop's critical path as a load-add-store would put there
-        red_add_f32(dkb + (long long)(f0 + j) * A + tid, dpre);
-      }
-      if (loc) {
-        int idx;
-        const float tot = warp_reduce16(v, lane, idx);
-        if ((lane & 1) == 0) dfpart[((size_t)warp * TFK + j) * 16 + idx] = tot;
       }
     }
     __syncthreads();
     if (loc) {
-      for (int item = tid; item < n * CP; item += NT) {
-        const int j = item / CP, c = item - j * CP;
-        float acc = 0.f;
-        for (int w = 0; w < nwarp; ++w) acc += dfpart[((size_t)w * TFK + j) * 16 + c];
-        dfo[(size_t)(f0 + j) * CP + c] = acc;
+      const float4* wl4 = reinterpret_cast<const float4*>(wls);
+      for (int task = warp; task < n * CQ; task += nwarp) {
+        const int j = task / CQ, cq = task - j * CQ;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int a = lane; a < A; a += 32) {
+          const float dz = kt[j * A + a];
+          const float4 w = wl4[a * CQ + cq];
+          acc.x = fmaf(dz, w.x, acc.x); acc.y = fmaf(dz, w.y, acc.y); acc.z = fmaf(dz, w.z, acc.z); acc.w = fmaf(dz, w.w, acc.w);
+        }
+        {
+          const bool up = lane & 16;
+          const float s0 = up ? acc.x : acc.z, s1 = up ? acc.y : acc.w;
+          const float k0 = up ? acc.z : acc.x, k1 = up ? acc.w : acc.y;
+          acc.x = k0 + __shfl_xor_sync(kFull, s0, 16);
+          acc.y = k1 + __shfl_xor_sync(kFull, s1, 16);
+        }
+        {
+          const bool up = lane & 8;
+          const float s0 = up ? acc.x : acc.y, k0 = up ? acc.y : acc.x;
+          acc.x = k0 + __shfl_xor_sync(kFull, s0, 8);
+        }
+        acc.x += __shfl_xor_sync(kFull, acc.x, 4);
+        acc.x += __shfl_xor_sync(kFull, acc.x, 2);
+        acc.x += __shfl_xor_sync(kFull, acc.x, 1);
+        if ((lane & 7) == 0) dfo[(size_t)(f0 + j) * CP + cq * 4 + ((lane >> 4) & 1) * 2 + ((lane >> 3) & 1)] = acc.x;
       }
     }
     __syncthreads();
     if (tid == 0) { fence_proxy_async_smem(); issue(ti + NS); }
   }
 
+  B2_TRACE(p, 21);
   // ---- parameter-gradient slot: dWl rows and dwg (private to this CTA; plain read-modify-write) ---
   if (loc && slot && active) {
 #pragma unroll
-    for (int c = 0; c < kAttMaxC; ++c) if (c < C) slot[(long long)tid * C + c] += dwl[c];
-    slot[(long long)A * C + (long long)C * KW1 + tid] += dwg_acc;
+    for (int c = 0; c < CPT; ++c) if (c < C) red_add_f32(slot + (long long)tid * C + c, dwl[c]);
+    red_add_f32(slot + (long long)A * C + (long long)C * KW1 + tid, dwg_acc);
   }
   if (active) dqp[tid] = dq_acc;
   cluster_or_cta_sync(CS);            // #2: dq partials and df of every CTA are complete
+  B2_TRACE(p, 22);
 
   // ---- dq: slice-reduce over the cluster, through tanh', broadcast for the d_s product --------
   {
@@ -278,27 +314,40 @@ __global__ void __launch_bounds__(512, 1) attn_step_bwd_kernel(AttnArgs p) {
     }
   }
 
+  B2_TRACE(p, 23);
   // ---- location branch: gather df halo from the neighbours, then dWc and d_prev_att -------------
   if (loc) {
     const int nw = nf + 2 * p.Kw;
-    for (int item = tid; item < nw * CP; item += NT) {
-      const int w = item / CP, c = item - w * CP;
+#pragma unroll 4
+    for (int item = tid; item < nw * CQ; item += NT) {       // one 128-bit (4-channel) load per item
+      const int w = item / CQ, cg = item - w * CQ;
       const int tg = t0 - p.Kw + w;
-      float v = 0.f;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
       if (tg >= 0 && tg < len && chunk > 0) {
         const int rr = tg / chunk, li = tg - rr * chunk;
-        v = (CS > 1) ? ld_dsmem_f32(dsmem_addr(dfo + (size_t)li * CP + c, (unsigned)rr)) : dfo[(size_t)li * CP + c];
+        const float* src = dfo + (size_t)li * CP + cg * 4;
+        v = (CS > 1) ? ld_dsmem_f32x4(dsmem_addr(src, (unsigned)rr)) : *reinterpret_cast<const float4*>(src);
       }
-      dfw[item] = v;
+      reinterpret_cast<float4*>(dfw)[item] = v;
     }
     __syncthreads();
-    if (slot) {                     // dWc[c][k] += sum_j df[j][c] * prev_att[t0+j+k-Kw]
+    if (slot) {                     // dWc[c][k] += sum_j df[j][c] * prev_att[t0+j+k-Kw]; thread = (tap, 4 channels)
       float* sWc = slot + (long long)A * C;
-      for (int item = tid; item < C * KW1; item += NT) {
-        const int c = item / KW1, k = item - c * KW1;
-        float acc = 0.f;
-        for (int j = 0; j < nf; ++j) acc = fmaf(dfo[(size_t)j * CP + c], pa[j + k], acc);
-        sWc[item] += acc;
+      const float4* d4 = reinterpret_cast<const float4*>(dfo);
+      for (int item = tid; item < KW1 * CQ; item += NT) {
+        const int cg = item / KW1, k = item - cg * KW1;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+        for (int j = 0; j < nf; ++j) {
+          const float pv = pa[j + k];
+          const float4 d = d4[(size_t)j * CQ + cg];
+          acc.x = fmaf(d.x, pv, acc.x); acc.y = fmaf(d.y, pv, acc.y); acc.z = fmaf(d.z, pv, acc.z); acc.w = fmaf(d.w, pv, acc.w);
+        }
+        const int c0 = cg * 4;
+        if (c0 + 0 < C) red_add_f32(sWc + (c0 + 0) * KW1 + k, acc.x);
+        if (c0 + 1 < C) red_add_f32(sWc + (c0 + 1) * KW1 + k, acc.y);
+        if (c0 + 2 < C) red_add_f32(sWc + (c0 + 2) * KW1 + k, acc.z);
+        if (c0 + 3 < C) red_add_f32(sWc + (c0 + 3) * KW1 + k, acc.w);
       }
     }
     if (p.d_prev_att) {             // d_prev_att[t0+i] = sum_k sum_c Wc[c][k] * df[t0+i-k+Kw][c]
@@ -307,6 +356,7 @@ __global__ void __launch_bounds__(512, 1) attn_step_bwd_kernel(AttnArgs p) {
       for (int item = tid; item < nf * CQ; item += NT) {
         const int cg = item / nf, i = item - cg * nf;
         float acc = 0.f;
+#pragma unroll 4
         for (int k = 0; k < KW1; ++k) {
           const float4 w = w4[k * CQ + cg];
           const float4 d = d4[(size_t)(i - k + 2 * p.Kw) * CQ + cg];
@@ -323,24 +373,36 @@ __global__ void __launch_bounds__(512, 1) attn_step_bwd_kernel(AttnArgs p) {
       for (int t = len + (int)r * NT + tid; t < T; t += CS * NT) p.d_prev_att[(long long)b * T + t] = 0.f;
     }
   }
+  B2_TRACE(p, 24);
   cluster_or_cta_sync(CS);            // #3: d_zq broadcast complete (and all df halo reads done)
+  B2_TRACE(p, 25);
 
   // ---- d_s = d_zq Wphi (slice of the decoder dimension per CTA) -----------------------------------
   if (p.d_s) {
     const int jper = (p.dec + CS - 1) / CS;
     const int j0 = (int)r * jper, j1 = min(p.dec, j0 + jper);
-    for (int j = j0 + tid; j < j1; j += NT) {
-      float acc;
-      if (p.Wphi) {
-        acc = 0.f;
-        for (int a = 0; a < A; ++a) acc = fmaf(dzq[a], __ldg(p.Wphi + (long long)a * p.dec + j), acc);
-      } else {
-        acc = dzq[j];
+    if (p.Wphi) {
+      // thread = (output j, quarter of the attention dimension): independent coalesced loads, batched by unrolling
+      const int nj = j1 - j0;
+      const int aq = (A + 3) / 4;
+      float* part = tmp;                                  // [4][nj], sized in attn_bwd_extra
+      for (int item = tid; item < nj * 4; item += NT) {
+        const int qd = item / nj, j = j0 + item - qd * nj;
+        const int a0 = qd * aq, a1 = min(A, a0 + aq);
+        float acc = 0.f;
+#pragma unroll 8
+        for (int a = a0; a < a1; ++a) acc = fmaf(dzq[a], __ldg(p.Wphi + (long long)a * p.dec + j), acc);
+        part[item] = acc;
       }
-      p.d_s[(long long)b * p.dec + j] = acc;
+      __syncthreads();
+      for (int j = tid; j < nj; j += NT) p.d_s[(long long)b * p.dec + j0 + j] = part[j] + part[nj + j] + part[2 * nj + j] + part[3 * nj + j];
+    } else {
+      for (int j = j0 + tid; j < j1; j += NT) p.d_s[(long long)b * p.dec + j] = dzq[j];
     }
   }
+  B2_TRACE(p, 26);
   if (CS > 1) cluster_sync_all();     // #4
+  B2_TRACE(p, 27);
 }
 
 int attn_configure(AttnArgs& a, int cluster_hint, size_t extra_floats, size_t* smem_out);
@@ -386,6 +448,7 @@ extern "C" int b2asr_attn_step_bwd(int mode, const float* Wphi, const float* key
   a.d_keys = d_keys; a.dk_bstride = dk_bstride; a.d_prev_att = d_prev_att; a.d_zq = d_zq; a.d_s = d_s;
   a.pgrad = pgrad; a.pgrad_stride = pgrad_stride;
   a.B = B; a.T = T; a.D = D; a.A = A; a.dec = dec;
+  a.trace = attn_trace_buffer();
   // first pass fixes CS/NT/tiles, second pass sizes the ring with the backward's extra arrays
   size_t smem = 0;
   int rc = attn_configure(a, cluster, 0, &smem);
@@ -408,5 +471,5 @@ extern "C" int b2asr_attn_step_bwd(int mode, const float* Wphi, const float* key
     L = attn_smem_layout(a, X2.total);
   }
   B2_REQUIRE(L.total <= 227 * 1024, B2ASR_EUNSUPPORTED, "attn_step_bwd: needs %zu bytes of shared memory (T=%d, cluster %d)", L.total, T, cs);
-  return attn_launch(attn_step_bwd_kernel, a, L.total, (cudaStream_t)stream);
+  return attn_launch(a.C <= 12 ? attn_step_bwd_kernel<12> : attn_step_bwd_kernel<16>, a, L.total, (cudaStream_t)stream);
 }

@@ -12,7 +12,9 @@
 
 namespace b2asr {
 
-__global__ void __launch_bounds__(512, 1) attn_step_fwd_kernel(AttnArgs p) {
+// CPT: location channels held in registers (12 or 16); MAXNT/MINB: launch bounds (two CTAs per SM when NT <= 320)
+template <int CPT, int MAXNT, int MINB>
+__global__ void __launch_bounds__(MAXNT, MINB) attn_step_fwd_kernel(AttnArgs p) {
   extern __shared__ __align__(128) unsigned char smraw[];
   const AttnSmem L = attn_smem_layout(p, 0);
   float* ring = reinterpret_cast<float*>(smraw + L.off_ring);
@@ -44,13 +46,12 @@ __global__ void __launch_bounds__(512, 1) attn_step_fwd_kernel(AttnArgs p) {
   const int nK = (nf + TFK - 1) / TFK, nH = (nf + TFH - 1) / TFH, ntiles = nK + nH;
   const unsigned stage_floats = p.stage_bytes / 4;
 
+  B2_TRACE(p, 0);
   if (tid == 0) {
     for (int s = 0; s < NS; ++s) mbar_init(&full[s], 1);
     mbar_fence_init();
   }
-  cluster_or_cta_sync(CS);            // #0: barriers initialised; every CTA of the cluster is running (DSMEM is legal)
-
-  auto issue = [&](int i) {          // thread 0 only
+  auto issue = [&](int i) {          // thread 0 only: key tiles first, then encoder-feature tiles
     if (i >= ntiles) return;
     const int s = i % NS;
     float* dst = ring + (size_t)s * stage_floats;
@@ -61,42 +62,12 @@ __global__ void __launch_bounds__(512, 1) attn_step_fwd_kernel(AttnArgs p) {
     bulk_g2s(dst, src, bytes, &full[s]);
   };
   if (tid == 0) for (int i = 0; i < NS; ++i) issue(i);
+  B2_TRACE(p, 1);
 
-  // ---- query: q = tanh(phi s), each CTA computes a slice and scatters it through DSMEM ----------
+  // ---- stage the small operands: every global load is issued before the one barrier that publishes them ----
+  const int KW1 = 2 * p.Kw + 1;
   for (int i = tid; i < p.dec; i += NT) s_sm[i] = p.s[(long long)b * p.s_stride + i];
-  __syncthreads();
-  if (p.Wphi) {
-    const int aper = (A + CS - 1) / CS;
-    const int a0 = (int)r * aper, a1 = min(A, a0 + aper);
-    const bool v4 = (p.dec % 4 == 0) && (((uintptr_t)p.Wphi & 15) == 0);
-    for (int a = a0 + warp; a < a1; a += nwarp) {
-      const float* w = p.Wphi + (long long)a * p.dec;
-      float acc = 0.f;
-      if (v4) {
-        for (int i = lane; i < p.dec / 4; i += 32) {
-          const float4 wv = __ldg(reinterpret_cast<const float4*>(w) + i);
-          const float4 sv = reinterpret_cast<const float4*>(s_sm)[i];
-          acc = fmaf(wv.x, sv.x, acc); acc = fmaf(wv.y, sv.y, acc); acc = fmaf(wv.z, sv.z, acc); acc = fmaf(wv.w, sv.w, acc);
-        }
-      } else {
-        for (int i = lane; i < p.dec; i += 32) acc = fmaf(__ldg(w + i), s_sm[i], acc);
-      }
-      acc = warp_sum(acc);
-      if (lane == 0) {
-        const float qv = tanh_acc(acc);
-        if (CS > 1) { for (int rr = 0; rr < CS; ++rr) st_dsmem_f32(dsmem_addr(q_sm + a, rr), qv); }
-        else q_sm[a] = qv;
-        if (p.q_out) p.q_out[(long long)b * A + a] = qv;
-      }
-    }
-  } else {
-    for (int a = tid; a < A; a += NT) q_sm[a] = s_sm[a];
-  }
-
-  // ---- location features f[t][c] = sum_k Wc[c][k] * prev_att[t+k-Kw] for my frames ---------------
   if (p.mode == 1) {
-    const int KW1 = 2 * p.Kw + 1;
-    for (int i = tid; i < KW1 * CP; i += NT) wcT[i] = 0.f;
     const int npa = nf + 2 * p.Kw;
     const float unif = len > 0 ? 1.f / (float)len : 0.f;
     for (int j = tid; j < npa; j += NT) {
@@ -105,13 +76,79 @@ __global__ void __launch_bounds__(512, 1) attn_step_fwd_kernel(AttnArgs p) {
       if (t >= 0 && t < T) v = p.prev_att ? p.prev_att[(long long)b * T + t] : (t < len ? unif : 0.f);
       pa[j] = v;
     }
-    __syncthreads();
-    for (int i = tid; i < C * KW1; i += NT) { const int c = i / KW1, k = i - c * KW1; wcT[k * CP + c] = __ldg(p.Wc + i); }
-    __syncthreads();
+#pragma unroll 8
+    for (int i = tid; i < C * KW1; i += NT) {            // transposed [tap][channel] so one float4 feeds 4 channels
+      const int c = i / KW1, k = i - c * KW1;
+      wcT[k * CP + c] = __ldg(p.Wc + i);
+    }
+    for (int i = tid; i < KW1 * (CP - C); i += NT) { const int k = i / (CP - C), c = C + i - k * (CP - C); wcT[k * CP + c] = 0.f; }
+  }
+  cluster_or_cta_sync(CS);            // #0: operands staged; every CTA of the cluster is running (DSMEM is legal)
+  B2_TRACE(p, 2);
+
+  // ---- query: q = tanh(phi s), each CTA computes a slice and scatters it through DSMEM ----------
+  if (p.Wphi) {
+    const int aper = (A + CS - 1) / CS;
+    const int a0 = (int)r * aper, a1 = min(A, a0 + aper);
+    const bool v32 = (p.dec % 32 == 0) && (((uintptr_t)p.Wphi & 15) == 0);
+    if (v32) {
+      // eight lanes per row, an eighth of the row each, all of its 128-bit loads in flight at once
+      const int q8 = p.dec / 32;                          // float4 per lane
+      for (int item0 = 0; item0 < (a1 - a0) * 8; item0 += NT) {
+        const int item = item0 + tid;
+        const int a = a0 + (item >> 3), qd = item & 7;
+        float acc = 0.f;
+        if (a < a1) {
+          const float4* w = reinterpret_cast<const float4*>(p.Wphi + (long long)a * p.dec) + qd * q8;
+          const float4* sv4 = reinterpret_cast<const float4*>(s_sm) + qd * q8;
+          for (int i0 = 0; i0 < q8; i0 += 5) {             // five 128-bit loads in flight per lane
+            float4 wv[5];
+#pragma unroll
+            for (int i = 0; i < 5; ++i) wv[i] = (i0 + i < q8) ? __ldg(w + i0 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int i = 0; i < 5; ++i) {
+              if (i0 + i < q8) {
+                const float4 sv = sv4[i0 + i];
+                acc = fmaf(wv[i].x, sv.x, acc); acc = fmaf(wv[i].y, sv.y, acc); acc = fmaf(wv[i].z, sv.z, acc); acc = fmaf(wv[i].w, sv.w, acc);
+              }
+            }
+          }
+        }
+        acc += __shfl_xor_sync(kFull, acc, 1);
+        acc += __shfl_xor_sync(kFull, acc, 2);
+        acc += __shfl_xor_sync(kFull, acc, 4);
+        if (a < a1 && qd == 0) {
+          const float qv = tanh_acc(acc);
+          if (CS > 1) { for (int rr = 0; rr < CS; ++rr) st_dsmem_f32(dsmem_addr(q_sm + a, rr), qv); }
+          else q_sm[a] = qv;
+          if (p.q_out) p.q_out[(long long)b * A + a] = qv;
+        }
+      }
+    } else {
+      for (int a = a0 + warp; a < a1; a += nwarp) {
+        const float* w = p.Wphi + (long long)a * p.dec;
+        float acc = 0.f;
+        for (int i = lane; i < p.dec; i += 32) acc = fmaf(__ldg(w + i), s_sm[i], acc);
+        acc = warp_sum(acc);
+        if (lane == 0) {
+          const float qv = tanh_acc(acc);
+          if (CS > 1) { for (int rr = 0; rr < CS; ++rr) st_dsmem_f32(dsmem_addr(q_sm + a, rr), qv); }
+          else q_sm[a] = qv;
+          if (p.q_out) p.q_out[(long long)b * A + a] = qv;
+        }
+      }
+    }
+  } else {
+    for (int a = tid; a < A; a += NT) q_sm[a] = s_sm[a];
+  }
+
+  // ---- location features f[t][c] = sum_k Wc[c][k] * prev_att[t+k-Kw] for my frames ---------------
+  if (p.mode == 1) {
     const float4* w4 = reinterpret_cast<const float4*>(wcT);
     for (int item = tid; item < nf * CQ; item += NT) {
       const int cg = item / nf, fl = item - cg * nf;
       float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
       for (int k = 0; k < KW1; ++k) {
         const float pv = pa[fl + k];
         const float4 w = w4[k * CQ + cg];
@@ -120,43 +157,67 @@ __global__ void __launch_bounds__(512, 1) attn_step_fwd_kernel(AttnArgs p) {
       reinterpret_cast<float4*>(fsm)[fl * CQ + cg] = acc;
     }
   }
+  B2_TRACE(p, 3);
   cluster_or_cta_sync(CS);            // #1: q and f visible
+  B2_TRACE(p, 4);
 
-  // ---- energies: thread a owns attention dimension a, frames stream through the ring --------
   const bool active = tid < A;
-  float wl[kAttMaxC];
+  float wl[CPT];
 #pragma unroll
-  for (int c = 0; c < kAttMaxC; ++c) wl[c] = (active && p.mode == 1 && c < C) ? __ldg(p.Wl + (long long)tid * C + c) : 0.f;
+  for (int c = 0; c < CPT; ++c) wl[c] = (active && p.mode == 1 && c < C) ? __ldg(p.Wl + (long long)tid * C + c) : 0.f;
   const float qa = active ? q_sm[tid] : 0.f;
   const float wga = (active && p.mode == 1) ? __ldg(p.wg + tid) : 0.f;
   const float bgv = p.mode == 1 ? __ldg(p.bg) : 0.f;
+  const int kcol = active ? tid : 0;
+  // ---- energies: thread a owns attention dimension a, frames stream through the ring --------
+  // Four frames per iteration: four independent tanh chains per thread, and the four per-frame sums over the
+  // warp's 32 dimensions cost 6 shuffles together (transposing butterfly) instead of 5 each.
   for (int i = 0; i < nK; ++i) {
     const int s = i % NS;
     mbar_wait(&full[s], (unsigned)((i / NS) & 1));
     const float* kt = ring + (size_t)s * stage_floats;
     const int f0 = i * TFK, n = min(TFK, nf - f0);
-    for (int j = 0; j < n; ++j) {
-      float part = 0.f;
-      if (active) {
-        const float kv = kt[j * A + tid];
+    for (int j = 0; j < n; j += 4) {
+      float part[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int jj = min(j + u, n - 1);              // tail: recompute the last frame, the result is dropped
+        const float kv = kt[jj * A + kcol];
         if (p.mode == 1) {
-          const float4* f4 = reinterpret_cast<const float4*>(fsm) + (size_t)(f0 + j) * CQ;
+          const float4* f4 = reinterpret_cast<const float4*>(fsm) + (size_t)(f0 + jj) * CQ;
           float zl = 0.f;
 #pragma unroll
-          for (int c4 = 0; c4 < kAttMaxC / 4; ++c4) {
+          for (int c4 = 0; c4 < CPT / 4; ++c4) {
             if (c4 < CQ) {
               const float4 fv = f4[c4];
               zl = fmaf(wl[4 * c4 + 0], fv.x, zl); zl = fmaf(wl[4 * c4 + 1], fv.y, zl);
               zl = fmaf(wl[4 * c4 + 2], fv.z, zl); zl = fmaf(wl[4 * c4 + 3], fv.w, zl);
             }
           }
-          part = wga * tanh_acc(kv + qa + tanh_acc(zl));
+          part[u] = wga * tanh_fast(kv + qa + tanh_fast(zl));
         } else {
-          part = kv * qa;
+          part[u] = active ? kv * qa : 0.f;
         }
       }
-      part = warp_sum(part);
-      if (lane == 0) epart[warp * tfmax + j] = part;
+      {
+        const bool up = lane & 16;
+        const float s0 = up ? part[0] : part[2], s1 = up ? part[1] : part[3];
+        const float k0 = up ? part[2] : part[0], k1 = up ? part[3] : part[1];
+        part[0] = k0 + __shfl_xor_sync(kFull, s0, 16);
+        part[1] = k1 + __shfl_xor_sync(kFull, s1, 16);
+      }
+      {
+        const bool up = lane & 8;
+        const float s0 = up ? part[0] : part[1], k0 = up ? part[1] : part[0];
+        part[0] = k0 + __shfl_xor_sync(kFull, s0, 8);
+      }
+      part[0] += __shfl_xor_sync(kFull, part[0], 4);
+      part[0] += __shfl_xor_sync(kFull, part[0], 2);
+      part[0] += __shfl_xor_sync(kFull, part[0], 1);
+      if ((lane & 7) == 0) {
+        const int u = ((lane >> 4) & 1) * 2 + ((lane >> 3) & 1);
+        if (j + u < n) epart[warp * tfmax + j + u] = part[0];
+      }
     }
     __syncthreads();
     for (int j = tid; j < n; j += NT) {
@@ -168,6 +229,7 @@ __global__ void __launch_bounds__(512, 1) attn_step_fwd_kernel(AttnArgs p) {
     if (tid == 0) { fence_proxy_async_smem(); issue(i + NS); }
   }
 
+  B2_TRACE(p, 5);
   // ---- masked softmax over the utterance: local statistics, then one exchange -----------------
   float m = -INFINITY;
   for (int j = tid; j < nf; j += NT) m = fmaxf(m, e[j]);
@@ -195,6 +257,7 @@ __global__ void __launch_bounds__(512, 1) attn_step_fwd_kernel(AttnArgs p) {
   for (int t = len + (int)r * NT + tid; t < T; t += CS * NT) p.att[(long long)b * T + t] = 0.f;
   __syncthreads();
 
+  B2_TRACE(p, 6);
   // ---- context: ctx = sum_t alpha_t h_t over my frames, then a DSMEM slice reduction ----------
   const int ngroups = D / 4, items = ngroups * p.FS;
   float4 acc[kAttMaxIPT];
@@ -232,7 +295,9 @@ __global__ void __launch_bounds__(512, 1) attn_step_fwd_kernel(AttnArgs p) {
     for (int fs = 0; fs < p.FS; ++fs) v += ctxp[(size_t)fs * D + d];
     ctxp[d] = v;
   }
+  B2_TRACE(p, 7);
   cluster_or_cta_sync(CS);            // #3: partial contexts visible cluster-wide
+  B2_TRACE(p, 8);
   {
     const int dper = (D + CS - 1) / CS;
     const int d0 = (int)r * dper, d1 = min(D, d0 + dper);
@@ -244,7 +309,9 @@ __global__ void __launch_bounds__(512, 1) attn_step_fwd_kernel(AttnArgs p) {
     }
   }
   if (CS > 1) cluster_sync_all();     // #4: nobody leaves while its shared memory is still being read
+  B2_TRACE(p, 9);
 }
+
 
 // ---------------------------------------------------------------------------------------------
 int attn_configure(AttnArgs& a, int cluster_hint, size_t extra_floats, size_t* smem_out) {
@@ -254,6 +321,7 @@ int attn_configure(AttnArgs& a, int cluster_hint, size_t extra_floats, size_t* s
              "attn: location conv C=%d Kw=%d unsupported", a.C, a.Kw);
   if (a.mode == 0) { a.C = 4; a.Kw = 0; }
   int CS = cluster_hint;
+  { const char* e = getenv("B2ASR_ATT_CS"); if (CS <= 0 && e && *e) CS = atoi(e); }
   if (CS <= 0) {
     CS = 1;
     while (CS < kAttMaxCluster && a.B * CS * 2 <= 148 && (a.T + CS * 2 - 1) / (CS * 2) >= 16) CS *= 2;
@@ -263,6 +331,7 @@ int attn_configure(AttnArgs& a, int cluster_hint, size_t extra_floats, size_t* s
   a.NT = (int)align_up((size_t)(a.A > 128 ? a.A : 128), 32);
   a.chunk_max = (a.T + CS - 1) / CS;
   a.stage_bytes = 40960u;
+  { const char* e = getenv("B2ASR_ATT_STAGE"); if (e && *e) a.stage_bytes = (unsigned)atoi(e); }
   const unsigned rowK = (unsigned)a.A * 4u, rowH = (unsigned)a.D * 4u;
   const unsigned rowmax = rowK > rowH ? rowK : rowH;
   if (rowmax * 4u > a.stage_bytes) a.stage_bytes = (unsigned)align_up((size_t)rowmax * 4u, 128);
@@ -272,11 +341,24 @@ int attn_configure(AttnArgs& a, int cluster_hint, size_t extra_floats, size_t* s
   a.IPT = ((a.D / 4) * a.FS + a.NT - 1) / a.NT;
   B2_REQUIRE(a.IPT <= kAttMaxIPT, B2ASR_EUNSUPPORTED, "attn: encoder dim %d too wide", a.D);
   a.NS = 4;
+  { const char* e = getenv("B2ASR_ATT_NS"); if (e && *e) a.NS = atoi(e); }
   AttnSmem L = attn_smem_layout(a, extra_floats);
   while (L.total > 227 * 1024 && a.NS > 2) { a.NS--; L = attn_smem_layout(a, extra_floats); }
   B2_REQUIRE(L.total <= 227 * 1024, B2ASR_EUNSUPPORTED, "attn: needs %zu bytes of shared memory (T=%d too long for cluster %d)", L.total, a.T, CS);
   *smem_out = L.total;
   return B2ASR_OK;
+}
+
+__device__ long long g_attn_trace[32];
+long long* attn_trace_buffer() {
+  static long long* buf = nullptr;
+  static int init = 0;
+  if (!init) {
+    init = 1;
+    const char* e = getenv("B2ASR_ATT_TRACE");
+    if (e && *e && *e != '0') { void* q = nullptr; if (cudaGetSymbolAddress(&q, g_attn_trace) == cudaSuccess) buf = (long long*)q; }
+  }
+  return buf;
 }
 
 int attn_launch(void (*kern)(AttnArgs), const AttnArgs& a, size_t smem, cudaStream_t st) {
@@ -316,8 +398,21 @@ extern "C" int b2asr_attn_step_fwd(int mode, const float* s, int64_t s_stride, c
   a.h = h; a.h_bstride = h_bstride; a.lens = lens; a.prev_att = prev_att; a.Wc = Wc; a.C = C; a.Kw = Kw;
   a.Wl = Wl; a.wg = wg; a.bg = bg; a.scale = scale; a.att = att; a.ctx = ctx; a.q_out = q_out;
   a.B = B; a.T = T; a.D = D; a.A = A; a.dec = dec;
+  a.trace = attn_trace_buffer();
   size_t smem = 0;
   int rc = attn_configure(a, cluster, 0, &smem);
   if (rc != B2ASR_OK) return rc;
-  return attn_launch(attn_step_fwd_kernel, a, smem, (cudaStream_t)stream);
+  void (*kern)(AttnArgs);
+  const bool small = a.NT <= 320;
+  if (a.C <= 12) kern = small ? attn_step_fwd_kernel<12, 320, 2> : attn_step_fwd_kernel<12, 512, 1>;
+  else kern = small ? attn_step_fwd_kernel<16, 320, 2> : attn_step_fwd_kernel<16, 512, 1>;
+  return attn_launch(kern, a, smem, (cudaStream_t)stream);
+}
+
+// debug aid: copy the phase stamps of the last traced launch (B2ASR_ATT_TRACE=1) to the host
+extern "C" int b2asr_debug_attn_trace(long long* host_out, int n) {
+  long long* buf = attn_trace_buffer();
+  B2_REQUIRE(buf && host_out && n > 0 && n <= 32, B2ASR_EINVAL, "attn trace: not enabled (set B2ASR_ATT_TRACE=1) or bad arguments");
+  B2_CUDA_TRY(cudaMemcpy(host_out, buf, sizeof(long long) * n, cudaMemcpyDeviceToHost));
+  return B2ASR_OK;
 }

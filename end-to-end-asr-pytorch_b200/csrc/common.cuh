@@ -81,6 +81,11 @@ __device__ __forceinline__ unsigned dsmem_addr(const void* local_smem, unsigned 
 __device__ __forceinline__ float ld_dsmem_f32(unsigned addr) {
   float v; asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory"); return v;
 }
+__device__ __forceinline__ float4 ld_dsmem_f32x4(unsigned addr) {
+  float4 v;
+  asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
+}
 __device__ __forceinline__ void st_dsmem_f32(unsigned addr, float v) {
   asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
 }
@@ -127,6 +132,12 @@ __device__ __forceinline__ void red_add_f32(float* gaddr, float v) {
 __device__ __forceinline__ float tanh_acc(float x) {
   const float xc = fminf(fmaxf(x, -15.f), 15.f);
   const float e = ex2(xc * (2.f * kLog2e));
+  return 1.f - __fdividef(2.f, 1.f + e);
+}
+
+// same formula without the range clamps: e = inf gives 1 - 2/inf = 1, e = 0 gives -1; never NaN for finite x
+__device__ __forceinline__ float tanh_fast(float x) {
+  const float e = ex2(x * (2.f * kLog2e));
   return 1.f - __fdividef(2.f, 1.f + e);
 }
 

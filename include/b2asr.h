@@ -211,6 +211,11 @@ typedef struct b2asr_beam_io {
 size_t b2asr_beam_io_size(void);   /* sizeof(b2asr_beam_io), for binding sanity checks */
 int    b2asr_beam_step(const b2asr_beam_io* io, void* stream);
 
+/* Debug aid, not part of the drop-in path: with B2ASR_ATT_TRACE=1 in the environment CTA 0 of every attention
+ * launch stamps clock64() at its phase boundaries (forward: slots 0-9, backward: 16-27); this copies the first n
+ * slots of the last launch to the host (synchronous). */
+int    b2asr_debug_attn_trace(long long* host_out, int n);
+
 #ifdef __cplusplus
 }
 #endif
