@@ -63,8 +63,8 @@ __device__ __forceinline__ float warp_reduce16(float (&v)[16], int lane, int& id
   return v[0];
 }
 
-template <int CPT>
-__global__ void __launch_bounds__(512, 1) attn_step_bwd_kernel(AttnArgs p) {
+template <int CPT, int MAXNT, int MINB>
+__global__ void __launch_bounds__(MAXNT, MINB) attn_step_bwd_kernel(AttnArgs p) {
   extern __shared__ __align__(128) unsigned char smraw[];
   const BwdExtra X = attn_bwd_extra(p);
   const AttnSmem L = attn_smem_layout(p, X.total);
@@ -117,26 +117,27 @@ __global__ void __launch_bounds__(512, 1) attn_step_bwd_kernel(AttnArgs p) {
   if (tid == 0) for (int i = 0; i < NS; ++i) issue(i);
   B2_TRACE(p, 17);
 
-  // ---- stage small operands (every global load issued before the one barrier that publishes them) ----------
-  for (int a = tid; a < A; a += NT) q_sm[a] = p.q_saved[(long long)b * A + a];
-  for (int d = tid; d < D; d += NT) dctx[d] = p.d_ctx[(long long)b * D + d];
-  for (int j = tid; j < nf; j += NT) al[j] = p.att_saved[(long long)b * T + t0 + j];
+  // ---- stage small operands: asynchronous 4-byte copies, all in flight at once, one wait ------------------
+  for (int a = tid; a < A; a += NT) cp_async4(q_sm + a, p.q_saved + (long long)b * A + a);
+  for (int d = tid; d < D; d += NT) cp_async4(dctx + d, p.d_ctx + (long long)b * D + d);
+  for (int j = tid; j < nf; j += NT) {
+    cp_async4(al + j, p.att_saved + (long long)b * T + t0 + j);
+    if (p.d_att) cp_async4(de + j, p.d_att + (long long)b * T + t0 + j); else de[j] = 0.f;
+  }
   if (loc) {
     const int npa = nf + 2 * p.Kw;
     const float unif = len > 0 ? 1.f / (float)len : 0.f;
     for (int j = tid; j < npa; j += NT) {
       const int t = t0 - p.Kw + j;
-      float v = 0.f;
-      if (t >= 0 && t < T) v = p.prev_att ? p.prev_att[(long long)b * T + t] : (t < len ? unif : 0.f);
-      pa[j] = v;
+      if (t >= 0 && t < T && p.prev_att) cp_async4(pa + j, p.prev_att + (long long)b * T + t);
+      else pa[j] = (t >= 0 && t < len) ? unif : 0.f;
     }
-#pragma unroll 8
-    for (int i = tid; i < C * KW1; i += NT) { const int c = i / KW1, k = i - c * KW1; wcT[k * CP + c] = __ldg(p.Wc + i); }
+    for (int i = tid; i < C * KW1; i += NT) { const int c = i / KW1, k = i - c * KW1; cp_async4(wcT + k * CP + c, p.Wc + i); }
     for (int i = tid; i < KW1 * (CP - C); i += NT) { const int k = i / (CP - C), c = C + i - k * (CP - C); wcT[k * CP + c] = 0.f; }
-#pragma unroll 4
-    for (int i = tid; i < A * C; i += NT) { const int a = i / C, c = i - a * C; wls[a * CP + c] = __ldg(p.Wl + i); }
+    for (int i = tid; i < A * C; i += NT) { const int a = i / C, c = i - a * C; cp_async4(wls + a * CP + c, p.Wl + i); }
     for (int i = tid; i < A * (CP - C); i += NT) { const int a = i / (CP - C), c = C + i - a * (CP - C); wls[a * CP + c] = 0.f; }
   }
+  cp_async_wait_all();
   cluster_or_cta_sync(CS);            // #0: operands staged; every CTA of the cluster is running (DSMEM is legal)
 
   // ---- recompute the location features of my frames ------------------------------------------------
@@ -172,7 +173,7 @@ __global__ void __launch_bounds__(512, 1) attn_step_bwd_kernel(AttnArgs p) {
         acc = fmaf(hv.x, dv.x, acc); acc = fmaf(hv.y, dv.y, acc); acc = fmaf(hv.z, dv.z, acc); acc = fmaf(hv.w, dv.w, acc);
       }
       acc = warp_sum(acc);
-      if (lane == 0) de[f0 + j] = acc + (p.d_att ? p.d_att[(long long)b * T + t0 + f0 + j] : 0.f);
+      if (lane == 0) de[f0 + j] += acc;              // de[] was staged with the external d_att (or 0)
     }
     __syncthreads();
     if (tid == 0) { fence_proxy_async_smem(); issue(i + NS); }
@@ -214,9 +215,10 @@ __global__ void __launch_bounds__(512, 1) attn_step_bwd_kernel(AttnArgs p) {
     mbar_wait(&full[s], (unsigned)((ti / NS) & 1));
     float* kt = ring + (size_t)s * stage_floats;
     const int f0 = i * TFK, n = min(TFK, nf - f0);
-    for (int j = 0; j < n; j += 2) {
+    constexpr int UNR = MINB > 1 ? 2 : 4;
+    for (int j = 0; j < n; j += UNR) {
 #pragma unroll
-      for (int u = 0; u < 2; ++u) {
+      for (int u = 0; u < UNR; ++u) {
         const int jj = j + u;
         if (jj < n) {                                     // uniform
           const float kv = kt[jj * A + kcol];
@@ -231,10 +233,10 @@ __global__ void __launch_bounds__(512, 1) attn_step_bwd_kernel(AttnArgs p) {
               if (c4 < CQ) t4 = f4[c4];
               fv[4 * c4 + 0] = t4.x; fv[4 * c4 + 1] = t4.y; fv[4 * c4 + 2] = t4.z; fv[4 * c4 + 3] = t4.w;
             }
-            float zl = 0.f;
+            float zl0 = 0.f, zl1 = 0.f;                     // two half-length dependency chains
 #pragma unroll
-            for (int c = 0; c < CPT; ++c) zl = fmaf(wl[c], fv[c], zl);
-            const float l = tanh_fast(zl);
+            for (int c = 0; c < CPT; c += 2) { zl0 = fmaf(wl[c], fv[c], zl0); zl1 = fmaf(wl[c + 1], fv[c + 1], zl1); }
+            const float l = tanh_fast(zl0 + zl1);
             const float uu = tanh_fast(kv + qa + l);
             dwg_acc = fmaf(dev, uu, dwg_acc);
             dpre = dev * wga * (1.f - uu * uu);
@@ -457,10 +459,12 @@ extern "C" int b2asr_attn_step_bwd(int mode, const float* Wphi, const float* key
   if (a.TFK > 32) a.TFK = 32;
   const BwdExtra X = attn_bwd_extra(a);
   a.NS = 4;
+  size_t cap = 227 * 1024;
+  { const char* e = getenv("B2ASR_ATT_CAP_KB"); if (e && *e) cap = (size_t)atoi(e) * 1024; }
   AttnSmem L = attn_smem_layout(a, X.total);
-  while (L.total > 227 * 1024 && a.NS > 2) { a.NS--; L = attn_smem_layout(a, X.total); }
+  while (L.total > cap && a.NS > 2) { a.NS--; L = attn_smem_layout(a, X.total); }
   BwdExtra X2 = X;
-  while (L.total > 227 * 1024 && a.TFK > 2 && a.TFH > 1) {     // long slices: shrink the ring tiles
+  while (L.total > cap && a.TFK > 2 && a.TFH > 1) {     // long slices: shrink the ring tiles
     a.stage_bytes = (unsigned)align_up((size_t)a.stage_bytes / 2, 128);
     const unsigned rk = (unsigned)A * 4u, rh = (unsigned)D * 4u;
     a.TFK = (int)(a.stage_bytes / rk); if (a.TFK > 32) a.TFK = 32; if (a.TFK < 1) a.TFK = 1;
@@ -471,5 +475,9 @@ extern "C" int b2asr_attn_step_bwd(int mode, const float* Wphi, const float* key
     L = attn_smem_layout(a, X2.total);
   }
   B2_REQUIRE(L.total <= 227 * 1024, B2ASR_EUNSUPPORTED, "attn_step_bwd: needs %zu bytes of shared memory (T=%d, cluster %d)", L.total, T, cs);
-  return attn_launch(a.C <= 12 ? attn_step_bwd_kernel<12> : attn_step_bwd_kernel<16>, a, L.total, (cudaStream_t)stream);
+  const bool two = a.NT <= 320 && L.total <= 113 * 1024;      // two CTAs per SM fit: compile for <= 102 registers
+  void (*kern)(AttnArgs);
+  if (a.C <= 12) kern = two ? attn_step_bwd_kernel<12, 320, 2> : attn_step_bwd_kernel<12, 512, 1>;
+  else kern = two ? attn_step_bwd_kernel<16, 320, 2> : attn_step_bwd_kernel<16, 512, 1>;
+  return attn_launch(kern, a, L.total, (cudaStream_t)stream);
 }

@@ -64,25 +64,24 @@ __global__ void __launch_bounds__(MAXNT, MINB) attn_step_fwd_kernel(AttnArgs p) 
   if (tid == 0) for (int i = 0; i < NS; ++i) issue(i);
   B2_TRACE(p, 1);
 
-  // ---- stage the small operands: every global load is issued before the one barrier that publishes them ----
+  // ---- stage the small operands: asynchronous 4-byte copies, all in flight at once, one wait ---------------
   const int KW1 = 2 * p.Kw + 1;
-  for (int i = tid; i < p.dec; i += NT) s_sm[i] = p.s[(long long)b * p.s_stride + i];
+  for (int i = tid; i < p.dec; i += NT) cp_async4(s_sm + i, p.s + (long long)b * p.s_stride + i);
   if (p.mode == 1) {
     const int npa = nf + 2 * p.Kw;
     const float unif = len > 0 ? 1.f / (float)len : 0.f;
     for (int j = tid; j < npa; j += NT) {
       const int t = t0 - p.Kw + j;
-      float v = 0.f;
-      if (t >= 0 && t < T) v = p.prev_att ? p.prev_att[(long long)b * T + t] : (t < len ? unif : 0.f);
-      pa[j] = v;
+      if (t >= 0 && t < T && p.prev_att) cp_async4(pa + j, p.prev_att + (long long)b * T + t);
+      else pa[j] = (t >= 0 && t < len) ? unif : 0.f;
     }
-#pragma unroll 8
     for (int i = tid; i < C * KW1; i += NT) {            // transposed [tap][channel] so one float4 feeds 4 channels
       const int c = i / KW1, k = i - c * KW1;
-      wcT[k * CP + c] = __ldg(p.Wc + i);
+      cp_async4(wcT + k * CP + c, p.Wc + i);
     }
     for (int i = tid; i < KW1 * (CP - C); i += NT) { const int k = i / (CP - C), c = C + i - k * (CP - C); wcT[k * CP + c] = 0.f; }
   }
+  cp_async_wait_all();
   cluster_or_cta_sync(CS);            // #0: operands staged; every CTA of the cluster is running (DSMEM is legal)
   B2_TRACE(p, 2);
 
@@ -185,16 +184,16 @@ __global__ void __launch_bounds__(MAXNT, MINB) attn_step_fwd_kernel(AttnArgs p) 
         const float kv = kt[jj * A + kcol];
         if (p.mode == 1) {
           const float4* f4 = reinterpret_cast<const float4*>(fsm) + (size_t)(f0 + jj) * CQ;
-          float zl = 0.f;
+          float zl0 = 0.f, zl1 = 0.f;                    // two half-length dependency chains
 #pragma unroll
           for (int c4 = 0; c4 < CPT / 4; ++c4) {
             if (c4 < CQ) {
               const float4 fv = f4[c4];
-              zl = fmaf(wl[4 * c4 + 0], fv.x, zl); zl = fmaf(wl[4 * c4 + 1], fv.y, zl);
-              zl = fmaf(wl[4 * c4 + 2], fv.z, zl); zl = fmaf(wl[4 * c4 + 3], fv.w, zl);
+              zl0 = fmaf(wl[4 * c4 + 0], fv.x, zl0); zl1 = fmaf(wl[4 * c4 + 1], fv.y, zl1);
+              zl0 = fmaf(wl[4 * c4 + 2], fv.z, zl0); zl1 = fmaf(wl[4 * c4 + 3], fv.w, zl1);
             }
           }
-          part[u] = wga * tanh_fast(kv + qa + tanh_fast(zl));
+          part[u] = wga * tanh_fast(kv + qa + tanh_fast(zl0 + zl1));
         } else {
           part[u] = active ? kv * qa : 0.f;
         }
@@ -343,7 +342,9 @@ int attn_configure(AttnArgs& a, int cluster_hint, size_t extra_floats, size_t* s
   a.NS = 4;
   { const char* e = getenv("B2ASR_ATT_NS"); if (e && *e) a.NS = atoi(e); }
   AttnSmem L = attn_smem_layout(a, extra_floats);
-  while (L.total > 227 * 1024 && a.NS > 2) { a.NS--; L = attn_smem_layout(a, extra_floats); }
+  size_t cap = 227 * 1024;
+  { const char* e = getenv("B2ASR_ATT_CAP_KB"); if (e && *e) cap = (size_t)atoi(e) * 1024; }
+  while (L.total > cap && a.NS > 2) { a.NS--; L = attn_smem_layout(a, extra_floats); }
   B2_REQUIRE(L.total <= 227 * 1024, B2ASR_EUNSUPPORTED, "attn: needs %zu bytes of shared memory (T=%d too long for cluster %d)", L.total, a.T, CS);
   *smem_out = L.total;
   return B2ASR_OK;

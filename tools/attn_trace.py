@@ -27,7 +27,9 @@ for _ in range(3):
 torch.cuda.synchronize()
 buf = (ctypes.c_longlong * 32)()
 rc = lib.lib().b2asr_debug_attn_trace(buf, 32)
-assert rc == 0, lib.lib().b2asr_last_error()
+if rc != 0:
+    print("trace disabled:", lib.lib().b2asr_last_error().decode())
+    sys.exit(0)
 mhz = torch.cuda.clock_rate() if hasattr(torch.cuda, "clock_rate") else 1900
 names_f = ["", "init+issue", "stage+sync0", "query+conv", "sync1", "energy", "softmax", "context", "sync3", "dsmem reduce+sync4"]
 names_b = ["init+issue", "stage+sync0+conv", "d_alpha", "softmax bwd", "key pass", "pgrad+sync2", "dq", "loc branch", "sync3", "d_s", "sync4"]

@@ -1,0 +1,46 @@
+"""Is the train step GPU-bound or launch-bound?  Sum of kernel durations (torch.profiler, warm, concurrent-capable)
+against the step's wall clock, split by kernel family."""
+import importlib, os, sys, time
+import torch
+from torch.profiler import profile, ProfilerActivity
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+PKG = "end-to-end-asr-pytorch_b200"
+asr, solver, syn = (importlib.import_module(PKG + "." + m) for m in ("asr", "solver", "synthetic"))
+name = os.environ.get("B2ASR_WORKLOAD", "libri_m2")
+w = syn.WORKLOADS[name]
+dev = torch.device("cuda:0")
+torch.manual_seed(0)
+model = asr.Seq2Seq(torch.zeros(1, 8, w["d_in"]), w["vocab"], w["cfg"]).to(dev).train()
+opt = solver.make_optimizer(model, w["cfg"]["optimizer"])
+ts = solver.TrainStep(model, opt, w["cfg"]["optimizer"]["joint_ctc"])
+x, y, _ = syn.make_batch(name, 1234)
+x, y = x.to(dev), y.to(dev)
+for _ in range(3):
+    ts.step(x, y, 1.0)
+torch.cuda.synchronize()
+t0 = time.perf_counter()
+for _ in range(3):
+    ts.step(x, y, 1.0)
+torch.cuda.synchronize()
+print("plain step %.1f ms" % ((time.perf_counter() - t0) / 3 * 1e3))
+with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
+    t0 = time.perf_counter()
+    ts.step(x, y, 1.0)
+    torch.cuda.synchronize()
+    wall = time.perf_counter() - t0
+ev = [e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA]
+tot = sum(e.device_time for e in ev)
+print("profiled step wall %.1f ms; %d GPU kernels/memcpys, summed GPU time %.1f ms" % (wall * 1e3, len(ev), tot / 1e3))
+fam = {}
+for e in ev:
+    n = e.name
+    k = ("b2asr" if "b2asr" in n else "cudnn-rnn" if ("RNN" in n or "LSTM_elem" in n or "elemWise" in n) else
+         "gemm" if ("gemm" in n or "cutlass" in n or "splitK" in n) else "other")
+    a = fam.setdefault(k, [0, 0.0]); a[0] += 1; a[1] += e.device_time
+for k, (c, t) in sorted(fam.items(), key=lambda kv: -kv[1][1]):
+    print("  %-10s %6d launches %8.1f ms" % (k, c, t / 1e3))
+# time span of GPU activity vs summed: gaps = idle
+ev.sort(key=lambda e: e.time_range.start)
+span = ev[-1].time_range.end - ev[0].time_range.start
+print("GPU activity span %.1f ms -> idle inside the span %.1f ms" % (span / 1e3, (span - tot) / 1e3))
