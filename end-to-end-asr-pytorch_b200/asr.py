@@ -26,7 +26,7 @@ import torch.nn.functional as F
 from torch.distributions.categorical import Categorical
 from torch.nn.utils.rnn import pack_padded_sequence, pad_packed_sequence
 
-from . import _attn
+from . import _attn, _dec
 
 CTC_BEAM_RATIO = 1.5   # asr.py:15
 
@@ -216,6 +216,7 @@ class _AttnOpen(torch.autograd.Function):
     @staticmethod
     def forward(ctx, session, keys, h, phi, conv, lproj, gen_w, gen_b):
         ctx.session = session
+        ctx.set_materialize_grads(False)
         return torch.zeros(1, dtype=torch.float32, device=keys.device)
 
     @staticmethod
@@ -275,7 +276,7 @@ class _AttnStep(torch.autograd.Function):
         ses.dctxs.append(d_ctx)
         ses.dzqs.append(d_zq)
         ses.states.append(s)
-        return None, torch.zeros(1, dtype=torch.float32, device=att.device), d_s, d_prev
+        return None, None, d_s, d_prev      # the token only orders _AttnOpen.backward after every step
 
 
 class Attention(nn.Module):
@@ -436,6 +437,9 @@ class Seq2Seq(nn.Module):
                 teacher = self.embed(teacher)
             self.decoder.init_rnn(encode_feature)
             self.attention.reset_enc_mem()
+            if _dec.supported(self.decoder) and encode_feature.is_cuda:
+                att_output, att_maps = self._decode_loop_fused(encode_feature, encode_len, decode_step, tf_rate, teacher)
+                return ctc_output, encode_len, att_output, att_maps
             last_char = self.embed(torch.zeros(bs, dtype=torch.long, device=encode_feature.device))
             chars, maps = [], []
             for t in range(decode_step):
@@ -456,6 +460,55 @@ class Seq2Seq(nn.Module):
             # the device and is copied only if somebody asks (draw_att does .cpu() itself)
             att_maps = [torch.stack(maps, dim=1)]
         return ctc_output, encode_len, att_output, att_maps
+
+    def _decode_loop_fused(self, encode_feature, encode_len, decode_step, tf_rate, teacher):
+        """The decoder loop of forward() (asr.py:84-108) for a single-layer LSTMCell Speller, regrouped as
+        _dec.py describes: batched embedding projection before the loop, 3 launches per step around the
+        attention kernel, batched char_trans and weight gradients after it.  Same arithmetic, same coins."""
+        bs = encode_feature.shape[0]
+        dev = encode_feature.device
+        cell = self.decoder.layer0
+        emb_dim = self.embed.embedding_dim
+        w_emb = cell.weight_ih[:, :emb_dim]
+        sos = self.embed(torch.zeros(bs, dtype=torch.long, device=dev))
+        need_grad = torch.is_grad_enabled() and (encode_feature.requires_grad or cell.weight_ih.requires_grad)
+        E = None
+        if teacher is not None:
+            x_emb = torch.cat([sos.unsqueeze(1), teacher[:, 1:decode_step, :]], dim=1) if decode_step > 1 else sos.unsqueeze(1)
+            E = F.linear(x_emb, w_emb)                                  # [B, L, 4H]: every teacher-forced step at once
+        h, c = self.decoder.state_list[0], self.decoder.cell_list[0]
+        if need_grad:
+            ses = _dec.DecSession(cell, E, emb_dim, decode_step)
+            token = _dec.DecOpen.apply(ses, E, cell.weight_ih, cell.weight_hh, cell.bias_ih, cell.bias_hh)
+        outs, chars, maps = [], [None] * decode_step, []
+        own = None if teacher is not None else F.linear(sos, w_emb)     # embedding projection this step must use
+        for t in range(decode_step):
+            score, context = self.attention(h, encode_feature, encode_len)
+            if need_grad:
+                h, c = _dec.DecStep.apply(ses, token, t, own, context, h, c)
+            else:
+                h, c = _dec.step_nograd(cell, emb_dim, own if own is not None else E[:, t], context, h, c)
+            self.decoder.state_list[0], self.decoder.cell_list[0] = h, c
+            outs.append(h)
+            own = None
+            if teacher is not None:
+                if not (random.random() <= tf_rate):                   # one coin per step (asr.py:96)
+                    chars[t] = self.char_trans(h)
+                    own = F.linear(self.embed(Categorical(F.softmax(chars[t], dim=-1)).sample()), w_emb)
+            else:
+                chars[t] = self.char_trans(h)
+                own = F.linear(self.embed(torch.argmax(chars[t], dim=-1)), w_emb)
+            maps.append(score[0].detach())
+        todo = [t for t in range(decode_step) if chars[t] is None]
+        if len(todo) == decode_step:
+            att_output = self.char_trans(torch.stack(outs, dim=1))      # one GEMM for every step
+        else:
+            if todo:
+                late = self.char_trans(torch.stack([outs[t] for t in todo], dim=1)).unbind(1)
+                for t, v in zip(todo, late):
+                    chars[t] = v
+            att_output = torch.stack(chars, dim=1)
+        return att_output, [torch.stack(maps, dim=1)]
 
     def beam_decode(self, audio_feature, decode_step, state_len, decode_beam_size):
         """Joint CTC/attention/RNN-LM beam search, device-resident (asr.py:155-258); returns the top

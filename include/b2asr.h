@@ -211,6 +211,27 @@ typedef struct b2asr_beam_io {
 size_t b2asr_beam_io_size(void);   /* sizeof(b2asr_beam_io), for binding sanity checks */
 int    b2asr_beam_step(const b2asr_beam_io* io, void* stream);
 
+/* ------------------------------------------------------------------------
+ * Decoder-loop fusion: pointwise half of the
+ * Speller's torch.nn.LSTMCell, reference src/asr.py:352-357 stepped from the
+ * decoder loop asr.py:84-104.  The host mirror (_dec.py) batches the
+ * embedding half of the input projection and all weight gradients outside the
+ * loop; per step it needs two small GEMMs into `gates` and one of these.
+ *
+ *   gates   [B,4H] in: pre-activation sum W_ih x + W_hh h (gate order i,f,g,o
+ *           as torch.nn.LSTMCell); out: the four activations, kept for backward
+ *   b_ih, b_hh  [4H] or NULL
+ *   c_prev  [B,H];  h, c [B,H] out
+ * backward:
+ *   d_h, d_c  [B,H] or NULL (= 0);  act = the forward's `gates` output
+ *   d_gates   [B,4H] out with row stride dg_stride (>= 4H) so a step can write
+ *             its slice of a [B,L,4H] buffer;  d_c_prev [B,H] out
+ * ---------------------------------------------------------------------- */
+int b2asr_lstm_cell_fwd(float* gates, const float* b_ih, const float* b_hh, const float* c_prev,
+                        float* h, float* c, int B, int H, void* stream);
+int b2asr_lstm_cell_bwd(const float* d_h, const float* d_c, const float* act, const float* c_prev, const float* c,
+                        float* d_gates, int64_t dg_stride, float* d_c_prev, int B, int H, void* stream);
+
 /* Debug aid, not part of the drop-in path: with B2ASR_ATT_TRACE=1 in the environment CTA 0 of every attention
  * launch stamps clock64() at its phase boundaries (forward: slots 0-9, backward: 16-27); this copies the first n
  * slots of the last launch to the host (synchronous). */
