@@ -104,6 +104,12 @@ def algorithmic_bytes(kernel, enc_lens, B, Tp, A, D, dec, V, labels, C=10, KW1=2
         return 4 * s * (3 * A + D + 4) + 4 * B * (2 * A + D + dec) + wts
     if kernel == "b2asr_ctc_loss_fwd_bwd":   # every valid logit row read once, every grad row written once
         return 4 * V * (s + B * Tp) + 8 * sum(labels) + 16 * B
+    if kernel == "b2asr_attn_keys":          # features read, keys written, psi weight + bias (padded batch rows)
+        return 4 * B * Tp * (D + A) + 4 * A * (D + 1)
+    if kernel == "b2asr_lstm_cell_fwd":      # gates read + activations written, c_prev in, h and c out
+        return 4 * B * dec * (4 + 4 + 3)
+    if kernel == "b2asr_lstm_cell_bwd":      # activations, c_prev, c, d_h, d_c in; d_gates, d_c_prev out
+        return 4 * B * dec * (4 + 4 + 4 + 1)
     return 0
 
 

@@ -44,3 +44,10 @@ for k, (c, t) in sorted(fam.items(), key=lambda kv: -kv[1][1]):
 ev.sort(key=lambda e: e.time_range.start)
 span = ev[-1].time_range.end - ev[0].time_range.start
 print("GPU activity span %.1f ms -> idle inside the span %.1f ms" % (span / 1e3, (span - tot) / 1e3))
+
+byname = {}
+for e in ev:
+    a = byname.setdefault(e.name[:90], [0, 0.0]); a[0] += 1; a[1] += e.device_time
+print("top kernels:")
+for k, (c, t) in sorted(byname.items(), key=lambda kv: -kv[1][1])[:28]:
+    print("  %6d x %7.1f us = %7.2f ms  %s" % (c, t / c, t / 1e3, k))
