@@ -11,17 +11,18 @@
 //
 // CTA = 128 rows x one N tile (<= 160 columns, multiple of 16); grid = (ceil(M/128), ceil(A/160)).
 // Operand tiles are split into hi/lo on the way from global to shared memory (generic proxy stores into the
-// canonical K-major no-swizzle UMMA layout, then fence.proxy.async); two stages, so the global loads of
-// k-block i+1 overlap the MMAs of k-block i; tcgen05.commit on an mbarrier releases a stage.  Epilogue:
+// canonical K-major no-swizzle UMMA layout, then fence.proxy.async); three 37 KB stages and register double
+// buffering of the global loads, two CTAs per SM; tcgen05.commit on an mbarrier releases a stage.  Epilogue:
 // tcgen05.ld (32 lanes x 16 columns per warp), + bias, accurate tanh, 64-byte stores per thread.
 #include "common.cuh"
 
 namespace b2asr {
 
 constexpr int kBM = 128;          // rows per CTA == TMEM lanes == UMMA M
-constexpr int kBK = 32;           // fp32 per k-block (8 chunks of 16 B); UMMA K for tf32 is 8
+constexpr int kBK = 16;           // fp32 per k-block (4 chunks of 16 B); UMMA K for tf32 is 8
+constexpr int kStages = 3;        // 3 x 36.9 KB: two CTAs fit one SM (and 2 x 256 TMEM columns = all 512)
 constexpr int kBNmax = 160;       // widest N tile (A=300 -> 160 + 144)
-constexpr int kKeysNT = 128;      // 4 warps: warp w owns TMEM lanes 32w..32w+31 in the epilogue
+constexpr int kKeysNT = 256;      // 8 warps stage operands; in the epilogue warp w owns TMEM lanes 32(w%4).. and half of the columns
 constexpr int kTmemCols = 256;    // power of two >= kBNmax
 
 struct KeysArgs {
@@ -68,42 +69,59 @@ __device__ __forceinline__ void split4(const float4 v, float4& hi, float4& lo) {
   hi.w = tf32_rn(v.w); lo.w = tf32_rn(v.w - hi.w);
 }
 
-// Load a [rows x kBK] fp32 tile (row stride ld, rows >= rmax or k >= kmax read as 0) and store its hi/lo
-// split into the canonical layout: chunk j (4 floats) of row r at j*LBO + (r/8)*128 + (r%8)*16, LBO = rows*16.
-__device__ __forceinline__ void load_split_tile(const float* g, long long ld, int row0, int rmax, int k0, int kmax,
-                                                int rows, unsigned char* hi_base, unsigned char* lo_base) {
-  const int items = rows * (kBK / 4);
-  const unsigned lbo = (unsigned)rows * 16u;
-  float4 v[4];
-  for (int base = 0; base < items; base += 4 * kKeysNT) {
+// One k-block of both operands in registers: kBK/4 = 4 chunks (float4) per row, rows*4 items spread over the CTA.
+// A tile: 128 rows -> 4 items per thread; W tile: <= 160 rows -> <= 5 items per thread.
+constexpr int kItemsA = kBM * (kBK / 4) / kKeysNT;                 // 4
+constexpr int kItemsW = (kBNmax * (kBK / 4) + kKeysNT - 1) / kKeysNT;   // 5
+struct KTile { float4 a[kItemsA]; float4 w[kItemsW]; };
+
+// item idx of a tile with `rows` rows: row r = (idx>>5)*8 + (idx&7), chunk ch = (idx>>3)&3; a quarter-warp reads one
+// 16-byte chunk of 8 consecutive rows, and the same quarter-warp later writes one 128-byte core matrix.
+__device__ __forceinline__ void load_ktile(KTile& t, const KeysArgs& p, int row0, int n0, int bn, int k0) {
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int idx = base + u * kKeysNT + threadIdx.x;
-      v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (idx < items) {
-        const int r8 = idx & 7, ch = (idx >> 3) & 7, rg = idx >> 6;
-        const int r = rg * 8 + r8, k = k0 + ch * 4;
-        if (row0 + r < rmax && k < kmax) v[u] = __ldg(reinterpret_cast<const float4*>(g + (long long)(row0 + r) * ld + k));
-      }
-    }
+  for (int u = 0; u < kItemsA; ++u) {
+    const int idx = u * kKeysNT + threadIdx.x;
+    const int r = (idx >> 5) * 8 + (idx & 7), k = k0 + ((idx >> 3) & 3) * 4;
+    t.a[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (row0 + r < p.M && k < p.D) t.a[u] = __ldg(reinterpret_cast<const float4*>(p.h + (long long)(row0 + r) * p.D + k));
+  }
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int idx = base + u * kKeysNT + threadIdx.x;
-      if (idx < items) {
-        const int r8 = idx & 7, ch = (idx >> 3) & 7, rg = idx >> 6;
-        const unsigned off = (unsigned)ch * lbo + (unsigned)rg * 128u + (unsigned)r8 * 16u;
-        float4 hi, lo;
-        split4(v[u], hi, lo);
-        *reinterpret_cast<float4*>(hi_base + off) = hi;
-        *reinterpret_cast<float4*>(lo_base + off) = lo;
-      }
+  for (int u = 0; u < kItemsW; ++u) {
+    const int idx = u * kKeysNT + threadIdx.x;
+    const int r = (idx >> 5) * 8 + (idx & 7), k = k0 + ((idx >> 3) & 3) * 4;
+    t.w[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (r < bn && n0 + r < p.A && k < p.D) t.w[u] = __ldg(reinterpret_cast<const float4*>(p.W + (long long)(n0 + r) * p.D + k));
+  }
+}
+
+// hi/lo split into the canonical layout: chunk ch of row r at ch*LBO + (r/8)*128 + (r%8)*16, LBO = rows*16.
+__device__ __forceinline__ void store_ktile(const KTile& t, int bn, unsigned char* a_hi, unsigned char* a_lo,
+                                            unsigned char* w_hi, unsigned char* w_lo) {
+#pragma unroll
+  for (int u = 0; u < kItemsA; ++u) {
+    const int idx = u * kKeysNT + threadIdx.x;
+    const unsigned off = (unsigned)((idx >> 3) & 3) * (kBM * 16u) + (unsigned)(idx >> 5) * 128u + (unsigned)(idx & 7) * 16u;
+    float4 hi, lo;
+    split4(t.a[u], hi, lo);
+    *reinterpret_cast<float4*>(a_hi + off) = hi;
+    *reinterpret_cast<float4*>(a_lo + off) = lo;
+  }
+#pragma unroll
+  for (int u = 0; u < kItemsW; ++u) {
+    const int idx = u * kKeysNT + threadIdx.x;
+    if (idx < bn * (kBK / 4)) {
+      const unsigned off = (unsigned)((idx >> 3) & 3) * ((unsigned)bn * 16u) + (unsigned)(idx >> 5) * 128u + (unsigned)(idx & 7) * 16u;
+      float4 hi, lo;
+      split4(t.w[u], hi, lo);
+      *reinterpret_cast<float4*>(w_hi + off) = hi;
+      *reinterpret_cast<float4*>(w_lo + off) = lo;
     }
   }
 }
 
-__global__ void __launch_bounds__(kKeysNT, 1) attn_keys_kernel(KeysArgs p) {
+__global__ void __launch_bounds__(kKeysNT, 2) attn_keys_kernel(KeysArgs p) {
   extern __shared__ __align__(128) unsigned char smk[];
-  __shared__ __align__(8) unsigned long long bar_free[2];
+  __shared__ __align__(8) unsigned long long bar_free[kStages];
   __shared__ __align__(8) unsigned long long bar_done;
   __shared__ unsigned tmem_base_sm;
 
@@ -115,7 +133,8 @@ __global__ void __launch_bounds__(kKeysNT, 1) attn_keys_kernel(KeysArgs p) {
   const unsigned a_bytes = kBM * kBK * 4, w_bytes = (unsigned)p.BN * kBK * 4;
 
   if (tid == 0) {
-    mbar_init(&bar_free[0], 1); mbar_init(&bar_free[1], 1); mbar_init(&bar_done, 1);
+    for (int s = 0; s < kStages; ++s) mbar_init(&bar_free[s], 1);
+    mbar_init(&bar_done, 1);
     mbar_fence_init();
   }
   if (warp == 0) {                                             // one warp allocates tensor memory
@@ -131,13 +150,17 @@ __global__ void __launch_bounds__(kKeysNT, 1) attn_keys_kernel(KeysArgs p) {
   const unsigned idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((unsigned)(bn >> 3) << 17) | ((unsigned)(kBM >> 4) << 24);
   const int nkb = (p.D + kBK - 1) / kBK;
 
+  // register double buffering: the global loads of k-block kb+1 are in flight while k-block kb is split, stored,
+  // and its MMAs issued; the second CTA on the SM fills whatever bubbles remain
+  KTile cur, nxt;
+  load_ktile(cur, p, row0, n0, bn, 0);
   for (int kb = 0; kb < nkb; ++kb) {
-    const int s = kb & 1;
+    const int s = kb % kStages;
     unsigned char* st = smk + (size_t)s * stage;
     unsigned char* a_hi = st, *a_lo = st + a_bytes, *w_hi = st + 2 * a_bytes, *w_lo = st + 2 * a_bytes + w_bytes;
-    if (kb >= 2) mbar_wait(&bar_free[s], (unsigned)(((kb - 2) >> 1) & 1));   // MMAs of k-block kb-2 have read this stage
-    load_split_tile(p.h, p.D, row0, p.M, kb * kBK, p.D, kBM, a_hi, a_lo);
-    load_split_tile(p.W, p.D, n0, p.A, kb * kBK, p.D, bn, w_hi, w_lo);
+    if (kb + 1 < nkb) load_ktile(nxt, p, row0, n0, bn, (kb + 1) * kBK);
+    if (kb >= kStages) mbar_wait(&bar_free[s], (unsigned)(((kb - kStages) / kStages) & 1));   // MMAs of k-block kb-kStages have read this stage
+    store_ktile(cur, bn, a_hi, a_lo, w_hi, w_lo);
     fence_proxy_async_smem();                                   // generic-proxy stores -> visible to the tensor core
     __syncthreads();
     if (tid == 0) {
@@ -155,16 +178,20 @@ __global__ void __launch_bounds__(kKeysNT, 1) attn_keys_kernel(KeysArgs p) {
       }
       umma_commit(&bar_free[s]);                                // arrives when the MMAs above have finished
     }
+    cur = nxt;
   }
   if (tid == 0) umma_commit(&bar_done);
   mbar_wait(&bar_done, 0u);
   tc_fence_after();
 
   // ---- epilogue: TMEM -> registers -> + bias -> tanh -> global ------------------------------------------
-  const int row = row0 + warp * 32 + lane;
-  for (int c0 = 0; c0 < bn; c0 += 16) {
+  const int lq = warp & 3;                                      // TMEM lane quarter this warp may read
+  const int nch = bn / 16, chalf = (nch + 1) / 2;
+  const int cbeg = (warp >> 2) ? chalf * 16 : 0, cend = (warp >> 2) ? bn : chalf * 16;
+  const int row = row0 + lq * 32 + lane;
+  for (int c0 = cbeg; c0 < cend; c0 += 16) {
     unsigned r[16];
-    const unsigned taddr = tmem + ((unsigned)(warp * 32) << 16) + (unsigned)c0;
+    const unsigned taddr = tmem + ((unsigned)(lq * 32) << 16) + (unsigned)c0;
     asm volatile(
         "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
         : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
@@ -209,7 +236,7 @@ extern "C" int b2asr_attn_keys(const float* h, const float* W, const float* bias
   a.h = h; a.W = W; a.bias = bias; a.out = out; a.M = M; a.D = D; a.A = A;
   const int ntiles = (A + kBNmax - 1) / kBNmax;
   a.BN = (((A + ntiles - 1) / ntiles) + 15) / 16 * 16;          // even split, multiple of 16 (A=300 -> 160)
-  const size_t smem = 2 * keys_stage_bytes(a.BN);
+  const size_t smem = kStages * keys_stage_bytes(a.BN);
   B2_CUDA_TRY(cudaFuncSetAttribute(attn_keys_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   dim3 grid((unsigned)((M + kBM - 1) / kBM), (unsigned)ntiles);
   attn_keys_kernel<<<grid, kKeysNT, smem, (cudaStream_t)stream>>>(a);
