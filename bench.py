@@ -116,6 +116,15 @@ def algorithmic_bytes(kernel, enc_lens, B, Tp, A, D, dec, V, labels, C=10, KW1=2
 # ------------------------------------------------------------------------------------------------
 # reference arm / cpu_baseline: the oracle port of the reference's train step on the host cores
 # ------------------------------------------------------------------------------------------------
+def use_all_host_threads():
+    """torchrun exports OMP_NUM_THREADS=1 to every rank; the CPU arm runs on rank 0 alone and may use the box."""
+    import torch
+    n = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    if torch.get_num_threads() < n:
+        torch.set_num_threads(n)
+    return torch.get_num_threads()
+
+
 def cpu_train_step_rate(steps, warmup, budget_s, seed=1234):
     """Times oracle/model_oracle.train_step (restating reference solver.py:132-182 + asr.py:58-112) on a
     bounded sample of the M2 workload: the first `bs` utterances of the synthetic batch at full length."""
@@ -127,7 +136,7 @@ def cpu_train_step_rate(steps, warmup, budget_s, seed=1234):
     model = mo.OracleModel(w["d_in"], w["vocab"], w["cfg"])
     opt = torch.optim.Adadelta(model.parameters(), lr=1.0, eps=1e-8)
     x, y, lens = syn.make_batch(WORKLOAD, seed)
-    cores = torch.get_num_threads()
+    cores = use_all_host_threads()
 
     def run(bs):
         xs = x[:bs]
@@ -228,6 +237,7 @@ def cpu_decode_rate(n_steps=2):
     from oracle import model_oracle as mo
     syn = pkg("synthetic")
     w = syn.WORKLOADS[DEC["workload"]]
+    use_all_host_threads()
     torch.manual_seed(0)
     model = mo.OracleModel(w["d_in"], w["vocab"], w["cfg"]).eval()
     lm = do.OracleLM(DEC["lm"][0], DEC["lm"][1], w["vocab"], layers=DEC["lm"][2]).eval()

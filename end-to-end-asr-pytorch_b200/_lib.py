@@ -48,6 +48,7 @@ _SIGNATURES = {
     "b2asr_beam_io_size": (c_sz, []),
     "b2asr_beam_step": (c_i, [ctypes.POINTER(BeamIO), c_p]),
     "b2asr_debug_attn_trace": (c_i, [ctypes.POINTER(ctypes.c_longlong), c_i]),
+    "b2asr_debug_beam_trace": (c_i, [ctypes.POINTER(ctypes.c_longlong), c_i]),
     "b2asr_lstm_cell_fwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_p]),
     "b2asr_lstm_cell_bwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_i64, c_p, c_i, c_i, c_p]),
     "b2asr_last_error": (ctypes.c_char_p, []),

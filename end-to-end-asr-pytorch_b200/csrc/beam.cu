@@ -213,6 +213,30 @@ __global__ void __launch_bounds__(kBeamNT) prefix_score_kernel(const float* x, i
 // ------------------------------------------------------------------------------------------------
 // Fused beam step
 // ------------------------------------------------------------------------------------------------
+// Stable descending rank of every child (asr.py:251): one warp per child; the lane's competitors (32*Q >= nc of
+// them) stay in registers while the warp walks its children.  A slot without a child holds -inf: it never
+// outranks anything and is never ranked itself.
+template <int Q>
+__device__ __forceinline__ void rank_children(const float* avg, const int* slotk, int* slot_child, int nc, int n) {
+  const int lane = threadIdx.x & 31;
+  float mine[Q];
+#pragma unroll
+  for (int q = 0; q < Q; ++q) { const int m = lane + 32 * q; mine[q] = m < nc ? avg[m] : -INFINITY; }
+  for (int c = threadIdx.x >> 5; c < nc; c += blockDim.x >> 5) {
+    if (slotk[c] == -2) continue;                              // warp-uniform
+    const float a = avg[c];
+    int rank = 0;
+#pragma unroll
+    for (int q = 0; q < Q; ++q) rank += (mine[q] > a) || (mine[q] == a && lane + 32 * q < c);
+    rank = __reduce_add_sync(kFull, rank);
+    if (lane == 0 && rank < n) slot_child[rank] = c;
+  }
+}
+
+// debug aid: clock64 stamps of CTA 0's phases (slots 0-7) and of the pruning CTA (8-13); see b2asr_debug_beam_trace
+__device__ long long g_beam_trace[16];
+#define BT(slot) do { if (threadIdx.x == 0 && ((slot) >= 8 || blockIdx.x == 0)) g_beam_trace[slot] = clock64(); } while (0)
+
 __global__ void __launch_bounds__(kBeamNT) beam_step_kernel(b2asr_beam_io io) {
   extern __shared__ __align__(16) float smf[];
   __shared__ TopkScratch S;
@@ -231,24 +255,29 @@ __global__ void __launch_bounds__(kBeamNT) beam_step_kernel(b2asr_beam_io io) {
   const int Vp = (V + 3) / 4 * 4;
   const bool live = io.valid_in[row] != 0;
 
+  BT(0);
   if (live) {
     const float* att = io.att_logp + (long long)row * V;
     for (int i = tid; i < V; i += NT) val[i] = att[i];
     __syncthreads();
     if (ctc) {
       // ---- CTC candidates: top-K of the attention log-probs (asr.py:215-216) -----------------------
+      BT(1);
       cta_topk(val, V, K, candv_sm, cand_sm, &S);
+      BT(2);
       const int Tp = (T + 3) / 4 * 4;
       float* base = smf + Vp;
       PrefixTables tb{base, base + (size_t)T * 32, base + (size_t)T * 32 + Tp, base + (size_t)T * 32 + 2 * Tp};
       const float* r_prev = io.r_in + (long long)row * T * 2;
       prefix_fill_tables(tb, io.x_ctc, T, V, r_prev, cand_sm, K, max(1, plen));
       __syncthreads();
+      BT(3);
       // ---- prefix scores of prefix+[c] (ctc.py:65-101) ------------------------------------------------
       if ((tid >> 5) * kCandPerWarp < K)
         prefix_recursion(tb, T, K, plen, (int)io.last_in[row], cand_sm, psi_sm,
                          io.r_all + (long long)row * T * K * 2, (long long)K * 2, 2);
       __syncthreads();
+      BT(4);
       // ---- fusion (asr.py:222-229): separate fp32 multiply and add roundings, as torch does -----------
       const float neg = __fmul_rn(io.w_ctc, kNegCtc);
       for (int i = tid; i < V; i += NT) val[i] = __fadd_rn(__fmul_rn(io.w_att, val[i]), neg);
@@ -269,7 +298,9 @@ __global__ void __launch_bounds__(kBeamNT) beam_step_kernel(b2asr_beam_io io) {
       __syncthreads();
     }
     // ---- top-`beam` of the fused scores (asr.py:238) ---------------------------------------------------
+    BT(5);
     cta_topk(val, V, n, topv_sm, topi_sm, &S);
+    BT(6);
     if (tid < n) { io.topv[row * n + tid] = topv_sm[tid]; io.topi[row * n + tid] = topi_sm[tid]; }
   }
 
@@ -278,13 +309,20 @@ __global__ void __launch_bounds__(kBeamNT) beam_step_kernel(b2asr_beam_io io) {
   __syncthreads();
   if (tid == 0) is_last = (atomicAdd(io.ticket, 1u) == (unsigned)n - 1u);
   __syncthreads();
+  BT(7);
   if (!is_last) return;
   __threadfence();
+  BT(8);
 
   float* avg = smf;                                            // [n*n] mean score of every child (or -inf)
   int* slotk = reinterpret_cast<int*>(smf + n * n);            // [n*n] candidate slot of the child's token
   const float cnt = (float)(plen + 1);
   const int nc = n * n;
+  int* slot_child = slotk + nc;                                // [n] child index occupying each survivor slot
+  int* cand_all = slot_child + n;                              // [n*K] every row's CTC candidates, staged once
+  if (ctc) for (int i = tid; i < n * K; i += NT) cand_all[i] = __ldcg(io.cand + i);
+  for (int j = tid; j < n; j += NT) slot_child[j] = -1;
+  __syncthreads();
   for (int c = tid; c < nc; c += NT) {
     const int r = c / n;
     float a = -INFINITY; int sk = -2;                           // -2: no child here; -1: child, token not a CTC candidate
@@ -293,23 +331,18 @@ __global__ void __launch_bounds__(kBeamNT) beam_step_kernel(b2asr_beam_io io) {
       if (tok >= 0 && tok != kEos) {
         a = __fdiv_rn(__fadd_rn(io.sum_in[r], __ldcg(io.topv + c)), cnt);      // postprocess.py:71-74
         sk = -1;
-        if (ctc) for (int j = 0; j < K; ++j) if (__ldcg(io.cand + r * K + j) == tok) { sk = j; break; }
+        if (ctc) for (int j = 0; j < K; ++j) if (cand_all[r * K + j] == tok) { sk = j; break; }
       }
     }
     avg[c] = a; slotk[c] = sk;
   }
-  int* slot_child = slotk + nc;                                // [n] child index occupying each survivor slot
-  for (int j = tid; j < n; j += NT) slot_child[j] = -1;
+  BT(9);
   __syncthreads();
-  for (int c = tid; c < nc; c += NT) {
-    if (slotk[c] == -2) continue;
-    const float a = avg[c];
-    int rank = 0;                                              // stable descending order (asr.py:251)
-    for (int m = 0; m < nc; ++m)
-      if (slotk[m] != -2 && (avg[m] > a || (avg[m] == a && m < c))) ++rank;
-    if (rank < n) slot_child[rank] = c;
-  }
+  // stable descending rank of every child (asr.py:251): one warp per child, lanes stride the competitors.
+  // A slot without a child holds -inf: it never outranks anything and is never ranked itself.
+  if (nc <= 512) rank_children<16>(avg, slotk, slot_child, nc, n); else rank_children<32>(avg, slotk, slot_child, nc, n);
   __syncthreads();
+  BT(10);
   const long long hoff = (long long)min(plen, io.max_steps - 1) * n;
   for (int j = tid; j < n; j += NT) {
     const int c = slot_child[j];
@@ -326,16 +359,40 @@ __global__ void __launch_bounds__(kBeamNT) beam_step_kernel(b2asr_beam_io io) {
       io.hist_parent[hoff + j] = -1; io.hist_tok[hoff + j] = -1; io.hist_score[hoff + j] = 0.f;
     }
   }
+  BT(11);
   if (ctc) {                                                   // survivors inherit r[cand slot] (postprocess.py:95-97)
-    for (int i = tid; i < n * T * 2; i += NT) {
-      const int j = i / (T * 2), rem = i - j * (T * 2), t = rem >> 1, z = rem & 1;
+    // one warp-strided pass per survivor: (r[t,0], r[t,1]) is one 8-byte load from the parent's candidate slot
+    const float2* rall2 = reinterpret_cast<const float2*>(io.r_all);
+    float2* rout2 = reinterpret_cast<float2*>(io.r_out);
+    // survivors' source offsets once, then a flat (survivor, frame) sweep with 8 loads in flight per thread
+    long long* src_of = reinterpret_cast<long long*>(reinterpret_cast<int*>(smf) + ((2 * nc + n + n * K + 1) & ~1));   // [n], 8-byte aligned
+    for (int j = tid; j < n; j += NT) {
       const int c = slot_child[j];
-      float v = kLogZero;
-      if (c >= 0 && slotk[c] >= 0) v = __ldcg(io.r_all + (((long long)(c / n) * T + t) * K + slotk[c]) * 2 + z);
-      io.r_out[i] = v;
+      src_of[j] = (c >= 0 && slotk[c] >= 0) ? ((long long)(c / n) * T * K + slotk[c]) : -1;
+    }
+    __syncthreads();
+    const int total = n * T;
+    for (int i0 = 0; i0 < total; i0 += 8 * NT) {
+      float2 v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int i = i0 + u * NT + tid;
+        v[u] = make_float2(kLogZero, kLogZero);
+        if (i < total) {
+          const int j = i / T, t = i - j * T;
+          const long long so = src_of[j];
+          if (so >= 0) v[u] = __ldcg(rall2 + so + (long long)t * K);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int i = i0 + u * NT + tid;
+        if (i < total) rout2[i] = v[u];
+      }
     }
   }
   __syncthreads();
+  BT(12);
   int* eos_at = slot_child;                                    // reuse: [n] child index holding <eos> per row, or -1
   for (int j = tid; j < n; j += NT) eos_at[j] = -1;
   __syncthreads();
@@ -354,6 +411,7 @@ __global__ void __launch_bounds__(kBeamNT) beam_step_kernel(b2asr_beam_io io) {
     *io.step = plen + 1;
     *io.ticket = 0u;
   }
+  BT(13);
 }
 
 }  // namespace b2asr
@@ -397,12 +455,19 @@ extern "C" int b2asr_beam_step(const b2asr_beam_io* io, void* stream) {
     B2_REQUIRE(a.r_in && a.r_out && a.ctc_prob_in && a.cand && a.psi && a.r_all, B2ASR_EINVAL, "beam_step: joint CTC needs r_in/r_out/ctc_prob_in/cand/psi/r_all");
     floats += prefix_smem_floats(a.T);
   }
-  const size_t prune = (size_t)2 * a.n * a.n + a.n;
+  const size_t prune = (size_t)2 * a.n * a.n + a.n + (size_t)a.n * (a.x_ctc ? a.K : 0) + 2 + 2 * (size_t)a.n;
   if (floats < prune) floats = prune;
   const size_t smem = floats * sizeof(float);
   B2_REQUIRE(smem <= 200 * 1024, B2ASR_EUNSUPPORTED, "beam_step: V=%d, T=%d need %zu bytes of shared memory", a.V, a.T, smem);
   B2_CUDA_TRY(cudaFuncSetAttribute(beam_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   beam_step_kernel<<<a.n, kBeamNT, smem, (cudaStream_t)stream>>>(a);
   B2_CUDA_TRY(cudaGetLastError());
+  return B2ASR_OK;
+}
+
+// debug aid: phase stamps of the last beam_step launch (synchronous copy)
+extern "C" int b2asr_debug_beam_trace(long long* host_out, int n) {
+  B2_REQUIRE(host_out && n > 0 && n <= 16, B2ASR_EINVAL, "beam trace: bad arguments");
+  B2_CUDA_TRY(cudaMemcpyFromSymbol(host_out, b2asr::g_beam_trace, sizeof(long long) * n));
   return B2ASR_OK;
 }

@@ -236,6 +236,8 @@ int b2asr_lstm_cell_bwd(const float* d_h, const float* d_c, const float* act, co
  * launch stamps clock64() at its phase boundaries (forward: slots 0-9, backward: 16-27); this copies the first n
  * slots of the last launch to the host (synchronous). */
 int    b2asr_debug_attn_trace(long long* host_out, int n);
+/* Same for the beam step: CTA 0's phases in slots 0-7, the pruning CTA's in 8-13 (always on: 14 stores per launch). */
+int    b2asr_debug_beam_trace(long long* host_out, int n);
 
 #ifdef __cplusplus
 }

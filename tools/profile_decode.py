@@ -59,6 +59,16 @@ with torch.no_grad():
     torch.cuda.synchronize()
     torch.cuda.cudart().cudaProfilerStop()
     print("beam_step kernel: %.1f us per step (T'=%d, V=%d, beam %d, K=%d)" % (e0.elapsed_time(e1) / 20 * 1e3, T, V, n, bs.K))
+    import ctypes
+    buf = (ctypes.c_longlong * 16)()
+    if lib.lib().b2asr_debug_beam_trace(buf, 16) == 0:
+        v = list(buf)
+        names = ["load att", "top-K", "tables", "recursion", "fusion", "top-beam", "store", "", "rank in", "rank", "state", "r gather", "eos+final"]
+        print("beam_step phases (CTA 0: 0-6; pruning CTA: 8-13), us at 1965 MHz:")
+        for i in range(1, 7):
+            print("  %-10s %7.2f" % (names[i - 1], (v[i] - v[i - 1]) / 1965.0))
+        for i in range(9, 14):
+            print("  %-10s %7.2f" % (names[i - 1], (v[i] - v[i - 1]) / 1965.0))
     t0 = sync()
     res = bs.results()
     t1 = sync()
