@@ -419,7 +419,10 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-decode", action="store_true", help="skip the beam-decode RTF leg")
     ap.add_argument("--decode-utts", type=int, default=4, help="utterances per GPU in the decode leg")
+    ap.add_argument("--workload", default=WORKLOAD, help="train-step workload (synthetic.WORKLOADS); the default is the "
+                    "configuration BASELINE.json's metric is quoted on, the others are reported in BASELINE.md only")
     args = ap.parse_args()
+    globals()["WORKLOAD"] = args.workload
     if args.impl == "reference":
         run_reference(args)
     else:
