@@ -216,74 +216,94 @@ __global__ void __launch_bounds__(MAXNT, MINB) attn_step_bwd_kernel(AttnArgs p) 
     float* kt = ring + (size_t)s * stage_floats;
     const int f0 = i * TFK, n = min(TFK, nf - f0);
     constexpr int UNR = MINB > 1 ? 2 : 4;
-    for (int j = 0; j < n; j += UNR) {
+    // Branch-free over the UNR frames so their chains interleave: a frame past the tile end recomputes the last
+    // frame with d_e = 0 (every contribution vanishes) and its stores are predicated off; inactive threads
+    // (a >= A) carry wga = wl = 0, so their d_pre and d_zl are 0 and only their (unused) accumulators see garbage.
+    if (loc) {
+      for (int j = 0; j < n; j += UNR) {
 #pragma unroll
-      for (int u = 0; u < UNR; ++u) {
-        const int jj = j + u;
-        if (jj < n) {                                     // uniform
+        for (int u = 0; u < UNR; ++u) {
+          const bool ok = j + u < n;
+          const int jj = ok ? j + u : n - 1;
           const float kv = kt[jj * A + kcol];
-          const float dev = de[f0 + jj];
-          float dpre, dzl = 0.f;
-          if (loc) {
-            const float4* f4 = reinterpret_cast<const float4*>(fsm) + (size_t)(f0 + jj) * CQ;
-            float fv[CPT];
+          const float dev = ok ? de[f0 + jj] : 0.f;
+          const float4* f4 = reinterpret_cast<const float4*>(fsm) + (size_t)(f0 + jj) * CQ;
+          float fv[CPT];
 #pragma unroll
-            for (int c4 = 0; c4 < CPT / 4; ++c4) {
-              float4 t4 = make_float4(0.f, 0.f, 0.f, 0.f);
-              if (c4 < CQ) t4 = f4[c4];
-              fv[4 * c4 + 0] = t4.x; fv[4 * c4 + 1] = t4.y; fv[4 * c4 + 2] = t4.z; fv[4 * c4 + 3] = t4.w;
-            }
-            float zl0 = 0.f, zl1 = 0.f;                     // two half-length dependency chains
-#pragma unroll
-            for (int c = 0; c < CPT; c += 2) { zl0 = fmaf(wl[c], fv[c], zl0); zl1 = fmaf(wl[c + 1], fv[c + 1], zl1); }
-            const float l = tanh_fast(zl0 + zl1);
-            const float uu = tanh_fast(kv + qa + l);
-            dwg_acc = fmaf(dev, uu, dwg_acc);
-            dpre = dev * wga * (1.f - uu * uu);
-            dq_acc += dpre;
-            dzl = dpre * (1.f - l * l);
-#pragma unroll
-            for (int c = 0; c < CPT; ++c) dwl[c] = fmaf(dzl, fv[c], dwl[c]);
-          } else {
-            dpre = dev * qa;
-            dq_acc = fmaf(dev, kv, dq_acc);
+          for (int c4 = 0; c4 < CPT / 4; ++c4) {
+            float4 t4 = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (c4 < CQ) t4 = f4[c4];
+            fv[4 * c4 + 0] = t4.x; fv[4 * c4 + 1] = t4.y; fv[4 * c4 + 2] = t4.z; fv[4 * c4 + 3] = t4.w;
           }
-          if (active) {
-            // fire-and-forget reduction (RED.ADD.F32): one owner per element and launch, so no contention, and
-            // no L2 round trip on the loop's critical path as a load-add-store would put there
-            red_add_f32(dkb + (long long)(f0 + jj) * A + tid, dpre);
-            if (loc) kt[jj * A + tid] = dzl;
-          }
+          float zl0 = 0.f, zl1 = 0.f;                     // two half-length dependency chains
+#pragma unroll
+          for (int c = 0; c < CPT; c += 2) { zl0 = fmaf(wl[c], fv[c], zl0); zl1 = fmaf(wl[c + 1], fv[c + 1], zl1); }
+          const float l = tanh_fast(zl0 + zl1);
+          const float uu = tanh_fast(kv + qa + l);
+          dwg_acc = fmaf(dev, uu, dwg_acc);
+          const float dpre = dev * wga * (1.f - uu * uu);
+          dq_acc += dpre;
+          const float dzl = dpre * (1.f - l * l);
+#pragma unroll
+          for (int c = 0; c < CPT; ++c) dwl[c] = fmaf(dzl, fv[c], dwl[c]);
+          // fire-and-forget reduction (RED.ADD.F32): one owner per element and launch, so no contention, and
+          // no L2 round trip on the loop's critical path as a load-add-store would put there.  Predicated, not
+          // branched; the d_zl write-back of a masked frame rewrites the slot it was clamped to with the same role.
+          // Unconditional and branch-free (ptxas turns a predicated RED into a branch, which would split the
+          // unrolled frames into basic blocks again): masked lanes add 0.0 to a valid element and park their
+          // d_zl in a scratch slot.
+          const bool live = active && ok;
+          red_add_f32(dkb + (long long)(f0 + jj) * A + kcol, live ? dpre : 0.f);
+          float* zdst = live ? kt + jj * A + tid : red + (tid & 31);
+          *zdst = dzl;
         }
+      }
+    } else {
+      float* dkp = dkb + (long long)f0 * A + kcol;
+      for (int j = 0; j < n; ++j, dkp += A) {
+        const float kv = kt[j * A + kcol];
+        const float dev = de[f0 + j];
+        dq_acc = fmaf(dev, kv, dq_acc);
+        if (active) red_add_f32(dkp, dev * qa);
       }
     }
     __syncthreads();
     if (loc) {
+      // df[j][c] = sum_a d_zl[j][a] Wl[a][c]: one warp per frame, lanes stride a, all CPT channels at once (CPT/4
+      // independent float4 accumulators and butterflies -> instruction-level parallelism instead of a task loop)
       const float4* wl4 = reinterpret_cast<const float4*>(wls);
-      for (int task = warp; task < n * CQ; task += nwarp) {
-        const int j = task / CQ, cq = task - j * CQ;
-        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int j = warp; j < n; j += nwarp) {
+        float4 acc[CPT / 4];
+#pragma unroll
+        for (int q = 0; q < CPT / 4; ++q) acc[q] = make_float4(0.f, 0.f, 0.f, 0.f);
         for (int a = lane; a < A; a += 32) {
           const float dz = kt[j * A + a];
-          const float4 w = wl4[a * CQ + cq];
-          acc.x = fmaf(dz, w.x, acc.x); acc.y = fmaf(dz, w.y, acc.y); acc.z = fmaf(dz, w.z, acc.z); acc.w = fmaf(dz, w.w, acc.w);
+#pragma unroll
+          for (int q = 0; q < CPT / 4; ++q) {
+            if (q < CQ) {
+              const float4 w = wl4[a * CQ + q];
+              acc[q].x = fmaf(dz, w.x, acc[q].x); acc[q].y = fmaf(dz, w.y, acc[q].y);
+              acc[q].z = fmaf(dz, w.z, acc[q].z); acc[q].w = fmaf(dz, w.w, acc[q].w);
+            }
+          }
         }
-        {
-          const bool up = lane & 16;
-          const float s0 = up ? acc.x : acc.z, s1 = up ? acc.y : acc.w;
-          const float k0 = up ? acc.z : acc.x, k1 = up ? acc.w : acc.y;
-          acc.x = k0 + __shfl_xor_sync(kFull, s0, 16);
-          acc.y = k1 + __shfl_xor_sync(kFull, s1, 16);
+        const bool up16 = lane & 16, up8 = lane & 8;
+        const int sub = ((lane >> 4) & 1) * 2 + ((lane >> 3) & 1);
+#pragma unroll
+        for (int q = 0; q < CPT / 4; ++q) {
+          if (q < CQ) {
+            const float s0 = up16 ? acc[q].x : acc[q].z, s1 = up16 ? acc[q].y : acc[q].w;
+            const float k0 = up16 ? acc[q].z : acc[q].x, k1 = up16 ? acc[q].w : acc[q].y;
+            float x0 = k0 + __shfl_xor_sync(kFull, s0, 16);
+            const float x1 = k1 + __shfl_xor_sync(kFull, s1, 16);
+            const float t0 = up8 ? x0 : x1, t1 = up8 ? x1 : x0;
+            x0 = t1 + __shfl_xor_sync(kFull, t0, 8);
+            x0 += __shfl_xor_sync(kFull, x0, 4);
+            x0 += __shfl_xor_sync(kFull, x0, 2);
+            x0 += __shfl_xor_sync(kFull, x0, 1);
+            if ((lane & 7) == 0) dfo[(size_t)(f0 + j) * CP + q * 4 + sub] = x0;
+          }
         }
-        {
-          const bool up = lane & 8;
-          const float s0 = up ? acc.x : acc.y, k0 = up ? acc.y : acc.x;
-          acc.x = k0 + __shfl_xor_sync(kFull, s0, 8);
-        }
-        acc.x += __shfl_xor_sync(kFull, acc.x, 4);
-        acc.x += __shfl_xor_sync(kFull, acc.x, 2);
-        acc.x += __shfl_xor_sync(kFull, acc.x, 1);
-        if ((lane & 7) == 0) dfo[(size_t)(f0 + j) * CP + cq * 4 + ((lane >> 4) & 1) * 2 + ((lane >> 3) & 1)] = acc.x;
       }
     }
     __syncthreads();
@@ -357,14 +377,14 @@ __global__ void __launch_bounds__(MAXNT, MINB) attn_step_bwd_kernel(AttnArgs p) 
       const float4* d4 = reinterpret_cast<const float4*>(dfw);
       for (int item = tid; item < nf * CQ; item += NT) {
         const int cg = item / nf, i = item - cg * nf;
-        float acc = 0.f;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);       // four independent chains
 #pragma unroll 4
         for (int k = 0; k < KW1; ++k) {
           const float4 w = w4[k * CQ + cg];
           const float4 d = d4[(size_t)(i - k + 2 * p.Kw) * CQ + cg];
-          acc = fmaf(w.x, d.x, acc); acc = fmaf(w.y, d.y, acc); acc = fmaf(w.z, d.z, acc); acc = fmaf(w.w, d.w, acc);
+          acc.x = fmaf(w.x, d.x, acc.x); acc.y = fmaf(w.y, d.y, acc.y); acc.z = fmaf(w.z, d.z, acc.z); acc.w = fmaf(w.w, d.w, acc.w);
         }
-        tmp[cg * p.chunk_max + i] = acc;
+        tmp[cg * p.chunk_max + i] = (acc.x + acc.y) + (acc.z + acc.w);
       }
       __syncthreads();
       for (int i = tid; i < nf; i += NT) {
@@ -477,7 +497,8 @@ extern "C" int b2asr_attn_step_bwd(int mode, const float* Wphi, const float* key
   B2_REQUIRE(L.total <= 227 * 1024, B2ASR_EUNSUPPORTED, "attn_step_bwd: needs %zu bytes of shared memory (T=%d, cluster %d)", L.total, T, cs);
   const bool two = a.NT <= 320 && L.total <= 113 * 1024;      // two CTAs per SM fit: compile for <= 102 registers
   void (*kern)(AttnArgs);
-  if (a.C <= 12) kern = two ? attn_step_bwd_kernel<12, 320, 2> : attn_step_bwd_kernel<12, 512, 1>;
-  else kern = two ? attn_step_bwd_kernel<16, 320, 2> : attn_step_bwd_kernel<16, 512, 1>;
+  const bool small = a.NT <= 320;                              // one CTA per SM but <= 320 threads: up to 200 registers
+  if (a.C <= 12) kern = two ? attn_step_bwd_kernel<12, 320, 2> : (small ? attn_step_bwd_kernel<12, 320, 1> : attn_step_bwd_kernel<12, 512, 1>);
+  else kern = two ? attn_step_bwd_kernel<16, 320, 2> : (small ? attn_step_bwd_kernel<16, 320, 1> : attn_step_bwd_kernel<16, 512, 1>);
   return attn_launch(kern, a, L.total, (cudaStream_t)stream);
 }

@@ -128,8 +128,15 @@ __device__ __forceinline__ void fence_proxy_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
 
+// fire-and-forget reduction.  No "memory" clobber on purpose: nothing in the issuing kernel reads the target back,
+// and a clobber would pin every surrounding load/store in program order (it serialised the unrolled frames of
+// the attention backward's key pass).
 __device__ __forceinline__ void red_add_f32(float* gaddr, float v) {
-  asm volatile("red.global.add.f32 [%0], %1;" ::"l"(gaddr), "f"(v) : "memory");
+  asm volatile("red.global.add.f32 [%0], %1;" ::"l"(gaddr), "f"(v));
+}
+// predicated form: no branch around the instruction, so unrolled iterations stay one basic block
+__device__ __forceinline__ void red_add_f32_if(bool on, float* gaddr, float v) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %2, 0;\n\t@p red.global.add.f32 [%0], %1;\n\t}" ::"l"(gaddr), "f"(v), "r"((int)on));
 }
 
 // accurate tanh from one ex2 and one reciprocal: 1 - 2/(1+e^{2x}); abs error ~1e-7
