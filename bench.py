@@ -106,6 +106,8 @@ def algorithmic_bytes(kernel, enc_lens, B, Tp, A, D, dec, V, labels, C=10, KW1=2
         return 4 * V * (s + B * Tp) + 8 * sum(labels) + 16 * B
     if kernel == "b2asr_attn_keys":          # features read, keys written, psi weight + bias (padded batch rows)
         return 4 * B * Tp * (D + A) + 4 * A * (D + 1)
+    if kernel == "b2asr_ce_loss_fwd_bwd":    # decoder logits read once, finished gradient written once
+        return 8 * V * B * max(labels) + 16 * B * max(labels)
     if kernel == "b2asr_lstm_cell_fwd":      # gates read + activations written, c_prev in, h and c out
         return 4 * B * dec * (4 + 4 + 3)
     if kernel == "b2asr_lstm_cell_bwd":      # activations, c_prev, c, d_h, d_c in; d_gates, d_c_prev out

@@ -124,10 +124,12 @@ class Hypothesis:
         return self.emb(torch.LongTensor([idx]).to(next(self.emb.parameters()).device))
 
 
-def cal_acc(pred, label):
+def cal_acc(pred, label, hyp=None):
     '''Mean per-utterance token accuracy up to the first padding label (postprocess.py:121-133),
-    computed on the device; one scalar crosses to the host.'''
-    hyp = pred.detach().argmax(dim=-1)
+    computed on the device; one scalar crosses to the host.  `hyp` = the row argmax of `pred` when the caller
+    already has it (the CE kernel returns it), saving the pass over the logits.'''
+    if hyp is None:
+        hyp = pred.detach().argmax(dim=-1)
     label = label.to(hyp.device)
     live = torch.cumprod((label != 0).to(torch.int64), dim=-1) > 0       # stop at the first 0, as the loop does
     n = min(hyp.shape[1], label.shape[1])

@@ -15,6 +15,7 @@ import math
 import torch
 import torch.nn.functional as F
 
+from . import ce as _ce
 from . import ctc as _ctc
 
 GRAD_CLIP = 5            # solver.py:20
@@ -28,21 +29,24 @@ def infer_lengths(x):
     return [int(v) for v in (x.sum(dim=-1) != 0).sum(dim=-1).tolist()]
 
 
-def hybrid_loss(ctc_pred, att_pred, y, enc_len, ctc_weight, ans_len=None):
+def hybrid_loss(ctc_pred, att_pred, y, enc_len, ctc_weight, ans_len=None, aux=None):
     """(1-w)*att_loss + w*ctc_loss exactly as solver.py:144-163 forms them.
 
     ctc_pred [B,T',V] raw logits (Seq2Seq.ctc_layer), att_pred [B,L,V] logits, y [B,>=L+1] int64 with
     y[:,0]=<sos>=0, <eos>=1 appended, right padded with 0; enc_len list[int].
-    Returns (loss, att_loss, ctc_loss)."""
+    Returns (loss, att_loss, ctc_loss); a dict passed as `aux` receives 'att_argmax' [B,L], the row argmax of
+    att_pred that the CE kernel finds on its way (what cal_acc / cal_cer take of the same logits)."""
     tgt_len = torch.sum(y != 0, dim=-1)
     if ans_len is None:
         ans_len = int(torch.max(tgt_len))
     label = y[:, 1:ans_len + 1].contiguous()
     att_loss = ctc_loss = 0
     if ctc_weight < 1:
-        b, t, c = att_pred.shape
-        ce = F.cross_entropy(att_pred.reshape(b * t, c), label.reshape(-1), ignore_index=0, reduction='none')
-        att_loss = torch.mean(ce.view(b, t).sum(dim=-1) / tgt_len.to(torch.float32))
+        # solver.py:149-155 -- CE(ignore_index=0,'none'), per-utterance sum / length, batch mean; one launch
+        att_loss, _, argmax = _ce.seq_loss_mean(att_pred, label, tgt_len, ignore_index=0,
+                                                grad_prescale=1 - ctc_weight, return_aux=True)
+        if aux is not None:
+            aux['att_argmax'] = argmax
     if ctc_weight > 0:
         # solver.py:160 -- F.log_softmax(ctc_pred.transpose(0,1)) + CTCLoss(blank=0,'mean'); fused here
         ctc_loss = _ctc.ctc_loss(ctc_pred, label, enc_len, tgt_len, blank=0, reduction='mean',
@@ -104,7 +108,8 @@ class TrainStep:
         ans_len = int(torch.max(tgt_len))
         self.grads.zero()                                           # asr_opt.zero_grad(), solver.py:139
         ctc_pred, enc_len, att_pred, _ = self.model(x, ans_len, tf_rate=tf_rate, teacher=y, state_len=state_len)
-        loss, att_loss, ctc_loss = hybrid_loss(ctc_pred, att_pred, y, enc_len, self.w, ans_len)
+        aux = {}
+        loss, att_loss, ctc_loss = hybrid_loss(ctc_pred, att_pred, y, enc_len, self.w, ans_len, aux)
         loss.backward()
         self.grads.allreduce_mean(self.group)
         grad_norm = self.grads.clip_(self.clip)
@@ -113,7 +118,8 @@ class TrainStep:
             self.opt.step()
         return dict(loss=loss.detach(), att_loss=att_loss if not torch.is_tensor(att_loss) else att_loss.detach(),
                     ctc_loss=ctc_loss if not torch.is_tensor(ctc_loss) else ctc_loss.detach(),
-                    grad_norm=grad_norm, stepped=stepped, att_pred=att_pred, ctc_pred=ctc_pred, enc_len=enc_len)
+                    grad_norm=grad_norm, stepped=stepped, att_pred=att_pred, ctc_pred=ctc_pred, enc_len=enc_len,
+                    att_argmax=aux.get('att_argmax'))
 
 
 def make_optimizer(model, opt_cfg):
@@ -218,7 +224,7 @@ class Trainer(Solver):
         self.asr_model = Seq2Seq(self.sample_x, self.mapper.get_dim(), self.config['asr_model']).to(self.device)
         if 'VGG' in self.config['asr_model']['encoder']['enc_type']:
             self.verbose('VCC Extractor in Encoder is enabled, time subsample rate = 4.')
-        self.seq_loss = torch.nn.CrossEntropyLoss(ignore_index=0, reduction='none').to(self.device)
+        self.seq_loss = _ce.CrossEntropyLoss(ignore_index=0, reduction='none').to(self.device)
         self.ctc_loss = _ctc.CTCLoss(blank=0, reduction='mean')                    # solver.py:93, on the sm_100a kernel
         self.ctc_weight = opt_cfg['joint_ctc']
         if self.paras.load:
@@ -268,7 +274,7 @@ class Trainer(Solver):
                 self.write_log('loss', loss_log)
                 label = y[:, 1:out['att_pred'].shape[1] + 1] if out['att_pred'] is not None else None
                 if self.ctc_weight < 1:
-                    self.write_log('acc', {'train': cal_acc(out['att_pred'], label)})
+                    self.write_log('acc', {'train': cal_acc(out['att_pred'], label, hyp=out['att_argmax'])})
                 if self.step % TRAIN_WER_STEP == 0 and self.ctc_weight < 1:
                     self.write_log('error rate', {'train': cal_cer(out['att_pred'], label, mapper=self.mapper)})
                 if self.step % self.valid_step == 0:

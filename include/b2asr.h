@@ -232,6 +232,25 @@ int b2asr_lstm_cell_fwd(float* gates, const float* b_ih, const float* b_hh, cons
 int b2asr_lstm_cell_bwd(const float* d_h, const float* d_c, const float* act, const float* c_prev, const float* c,
                         float* d_gates, int64_t dg_stride, float* d_c_prev, int B, int H, void* stream);
 
+/* ------------------------------------------------------------------------
+ * the attention branch's sequence loss, reference src/solver.py:90,149-155
+ *     seq_loss = CrossEntropyLoss(ignore_index=0, reduction='none')
+ *     att_loss = seq_loss(att_pred.view(b*t,c), label.view(-1))
+ *     att_loss = torch.sum(att_loss.view(b,t),dim=-1) / torch.sum(y!=0,dim=-1).float();  att_loss = torch.mean(att_loss)
+ * and the argmax cal_acc / cal_cer take of the same logits (src/postprocess.py:121-146), in ONE pass.
+ *   logits [N,V] fp32 (row stride in elements), labels [N] int64, rows_per_group = decoder steps per utterance
+ *   (row n belongs to group n / rows_per_group), group_len [G] int64 divisors (target lengths; NULL -> 1)
+ *   loss_rows [N] out: lse - x[label], 0 where label == ignore_index        (the reduction='none' vector)
+ *   argmax    [N] out (NULL to skip): first index of the row maximum
+ *   grad      [N,V] out (NULL to skip): grad_prescale / (group_len * G) * (softmax - onehot), zero rows where ignored
+ *   loss      [1] out (NULL to skip): mean over groups of (sum of the group's rows / group_len), fixed summation
+ *             order (bit-reproducible); a second one-CTA launch
+ * ---------------------------------------------------------------------- */
+int b2asr_ce_loss_fwd_bwd(const float* logits, int64_t stride_row, const int64_t* labels, int64_t N, int V,
+                          int rows_per_group, const int64_t* group_len, int64_t ignore_index, float grad_prescale,
+                          float* loss_rows, int64_t* argmax, float* grad, int64_t grad_stride_row,
+                          float* loss, void* stream);
+
 /* Debug aid, not part of the drop-in path: with B2ASR_ATT_TRACE=1 in the environment CTA 0 of every attention
  * launch stamps clock64() at its phase boundaries (forward: slots 0-9, backward: 16-27); this copies the first n
  * slots of the last launch to the host (synchronous). */

@@ -8,6 +8,7 @@ import torch
 
 from oracle import attention_oracle as ao
 from oracle import beam_oracle as bo
+from oracle import ce_oracle as ceo
 from oracle import ctc_oracle as co
 from oracle import decode_oracle as do
 from oracle import model_oracle as mo
@@ -109,3 +110,18 @@ def test_ctc_oracle_three_ways_agree():
     lp = torch.log_softmax(torch.randn(5, 3), -1).numpy()
     for lab in ([1, 2], [1, 1], [2], []):
         assert abs(co.brute_force_nll(lp, lab) - co.graves_log_lattice(lp, lab)[0]) < 1e-10
+
+
+@pytest.mark.parametrize("name", ["small", "wide"])
+def test_seq_loss_oracle_matches_reference_call(name):
+    """oracle/ce_oracle.py vs the reference's own call sequence (solver.py:90,149-155) and its own cal_acc."""
+    g = load("seqloss.pt")[name]
+    tgt_len = torch.sum(g["y"] != 0, dim=-1).numpy()
+    loss, rows, grad, argmax = ceo.seq_loss_mean(g["att_pred"].numpy(), g["label"].numpy(), tgt_len, 0, g["upstream"])
+    assert abs(loss - float(g["att_loss"])) <= 1e-6 * abs(float(g["att_loss"]))
+    assert np.allclose(rows, g["rows"].numpy(), rtol=1e-5, atol=1e-6)
+    # the reference ran in fp32: entries softmax-1 next to a saturated softmax carry its rounding (<= 1 ulp of 1 x row scale)
+    assert np.allclose(grad, g["grad"].numpy(), rtol=1e-5, atol=1e-7)
+    assert np.array_equal(argmax, g["argmax"].numpy())
+    assert argmax[0, 1] == 5                                           # the tie row: first maximum
+    assert abs(ceo.cal_acc(argmax, g["label"].numpy()) - g["acc"]) < 1e-12

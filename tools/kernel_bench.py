@@ -1,6 +1,6 @@
 """Stand-alone timing of each kernel group at the SURVEY.md section 8d shapes, with algorithmic bytes / flops
 and the fraction of the measured peaks.  Inputs are larger than L2 or rotated so that every timed launch
-streams from HBM unless noted.  usage: python tools/kernel_bench.py [ctc|keys|attn|all]"""
+streams from HBM unless noted.  usage: python tools/kernel_bench.py [ctc|keys|attn|ce|all]"""
 import importlib
 import json
 import os
@@ -11,7 +11,7 @@ import torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 PKG = "end-to-end-asr-pytorch_b200"
-ctc, keys, attn, lib = (importlib.import_module(PKG + "." + m) for m in ("ctc", "_keys", "_attn", "_lib"))
+ctc, keys, attn, lib, ce = (importlib.import_module(PKG + "." + m) for m in ("ctc", "_keys", "_attn", "_lib", "ce"))
 dev = torch.device("cuda:0")
 PEAK = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0}
 which = sys.argv[1] if len(sys.argv) > 1 else "all"
@@ -119,6 +119,44 @@ def bench_attn():
         print("bwd %-26s %.1f us  %.0f GB/s algorithmic = %.2f of measured HBM peak" % (label, t * 1e6, by_b / t / 1e9, by_b / t / 1e9 / PEAK["hbm_gbs"]))
 
 
+def bench_ce():
+    print("== sequence loss (section 8f-3): CE + gradient + argmax in one launch; bytes = 8 V N (logits read, gradient written)")
+    import torch.nn.functional as F
+    g = torch.Generator().manual_seed(0)
+    for B, L, V in [(32, 100, 5000), (64, 400, 5000), (32, 200, 31)]:
+        nrot = max(2, int(3e8 // (8 * B * L * V)) + 1)                 # rotate inputs so launches stream from HBM
+        xs = [torch.randn(B, L, V, device=dev).requires_grad_(True) for _ in range(min(nrot, 8))]
+        y = torch.randint(2, V, (B, L), generator=g)
+        tl = torch.randint(L // 2, L + 1, (B,), generator=g); tl[0] = L
+        for b in range(B):
+            y[b, tl[b]:] = 0
+        yd, tld = y.to(dev), tl.to(dev)
+        k = [0]
+
+        def ours():
+            x = xs[k[0] % len(xs)]; k[0] += 1
+            x.grad = None
+            ce.seq_loss_mean(x, yd, tld, 0, 0.5).backward()
+
+        def stock():
+            x = xs[k[0] % len(xs)]; k[0] += 1
+            x.grad = None
+            r = F.cross_entropy(x.reshape(B * L, V), yd.reshape(-1), ignore_index=0, reduction='none')
+            (0.5 * torch.mean(r.view(B, L).sum(-1) / tld.float())).backward()
+            x.detach().argmax(-1)
+        lib.profile_start()
+        t = timeit(ours, iters=10, warm=3)
+        prof = lib.profile_stop()
+        kt = prof["b2asr_ce_loss_fwd_bwd"][1] / prof["b2asr_ce_loss_fwd_bwd"][0] * 1e-3
+        ts = timeit(stock, iters=10, warm=3)
+        nbytes = 8 * V * B * L
+        print("B=%2d L=%3d V=%4d: kernel %.1f us (with autograd %.1f us)  %.0f GB/s = %.2f of measured HBM peak; torch cross_entropy+argmax fwd+bwd %.1f us"
+              % (B, L, V, kt * 1e6, t * 1e6, nbytes / kt / 1e9, nbytes / kt / 1e9 / PEAK["hbm_gbs"], ts * 1e6))
+        del xs
+
+
+if which in ("ce", "all"):
+    bench_ce()
 if which in ("ctc", "all"):
     bench_ctc()
 if which in ("keys", "all"):

@@ -142,9 +142,47 @@ def beam_fixture(ref, ctc_w, lm_w, beam, seed):
                 lm_state_dict={k: v.clone() for k, v in lm.state_dict().items()}, lm_dims=(8, 8, V, 2), hyps=res)
 
 
+def seqloss_fixture(ref):
+    """The attention branch's loss exactly as the reference forms it (solver.py:90,149-155) plus the reference's
+    own cal_acc (postprocess.py:121-133) on the same logits; two vocabulary sizes, padded labels, one tie row."""
+    seed_all(11)
+    out = {}
+    for name, (B, L, V) in {'small': (4, 9, 31), 'wide': (3, 6, 1301)}.items():
+        att_pred = (torch.randn(B, L, V) * 3).requires_grad_(True)
+        lens = [L] + [int(v) for v in torch.randint(1, L + 1, (B - 1,))]
+        y = torch.zeros(B, L + 1, dtype=torch.long)
+        for b, n in enumerate(lens):
+            y[b, 1:n] = torch.randint(2, V, (n - 1,))
+            y[b, n] = 1                                                  # <eos>
+        with torch.no_grad():
+            hit = torch.rand(B, L) < 0.5                                 # make about half the steps "correct"
+            for b in range(B):
+                for t in range(L):
+                    if hit[b, t]:
+                        att_pred[b, t, y[b, t + 1]] += 20.0
+            att_pred[0, 1, 5] = att_pred[0, 1, 17] = att_pred[0, 1].max() + 1    # tie: argmax takes the first
+        ans_len = int(torch.max(torch.sum(y != 0, dim=-1)))
+        label = y[:, 1:ans_len + 1].contiguous()
+        seq_loss = torch.nn.CrossEntropyLoss(ignore_index=0, reduction='none')      # solver.py:90
+        b, t, c = att_pred.shape
+        rows = seq_loss(att_pred.view(b * t, c), label.view(-1))                    # solver.py:151
+        att_loss = torch.sum(rows.view(b, t), dim=-1) / torch.sum(y != 0, dim=-1).to(dtype=torch.float32)
+        att_loss = torch.mean(att_loss)                                             # solver.py:154
+        w = 0.5
+        ((1 - w) * att_loss).backward()                                             # solver.py:163,177
+        out[name] = dict(att_pred=att_pred.detach().clone(), y=y, label=label, rows=rows.detach().view(b, t),
+                         att_loss=att_loss.detach(), grad=att_pred.grad.clone(), upstream=1 - w,
+                         acc=float(ref.postprocess.cal_acc(att_pred, label)),
+                         argmax=torch.as_tensor(np.argmax(att_pred.detach().numpy(), axis=-1)))
+    return out
+
+
 def main():
     ref = reference_loader.load()
     os.makedirs(OUT, exist_ok=True)
+    if len(sys.argv) > 1 and sys.argv[1] == 'seqloss':      # add this fixture without regenerating the others
+        torch.save(seqloss_fixture(ref), os.path.join(OUT, 'seqloss.pt'))
+        return
     torch.save(attention_fixture(ref, 'loc'), os.path.join(OUT, 'attention_loc.pt'))
     torch.save(attention_fixture(ref, 'dot'), os.path.join(OUT, 'attention_dot.pt'))
     torch.save(prefix_fixture(ref), os.path.join(OUT, 'prefix.pt'))
@@ -152,6 +190,7 @@ def main():
     torch.save(beam_fixture(ref, 0.5, 0.5, 4, 21), os.path.join(OUT, 'beam_joint.pt'))
     torch.save(beam_fixture(ref, 0.0, 0.0, 3, 22), os.path.join(OUT, 'beam_att_only.pt'))
     torch.save(beam_fixture(ref, 0.3, 0.0, 5, 23), os.path.join(OUT, 'beam_ctc.pt'))
+    torch.save(seqloss_fixture(ref), os.path.join(OUT, 'seqloss.pt'))
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 
