@@ -52,6 +52,7 @@ _SIGNATURES = {
     "b2asr_lstm_cell_fwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_p]),
     "b2asr_lstm_cell_bwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_i64, c_p, c_i, c_i, c_p]),
     "b2asr_ce_loss_fwd_bwd": (c_i, [c_p, c_i64, c_p, c_i64, c_i, c_i, c_p, c_i64, c_f, c_p, c_p, c_p, c_i64, c_p, c_p]),
+    "b2asr_edit_distance": (c_i64, [c_p, c_i64, c_p, c_i64]),
     "b2asr_last_error": (ctypes.c_char_p, []),
     "b2asr_version": (c_i, []),
     "b2asr_arch": (c_i, []),

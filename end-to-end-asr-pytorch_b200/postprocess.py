@@ -5,8 +5,8 @@ hypothesis record).  Pure host code, same names and return conventions.
   cal_acc       postprocess.py:121-133  cal_cer      postprocess.py:135-146
   draw_att      postprocess.py:149-155  collapse_phn postprocess.py:158-169   trim_eos postprocess.py:171-177
 
-`editdistance` is absent from this image, so a small Levenshtein stands in (same `eval(a, b)`
-contract).  The device-resident beam search (beam.py) does not build Hypothesis objects while it
+`editdistance` is absent from this image; `edit_distance` (same `eval(a, b)` contract) runs the
+Levenshtein DP in the library's host C++ (csrc/host.cu).  The device-resident beam search (beam.py) does not build Hypothesis objects while it
 searches; it rebuilds them from the device history after the last step, with the same fields.
 """
 import os
@@ -15,16 +15,22 @@ import pickle
 import numpy as np
 import torch
 
+from . import _lib
+
 
 def edit_distance(a, b):
-    """Levenshtein distance between two sequences (stand-in for editdistance.eval)."""
-    prev = list(range(len(b) + 1))
-    for i, x in enumerate(a, 1):
-        cur = [i]
-        for j, y in enumerate(b, 1):
-            cur.append(min(prev[j] + 1, cur[j - 1] + 1, prev[j - 1] + (x != y)))
-        prev = cur
-    return prev[-1]
+    """Levenshtein distance between two sequences of hashable items -- `editdistance.eval(a, b)` as eval.py:17-18 and
+    cal_cer (postprocess.py:135-146) call it.  The items are numbered and the DP runs in the C++ of csrc/host.cu."""
+    import ctypes
+    ids = {}
+    ia = [ids.setdefault(x, len(ids)) for x in a]
+    ib = [ids.setdefault(x, len(ids)) for x in b]
+    arr_a = (ctypes.c_int32 * max(len(ia), 1))(*ia)
+    arr_b = (ctypes.c_int32 * max(len(ib), 1))(*ib)
+    d = _lib.lib().b2asr_edit_distance(ctypes.cast(arr_a, ctypes.c_void_p), len(ia), ctypes.cast(arr_b, ctypes.c_void_p), len(ib))
+    if d < 0:
+        raise ValueError("b2asr_edit_distance: bad argument")
+    return int(d)
 
 
 class Mapper():

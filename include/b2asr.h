@@ -251,6 +251,14 @@ int b2asr_ce_loss_fwd_bwd(const float* logits, int64_t stride_row, const int64_t
                           float* loss_rows, int64_t* argmax, float* grad, int64_t grad_stride_row,
                           float* loss, void* stream);
 
+/* ------------------------------------------------------------------------
+ * SURVEY.md section 8(f) rank 4 (host code, no device work): the Levenshtein distance that eval.py:17-18 and
+ * src/postprocess.py:135-146 (cal_cer) take from the third-party `editdistance` package -- `ed.eval(a, b)`.
+ * a [na], b [nb]: int32 ids of the sequence items (code points, or one id per distinct word); unit costs.
+ * Returns the distance, or -1 on a bad argument.
+ * ---------------------------------------------------------------------- */
+int64_t b2asr_edit_distance(const int32_t* a, int64_t na, const int32_t* b, int64_t nb);
+
 /* Debug aid, not part of the drop-in path: with B2ASR_ATT_TRACE=1 in the environment CTA 0 of every attention
  * launch stamps clock64() at its phase boundaries (forward: slots 0-9, backward: 16-27); this copies the first n
  * slots of the last launch to the host (synchronous). */

@@ -108,6 +108,21 @@ def test_hypothesis_addtopk_semantics():
 def test_edit_distance_and_eval_cli(tmp_path):
     pp = _m("postprocess")
     assert pp.edit_distance("kitten", "sitting") == 3 and pp.edit_distance([], [1, 2]) == 2
+    assert pp.edit_distance("", "") == 0 and pp.edit_distance("abc", "") == 3 and pp.edit_distance(["a b", "c"], ["c"]) == 1
+
+    def dp(a, b):                                   # textbook Wagner-Fischer, the definition editdistance implements
+        prev = list(range(len(b) + 1))
+        for i, x in enumerate(a, 1):
+            cur = [i]
+            for j, y in enumerate(b, 1):
+                cur.append(min(prev[j] + 1, cur[j - 1] + 1, prev[j - 1] + (x != y)))
+            prev = cur
+        return prev[-1]
+    rng = np.random.default_rng(0)
+    for _ in range(200):
+        a = rng.integers(0, 4, rng.integers(0, 30)).tolist()
+        b = rng.integers(0, 4, rng.integers(0, 30)).tolist()
+        assert pp.edit_distance(a, b) == dp(a, b) == pp.edit_distance(b, a)
     f = tmp_path / "decode.txt"
     f.write_text("the cat sat\tthe cat sat\nhello world\thello word\n")
     out = subprocess.run([sys.executable, os.path.join(ROOT, "eval.py"), "--file", str(f)], capture_output=True, text=True)
