@@ -40,6 +40,18 @@ class BeamIO(ctypes.Structure):
     ]
 
 
+class DecLoop(ctypes.Structure):
+    """Mirror of `b2asr_decloop` (include/b2asr.h); field order and types must match exactly."""
+    _fields_ = ([(n, ctypes.c_int32) for n in ("B", "T", "D", "A", "H", "L", "mode", "C", "Kw", "cluster")] +
+                [("scale", c_f), ("pad_", ctypes.c_int32)] +
+                [(n, c_p) for n in ("keys", "h", "lens", "w_phi", "w_conv", "w_lproj", "w_gen", "b_gen", "w_ctx")] +
+                [("w_ctx_ld", c_i64)] +
+                [(n, c_p) for n in ("w_hh", "b_ih", "b_hh", "h0", "c0", "att", "ctx", "q", "gates", "hs", "cs",
+                                    "d_hs", "d_h_last", "d_c_last", "d_gates", "d_ctx", "d_zq", "d_keys", "pgrad")] +
+                [("pgrad_stride", c_i64)] +
+                [(n, c_p) for n in ("d_prev", "d_s", "d_hrec", "d_c")])
+
+
 # name -> (restype, argtypes); must list every symbol include/b2asr.h declares.
 _SIGNATURES = {
     "b2asr_attn_keys": (c_i, [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_p]),
@@ -51,6 +63,9 @@ _SIGNATURES = {
     "b2asr_debug_beam_trace": (c_i, [ctypes.POINTER(ctypes.c_longlong), c_i]),
     "b2asr_lstm_cell_fwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_p]),
     "b2asr_lstm_cell_bwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_i64, c_p, c_i, c_i, c_p]),
+    "b2asr_decloop_size": (c_sz, []),
+    "b2asr_decoder_loop_fwd": (c_i, [ctypes.POINTER(DecLoop), c_p]),
+    "b2asr_decoder_loop_bwd": (c_i, [ctypes.POINTER(DecLoop), c_p]),
     "b2asr_ce_loss_fwd_bwd": (c_i, [c_p, c_i64, c_p, c_i64, c_i, c_i, c_p, c_i64, c_f, c_p, c_p, c_p, c_i64, c_p, c_p]),
     "b2asr_edit_distance": (c_i64, [c_p, c_i64, c_p, c_i64]),
     "b2asr_last_error": (ctypes.c_char_p, []),

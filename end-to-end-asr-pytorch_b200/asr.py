@@ -18,6 +18,7 @@ joint CTC/attention/LM beam step runs device-resident (beam.py).  There is no CP
 Attention or beam_decode: they raise if the tensors are not on a CUDA device.
 """
 import math
+import os
 import random
 
 import torch
@@ -26,7 +27,7 @@ import torch.nn.functional as F
 from torch.distributions.categorical import Categorical
 from torch.nn.utils.rnn import pack_padded_sequence, pad_packed_sequence
 
-from . import _attn, _dec
+from . import _attn, _dec, _decloop
 
 CTC_BEAM_RATIO = 1.5   # asr.py:15
 
@@ -338,15 +339,20 @@ class Attention(nn.Module):
         from . import _keys
         return _keys.project(listener_feature, self.psi.weight, self.psi.bias)
 
+    def prepare(self, listener_feature, state_len):
+        """First call after reset_enc_mem(): padding mask and cached key projection (asr.py:412-419)."""
+        if self.comp_listener_feature is None:
+            dev = listener_feature.device
+            self._lens_dev = _attn.lens_i32(state_len, dev)
+            ar = torch.arange(listener_feature.shape[1], device=dev)
+            self.state_mask = ar[None, :] >= self._lens_dev[:, None]            # asr.py:415-418
+            self.comp_listener_feature = self.project_keys(listener_feature) if self.proj else listener_feature
+        return self.comp_listener_feature
+
     def forward(self, decoder_state, listener_feature, state_len, scale=2.0):
         if not decoder_state.is_cuda:
             raise RuntimeError('Attention runs on the sm_100a kernels only (no CPU path); move the model to a CUDA device')
-        if self.comp_listener_feature is None:
-            self._lens_dev = _attn.lens_i32(state_len, decoder_state.device)
-            ar = torch.arange(listener_feature.shape[1], device=decoder_state.device)
-            self.state_mask = ar[None, :] >= self._lens_dev[:, None]            # asr.py:415-418
-            self.comp_listener_feature = self.project_keys(listener_feature) if self.proj else listener_feature
-        keys = self.comp_listener_feature
+        keys = self.prepare(listener_feature, state_len)
         p = self._params()
         prev = None
         if self.mode == 'loc' and self.prev_att is not None:
@@ -477,6 +483,12 @@ class Seq2Seq(nn.Module):
             x_emb = torch.cat([sos.unsqueeze(1), teacher[:, 1:decode_step, :]], dim=1) if decode_step > 1 else sos.unsqueeze(1)
             E = F.linear(x_emb, w_emb)                                  # [B, L, 4H]: every teacher-forced step at once
         h, c = self.decoder.state_list[0], self.decoder.cell_list[0]
+        # the reference draws one coin per step inside the loop (asr.py:96); nothing else touches Python's
+        # generator in between, so drawing the L coins up front yields the same sequence
+        coins = [random.random() <= tf_rate for _ in range(decode_step)] if teacher is not None else None
+        if (coins is not None and all(coins) and decode_step > 0 and self.attention.comp_listener_feature is None
+                and os.environ.get("B2ASR_DECLOOP", "1") != "0"):
+            return self._decode_loop_native(encode_feature, encode_len, E, h, c)
         if need_grad:
             ses = _dec.DecSession(cell, E, emb_dim, decode_step)
             token = _dec.DecOpen.apply(ses, E, cell.weight_ih, cell.weight_hh, cell.bias_ih, cell.bias_hh)
@@ -492,7 +504,7 @@ class Seq2Seq(nn.Module):
             outs.append(h)
             own = None
             if teacher is not None:
-                if not (random.random() <= tf_rate):                   # one coin per step (asr.py:96)
+                if not coins[t]:
                     chars[t] = self.char_trans(h)
                     own = F.linear(self.embed(Categorical(F.softmax(chars[t], dim=-1)).sample()), w_emb)
             else:
@@ -509,6 +521,21 @@ class Seq2Seq(nn.Module):
                     chars[t] = v
             att_output = torch.stack(chars, dim=1)
         return att_output, [torch.stack(maps, dim=1)]
+
+    def _decode_loop_native(self, encode_feature, encode_len, E, h0, c0):
+        """Every step teacher-forced: the whole loop and its backward are one native call each (_decloop.py,
+        csrc/decloop.cu); leaves the module state (decoder state, prev_att) as the per-step loop would."""
+        att_mod, cell = self.attention, self.decoder.layer0
+        keys = att_mod.prepare(encode_feature, encode_len)
+        p = att_mod._params()
+        meta = dict(mode=att_mod.mode, lens=att_mod._lens_dev, scale=2.0, emb_dim=self.embed.embedding_dim)
+        hs, att, h_last, c_last = _decloop.DecoderLoop.apply(
+            meta, keys, encode_feature, E, h0, c0, p['phi'], p['conv'], p['lproj'], p['gen_w'], p['gen_b'],
+            cell.weight_ih, cell.weight_hh, cell.bias_ih, cell.bias_hh)
+        self.decoder.state_list[0], self.decoder.cell_list[0] = h_last, c_last
+        if att_mod.mode == 'loc':
+            att_mod.prev_att = att[-1].unsqueeze(1)                              # asr.py:456
+        return self.char_trans(hs), [att.transpose(0, 1)]
 
     def beam_decode(self, audio_feature, decode_step, state_len, decode_beam_size):
         """Joint CTC/attention/RNN-LM beam search, device-resident (asr.py:155-258); returns the top

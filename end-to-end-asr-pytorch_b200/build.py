@@ -63,7 +63,7 @@ def build(force=False, verbose=False):
         if pr.returncode != 0:
             raise RuntimeError("nvcc failed on %s" % src)
         objs.append(obj)
-    cmd = [nvcc, "-shared", "-o", OUT] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-lcudart"]
+    cmd = [nvcc, "-shared", "-o", OUT] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-lcudart", "-lcublas"]
     subprocess.check_call(cmd)
     with open(STAMP, "w") as f:
         f.write(dig)

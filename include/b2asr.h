@@ -233,6 +233,44 @@ int b2asr_lstm_cell_bwd(const float* d_h, const float* d_c, const float* act, co
                         float* d_gates, int64_t dg_stride, float* d_c_prev, int B, int H, void* stream);
 
 /* ------------------------------------------------------------------------
+ * the whole teacher-forced decoder loop of Seq2Seq.forward, reference
+ * src/asr.py:84-108 (per step: Attention.forward :86, Speller.forward :87 = nn.LSTMCell on cat([last_char, context])
+ * :352-357), and its backward, enqueued by ONE call each on the caller's stream (no host work between steps).
+ * Per step: b2asr_attn_step_fwd -> gates[:,t] += ctx_t W_ctx^T + h_{t-1} W_hh^T (cuBLAS SGEMM) -> LSTM cell kernel;
+ * backward walks t = L-1..0: cell backward -> d_ctx_t, d_h_{t-1} (SGEMM) -> b2asr_attn_step_bwd.
+ * The embedding half of W_ih is applied by the caller for all steps at once (gates arrives holding it), char_trans
+ * and every weight gradient are batched GEMMs on the caller's side over the stacks below.
+ *
+ *   sizes     B rows, T frames, D encoder width, A attention width, H decoder width (= dec), L steps,
+ *             mode 0 dot / 1 loc, C conv channels, Kw conv half width, cluster (0 = choose), scale (2.0)
+ *   operands  keys [B,T,A], h [B,T,D], lens [B] int32, attention weights as in b2asr_attn_step_fwd,
+ *             w_ctx = &W_ih[0][emb] with row stride w_ctx_ld (= emb + D), w_hh [4H,H], b_ih/b_hh [4H] or NULL,
+ *             h0, c0 [B,H]
+ *   stacks    att [L,B,T], ctx [L,B,D], q [L,B,A], gates [B,L,4H] (in: embedding projection; out: activations
+ *             i,f,g,o), hs [B,L,H] (h_t, the input of char_trans), cs [L,B,H]
+ *   backward  d_hs [B,L,H] upstream of hs; d_h_last / d_c_last [B,H] upstream of the final state or NULL;
+ *             out: d_gates [B,L,4H] (= gradient of the embedding projection), d_ctx [L,B,D], d_zq [L,B,A],
+ *             d_keys [B,T,A] and pgrad (accumulated, caller zeroes), scratch d_prev [2,B,T], d_s [B,H],
+ *             d_hrec [B,H], d_c [2,B,H].  On return d_s + d_hrec is the gradient of h0 and d_c[0] that of c0.
+ * ---------------------------------------------------------------------- */
+typedef struct b2asr_decloop {
+  int32_t B, T, D, A, H, L, mode, C, Kw, cluster;
+  float scale;
+  int32_t pad_;
+  const float* keys; const float* h; const int32_t* lens;
+  const float* w_phi; const float* w_conv; const float* w_lproj; const float* w_gen; const float* b_gen;
+  const float* w_ctx; int64_t w_ctx_ld; const float* w_hh; const float* b_ih; const float* b_hh;
+  const float* h0; const float* c0;
+  float* att; float* ctx; float* q; float* gates; float* hs; float* cs;
+  const float* d_hs; const float* d_h_last; const float* d_c_last;
+  float* d_gates; float* d_ctx; float* d_zq; float* d_keys; float* pgrad; int64_t pgrad_stride;
+  float* d_prev; float* d_s; float* d_hrec; float* d_c;
+} b2asr_decloop;
+size_t b2asr_decloop_size(void);
+int b2asr_decoder_loop_fwd(const b2asr_decloop* io, void* stream);
+int b2asr_decoder_loop_bwd(const b2asr_decloop* io, void* stream);
+
+/* ------------------------------------------------------------------------
  * the attention branch's sequence loss, reference src/solver.py:90,149-155
  *     seq_loss = CrossEntropyLoss(ignore_index=0, reduction='none')
  *     att_loss = seq_loss(att_pred.view(b*t,c), label.view(-1))
