@@ -52,6 +52,13 @@ class DecLoop(ctypes.Structure):
                 [(n, c_p) for n in ("d_prev", "d_s", "d_hrec", "d_c")])
 
 
+class LstmSeq(ctypes.Structure):
+    """Mirror of `b2asr_lstm_seq` (include/b2asr.h); field order and types must match exactly."""
+    _fields_ = ([(n, ctypes.c_int32) for n in ("B", "T", "H", "ND")] +
+                [("gates", c_p), ("w_hh", c_p * 2), ("b_ih", c_p * 2), ("b_hh", c_p * 2),
+                 ("lens", c_p), ("out", c_p), ("cells", c_p), ("d_out", c_p), ("d_gates", c_p), ("status", c_p)])
+
+
 # name -> (restype, argtypes); must list every symbol include/b2asr.h declares.
 _SIGNATURES = {
     "b2asr_attn_keys": (c_i, [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_p]),
@@ -66,6 +73,9 @@ _SIGNATURES = {
     "b2asr_decloop_size": (c_sz, []),
     "b2asr_decoder_loop_fwd": (c_i, [ctypes.POINTER(DecLoop), c_p]),
     "b2asr_decoder_loop_bwd": (c_i, [ctypes.POINTER(DecLoop), c_p]),
+    "b2asr_lstm_seq_size": (c_sz, []),
+    "b2asr_lstm_seq_fwd": (c_i, [ctypes.POINTER(LstmSeq), c_p]),
+    "b2asr_lstm_seq_bwd": (c_i, [ctypes.POINTER(LstmSeq), c_p]),
     "b2asr_ce_loss_fwd_bwd": (c_i, [c_p, c_i64, c_p, c_i64, c_i, c_i, c_p, c_i64, c_f, c_p, c_p, c_p, c_i64, c_p, c_p]),
     "b2asr_edit_distance": (c_i64, [c_p, c_i64, c_p, c_i64]),
     "b2asr_last_error": (ctypes.c_char_p, []),
@@ -115,6 +125,9 @@ def lib():
         if L.b2asr_beam_io_size() != ctypes.sizeof(BeamIO):
             raise B2asrError("b2asr_beam_io layout mismatch: library %d bytes, binding %d bytes"
                              % (L.b2asr_beam_io_size(), ctypes.sizeof(BeamIO)))
+        if L.b2asr_lstm_seq_size() != ctypes.sizeof(LstmSeq):
+            raise B2asrError("b2asr_lstm_seq layout mismatch: library %d bytes, binding %d bytes"
+                             % (L.b2asr_lstm_seq_size(), ctypes.sizeof(LstmSeq)))
         _lib = L
     return _lib
 

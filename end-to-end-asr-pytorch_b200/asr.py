@@ -7,12 +7,13 @@ reference) and return conventions:
     .forward(audio_feature, decode_step, tf_rate, teacher, state_len)   asr.py:58-112
     .beam_decode(audio_feature, decode_step, state_len, decode_beam_size)  asr.py:155-258
     .load_lm / .clear_att                                       asr.py:50-56
-  Listener / RNNLayer / VGGExtractor                            asr.py:266-317, 466-558 (stock cuDNN)
+  Listener / RNNLayer / VGGExtractor                            asr.py:266-317, 466-558 (LSTM recurrence:
+                                                                csrc/enc.cu persistent kernels; VGG: cuDNN)
   Speller                                                       asr.py:320-357 (nn.LSTMCell)
   Attention                                                     asr.py:370-462 -> kernels (2a)/(2b)
 
-What runs where: the encoder LSTMs / VGG convs and the decoder LSTMCell stay library calls
-(cuDNN/cuBLAS), exactly as SURVEY.md section 2 scopes them.  Attention.forward is one fused kernel
+What runs where: the VGG convs and every GEMM stay library calls (cuDNN/cuBLAS), as SURVEY.md section 2
+scopes them; the Listener's LSTM recurrences run as one persistent launch per layer and direction pair (_enc.py).  Attention.forward is one fused kernel
 launch per decoder step (forward and backward), the key projection is its own kernel, and the
 joint CTC/attention/LM beam step runs device-resident (beam.py).  There is no CPU path through
 Attention or beam_decode: they raise if the tensors are not on a CUDA device.
@@ -27,9 +28,11 @@ import torch.nn.functional as F
 from torch.distributions.categorical import Categorical
 from torch.nn.utils.rnn import pack_padded_sequence, pad_packed_sequence
 
-from . import _attn, _dec, _decloop
+from . import _attn, _dec, _decloop, _enc
 
 CTC_BEAM_RATIO = 1.5   # asr.py:15
+# B2ASR_ENC=cudnn keeps the Listener's LSTMs on the library's per-frame path (A/B measurements only)
+ENCODER_NATIVE = os.environ.get("B2ASR_ENC", "native") != "cudnn"
 
 
 # --------------------------------------------------------------------------------------------
@@ -81,11 +84,18 @@ class RNNLayer(nn.Module):
     def forward(self, input_x, state=None, state_len=None, pack_input=False):
         if pack_input:
             assert state_len is not None, "Please specify seq len for pack_padded_sequence."
-            input_x = pack_padded_sequence(input_x, state_len, batch_first=True)
-        output, hidden = self.layer(input_x, state)
-        if pack_input:
-            output, lens = pad_packed_sequence(output, batch_first=True)
-            state_len = lens.tolist()
+        if pack_input and state is None and ENCODER_NATIVE and _enc.supported(self.layer, input_x):
+            # persistent recurrence kernels (csrc/enc.cu) instead of the library's per-frame launches; the final
+            # (h_n, c_n) pair is not materialised -- Listener.forward (asr.py:313) discards it
+            state_len = [int(n) for n in state_len]
+            output, hidden = _enc.lstm_layer(self.layer, input_x, state_len), None
+        else:
+            if pack_input:
+                input_x = pack_padded_sequence(input_x, state_len, batch_first=True)
+            output, hidden = self.layer(input_x, state)
+            if pack_input:
+                output, lens = pad_packed_sequence(output, batch_first=True)
+                state_len = lens.tolist()
         if self.sample_rate > 1:
             bs, ts, fd = output.shape
             if self.sample_style == 'drop':

@@ -271,6 +271,34 @@ int b2asr_decoder_loop_fwd(const b2asr_decloop* io, void* stream);
 int b2asr_decoder_loop_bwd(const b2asr_decloop* io, void* stream);
 
 /* ------------------------------------------------------------------------
+ * The recurrence of one Listener layer, reference src/asr.py:466-501 (RNNLayer.forward: pack_padded_sequence ->
+ * nn.LSTM(bidirectional, batch_first) -> pad_packed_sequence), the producer of the features kernels (1) and (2)
+ * consume.  One persistent cooperative launch walks every frame of both directions (csrc/enc.cu).
+ *   sizes     B rows (lengths sorted or not), T frames (= max length), H units per direction, ND directions (1|2)
+ *   gates     [B,T,ND,4H] in: x W_ih^T (the caller's single GEMM; biases NOT included); out: activations i,f,g,o
+ *             (PyTorch gate order) at valid frames -- the buffer the backward call reads
+ *   w_hh      per direction [4H,H]; b_ih/b_hh per direction [4H] or NULL
+ *   lens      [B] int32 valid frames per row
+ *   forward   out [B,T,ND*H] (h_t; zeros past a row's length, like pad_packed_sequence), cells [B,T,ND,H]
+ *   backward  d_out [B,T,ND*H] upstream of out -> d_gates [B,T,ND,4H] (pre-activation gradients, zeros past a
+ *             row's length): the caller forms dx, dW_ih, dW_hh, db with batched GEMMs over it
+ *   status    [1] int32 device word the caller zeroes once; set to 1 if a launch gave up waiting for a peer CTA
+ * out (forward) and d_gates (backward) double as the exchange buffers between CTAs and are overwritten entirely.
+ * ---------------------------------------------------------------------- */
+typedef struct b2asr_lstm_seq {
+  int32_t B, T, H, ND;
+  float* gates;
+  const float* w_hh[2]; const float* b_ih[2]; const float* b_hh[2];
+  const int32_t* lens;
+  float* out; float* cells;
+  const float* d_out; float* d_gates;
+  int32_t* status;
+} b2asr_lstm_seq;
+size_t b2asr_lstm_seq_size(void);
+int b2asr_lstm_seq_fwd(const b2asr_lstm_seq* io, void* stream);
+int b2asr_lstm_seq_bwd(const b2asr_lstm_seq* io, void* stream);
+
+/* ------------------------------------------------------------------------
  * the attention branch's sequence loss, reference src/solver.py:90,149-155
  *     seq_loss = CrossEntropyLoss(ignore_index=0, reduction='none')
  *     att_loss = seq_loss(att_pred.view(b*t,c), label.view(-1))

@@ -1,0 +1,109 @@
+"""Persistent Listener recurrence (csrc/enc.cu, _enc.py) against the CPU oracle = the reference's own call sequence
+pack_padded_sequence -> nn.LSTM -> pad_packed_sequence (src/asr.py:466-501) evaluated in float64.
+
+Tolerance: 1e-4 relative (the bar BASELINE.json states for the fp32 kernels) with an absolute floor of 1e-4 times the
+tensor's largest magnitude -- most padded/late-frame entries are exactly or nearly zero."""
+import importlib
+
+import pytest
+import torch
+
+from oracle import encoder_oracle as eo
+
+PKG = "end-to-end-asr-pytorch_b200"
+pytestmark = pytest.mark.gpu
+
+
+def _close(a, b, what, rtol=1e-4):
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    assert a.shape == b.shape, (what, a.shape, b.shape)
+    floor = rtol * float(b.abs().max()) + 1e-12
+    err = (a - b).abs()
+    bad = err > rtol * torch.maximum(a.abs(), b.abs()) + floor
+    assert not bool(bad.any()), "%s: max abs err %.3e (floor %.3e), %d bad" % (what, float(err.max()), floor, int(bad.sum()))
+
+
+def _lens(B, T, seed, sort=True):
+    g = torch.Generator().manual_seed(seed)
+    lens = torch.randint(max(1, T // 3), T + 1, (B,), generator=g).tolist()
+    lens[0] = T
+    return sorted(lens, reverse=True) if sort else lens
+
+
+CASES = [
+    # B, T, n_in, H, bidir
+    (3, 9, 8, 8, True),            # tiny, U=4 path with 2 CTAs per direction
+    (5, 37, 24, 20, True),         # H not a multiple of the CTA's unit count or of 32 (padded k-slices)
+    (16, 60, 39, 256, True),       # M1 layer 0 (timit_example.yaml: 39-dim MFCC, 256 units)
+    (32, 120, 120, 320, True),     # M2 layer 0 shape, shortened in time
+    (32, 50, 640, 320, True),      # M2 layers 1-4
+    (7, 33, 16, 64, False),        # unidirectional ('RNN' enc_type)
+    (40, 21, 12, 320, True),       # more rows than one cooperative launch holds -> two launches
+    (4, 1, 8, 16, True),           # single frame
+    (6, 25, 40, 512, True),        # U=8 path
+]
+
+
+@pytest.mark.parametrize("B,T,n_in,H,bidir", CASES)
+def test_lstm_layer_forward_backward_match_reference_call(B, T, n_in, H, bidir):
+    enc = importlib.import_module(PKG + "._enc")
+    dev = torch.device("cuda:0")
+    layer64 = eo.make_layer(n_in, H, bidir, seed=B * 1000 + T)
+    lens = _lens(B, T, seed=7 + B)
+    g = torch.Generator().manual_seed(3)
+    x64 = torch.randn(B, T, n_in, generator=g, dtype=torch.float64)
+    for b, n in enumerate(lens):
+        x64[b, n:] = 0
+    w64 = torch.randn(B, T, (2 if bidir else 1) * H, generator=g, dtype=torch.float64)
+    x64.requires_grad_(True)
+    ref = eo.reference_call(layer64, x64, lens)
+    (ref * w64).sum().backward()
+
+    layer = torch.nn.LSTM(n_in, H, bidirectional=bidir, num_layers=1, batch_first=True).to(dev)
+    layer.load_state_dict({k: v.float() for k, v in layer64.state_dict().items()})
+    x = x64.detach().float().to(dev).requires_grad_(True)
+    assert enc.supported(layer, x)
+    out = enc.lstm_layer(layer, x, lens)
+    (out * w64.float().to(dev)).sum().backward()
+    torch.cuda.synchronize()
+    enc.check_status(dev)
+    _close(out, ref, "out")
+    for b, n in enumerate(lens):
+        assert float(out[b, n:].abs().max() if n < T else 0.0) == 0.0       # pad_packed_sequence zeros
+    _close(x.grad, x64.grad, "dx")
+    for (name, p), (_, p64) in zip(layer.named_parameters(), layer64.named_parameters()):
+        _close(p.grad, p64.grad, "d" + name)
+
+
+def test_unsorted_lengths_and_listener_routes_through_kernel():
+    """Rows need not be sorted for the kernel (the packed reference needs them sorted: compare per permutation)."""
+    enc = importlib.import_module(PKG + "._enc")
+    asr = importlib.import_module(PKG + ".asr")
+    lib = importlib.import_module(PKG + "._lib")
+    dev = torch.device("cuda:0")
+    B, T, n_in, H = 6, 30, 12, 32
+    layer64 = eo.make_layer(n_in, H, True, seed=11)
+    lens = [30, 12, 25, 30, 7, 19]
+    g = torch.Generator().manual_seed(5)
+    x64 = torch.randn(B, T, n_in, generator=g, dtype=torch.float64)
+    for b, n in enumerate(lens):
+        x64[b, n:] = 0
+    order = sorted(range(B), key=lambda i: -lens[i])
+    ref_sorted = eo.reference_call(layer64, x64[order], [lens[i] for i in order])
+    ref = torch.empty_like(ref_sorted)
+    ref[order] = ref_sorted
+    layer = torch.nn.LSTM(n_in, H, bidirectional=True, batch_first=True).to(dev)
+    layer.load_state_dict({k: v.float() for k, v in layer64.state_dict().items()})
+    out = enc.lstm_layer(layer, x64.float().to(dev), lens)
+    torch.cuda.synchronize()
+    enc.check_status(dev)
+    _close(out, ref, "out (unsorted)")
+
+    # RNNLayer.forward (asr.py:466-501) takes the kernel path on CUDA and keeps the reference's return convention
+    rl = asr.RNNLayer(n_in, H, 2, sample_style="drop").to(dev)
+    rl.layer.load_state_dict(layer.state_dict())
+    before = lib.LAUNCHES
+    y, hidden, new_len = rl(x64[order].float().to(dev), state_len=[lens[i] for i in order], pack_input=True)
+    assert lib.LAUNCHES == before + 1 and hidden is None
+    assert new_len == [int(lens[i] / 2) for i in order]
+    _close(y, ref_sorted[:, ::2], "RNNLayer drop output")

@@ -125,3 +125,17 @@ def test_seq_loss_oracle_matches_reference_call(name):
     assert np.array_equal(argmax, g["argmax"].numpy())
     assert argmax[0, 1] == 5                                           # the tie row: first maximum
     assert abs(ceo.cal_acc(argmax, g["label"].numpy()) - g["acc"]) < 1e-12
+
+
+def test_encoder_oracle_reference_call_matches_restated_equations():
+    """oracle/encoder_oracle.py: the reference's packed nn.LSTM call (asr.py:466-501) == the LSTM equations
+    written out frame by frame, both directions, ragged lengths."""
+    from oracle import encoder_oracle as eo
+    for bidir in (True, False):
+        layer = eo.make_layer(6, 5, bidir, seed=2)
+        lens = [9, 7, 7, 2]
+        x = torch.randn(4, 9, 6, generator=torch.Generator().manual_seed(1), dtype=torch.float64)
+        a = eo.reference_call(layer, x, lens)
+        b = eo.restated(layer, x, lens)
+        assert a.shape == b.shape
+        assert float((a - b).abs().max()) < 1e-12
