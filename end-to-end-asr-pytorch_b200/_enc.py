@@ -20,17 +20,18 @@ _status = {}
 
 
 def status_word(device):
-    """The per-device int32 word the kernels raise when a launch gives up waiting for a peer CTA."""
+    """The per-device int32 words of the kernels: [0] raised when a launch gives up waiting for a peer CTA,
+    [1] / [2] counts of failed exchange polls forward / backward."""
     key = (device.type, device.index)
     if key not in _status:
-        _status[key] = torch.zeros(1, dtype=torch.int32, device=device)
+        _status[key] = torch.zeros(16, dtype=torch.int32, device=device)
     return _status[key]
 
 
 def check_status(device):
     """Synchronising check used by tests and by the trainer's NaN guard."""
     s = status_word(device)
-    if int(s.item()) != 0:
+    if int(s[0].item()) != 0:
         s.zero_()
         raise _lib.B2asrError("b2asr_lstm_seq: a persistent launch timed out waiting for a peer CTA")
 

@@ -74,6 +74,7 @@ _SIGNATURES = {
     "b2asr_decoder_loop_fwd": (c_i, [ctypes.POINTER(DecLoop), c_p]),
     "b2asr_decoder_loop_bwd": (c_i, [ctypes.POINTER(DecLoop), c_p]),
     "b2asr_lstm_seq_size": (c_sz, []),
+    "b2asr_lstm_seq_path": (c_i, [c_i]),
     "b2asr_lstm_seq_fwd": (c_i, [ctypes.POINTER(LstmSeq), c_p]),
     "b2asr_lstm_seq_bwd": (c_i, [ctypes.POINTER(LstmSeq), c_p]),
     "b2asr_ce_loss_fwd_bwd": (c_i, [c_p, c_i64, c_p, c_i64, c_i, c_i, c_p, c_i64, c_f, c_p, c_p, c_p, c_i64, c_p, c_p]),

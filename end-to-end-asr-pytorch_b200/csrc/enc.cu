@@ -13,15 +13,15 @@
 //   * per frame a CTA needs the whole previous h (forward, H floats per row) or the whole previous d_gates
 //     (backward, 4H floats per row).  They are exchanged through the output tensors themselves in L2: the call
 //     pre-fills them with a sentinel (0xFFFFFFFF, a NaN no arithmetic here produces), owners store their slice
-//     with st.global.cg, readers pull rows with 1-D bulk (TMA) copies and recompute if a NaN shows up in the
-//     result (a sentinel word arrived = the row was not complete yet).  No flags, no atomics, no fences: every
-//     32-bit word is its own ready bit.  Two CTAs of different row groups share an SM, so one group's exchange
+//     with st.global.cg, readers pull rows with 1-D bulk (TMA) copies and pull them again while a sentinel word
+//     sits in the staged rows (= some peer's slice has not landed yet; the scan is an unsigned max over the
+//     words).  No flags, no atomics, no fences: every 32-bit word is its own ready bit.  Two CTAs of different row groups share an SM, so one group's exchange
 //     latency hides under the other's FMAs;
 //   * rows past their length write zeros (pad_packed_sequence semantics) and keep a zero state, so the reverse
 //     direction starts exactly at each row's last valid frame.
-#include <cooperative_groups.h>
+#include <stdlib.h>
 
-#include "common.cuh"
+#include "enc.cuh"
 
 namespace b2asr {
 
@@ -30,34 +30,10 @@ namespace {
 constexpr unsigned kSentinelBits = 0xffffffffu;
 constexpr int kSpinLimit = 400000;          // bulk-copy retries per frame before the launch gives up (~0.5 s)
 
-struct SeqArgs {
-  int B, T, H, ND;
-  int Kp;                                    // padded reduction length in shared memory
-  float* gates;                              // [B,T,ND,4H]
-  const float* w_hh[2];
-  const float* b_ih[2];
-  const float* b_hh[2];
-  const int* lens;
-  float* out;                                // [B,T,ND*H]
-  float* cells;                              // [B,T,ND,H]
-  const float* d_out;                        // [B,T,ND*H]
-  float* d_gates;                            // [B,T,ND,4H]
-  int* status;                               // device word: 0 ok, 1 exchange timed out
-};
-
 __device__ __forceinline__ void st_cg(float* p, float v) { asm volatile("st.global.cg.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory"); }
 __device__ __forceinline__ int ld_status(const int* p) {
   int v; asm volatile("ld.volatile.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory"); return v;
 }
-__device__ __forceinline__ float sigmoid_f(float x) { return __fdividef(1.f, 1.f + ex2(-x * kLog2e)); }
-__device__ __forceinline__ bool is_sentinel4(const float4& v) {
-  return __float_as_uint(v.x) == kSentinelBits || __float_as_uint(v.y) == kSentinelBits ||
-         __float_as_uint(v.z) == kSentinelBits || __float_as_uint(v.w) == kSentinelBits;
-}
-__device__ __forceinline__ float dot4(const float4& a, const float4& b, float acc) {
-  acc = fmaf(a.x, b.x, acc); acc = fmaf(a.y, b.y, acc); acc = fmaf(a.z, b.z, acc); return fmaf(a.w, b.w, acc);
-}
-
 // ---------------------------------------------------------------------------------------------------------
 // forward: grid (NC, row groups, ND), block 8 k-slices x BS/4 row quads x U units
 // ---------------------------------------------------------------------------------------------------------
@@ -99,6 +75,8 @@ __global__ void __launch_bounds__(8 * (BS / 4) * U) lstm_seq_fwd_kernel(const Se
   const int rows = min(BS, a.B - b0);        // valid rows of this group (> 0 by construction of the grid)
   float c = 0.f;
   unsigned phase = 0;
+  int retries = 0;
+  long long cyc_wait = 0, cyc_mac = 0, cyc_rest = 0;
   __syncthreads();
 
   for (int s = 0; s < T; ++s) {
@@ -112,9 +90,10 @@ __global__ void __launch_bounds__(8 * (BS / 4) * U) lstm_seq_fwd_kernel(const Se
       for (int g = 0; g < 4; ++g) pre[g] = grow[(long long)g * H];
     }
     float acc[4][4];
-    int tries = 0;
-    while (true) {
-      if (s > 0) {
+    const long long c0 = clock64();
+    if (s > 0) {
+      int tries = 0;
+      while (true) {
         if (tid < 32) {                       // warp 0 posts the transaction count, then one row copy per lane
           if (tid == 0) mbar_expect_tx(&bar, (unsigned)(rows * H * 4));
           __syncwarp();
@@ -123,11 +102,30 @@ __global__ void __launch_bounds__(8 * (BS / 4) * U) lstm_seq_fwd_kernel(const Se
         }
         mbar_wait(&bar, phase);
         phase ^= 1u;
+        // a sentinel word anywhere in the staged rows = some peer's slice of h has not landed in L2 yet
+        unsigned m = 0u;
+        for (int idx = tid; idx < BS * Kp / 4; idx += NTHR) {
+          const uint4 q = reinterpret_cast<const uint4*>(h_s)[idx];
+          m = max(m, max(max(q.x, q.y), max(q.z, q.w)));
+        }
+        if (!__syncthreads_or(m == kSentinelBits)) break;
+        ++tries;
+        if ((tries & 63) == 0) {              // now and then: did a peer give up, or should we?
+          const int st = (tid == 0) ? ld_status(a.status) : 0;
+          if (__syncthreads_or(st != 0 || tries > kSpinLimit)) {
+            if (tid == 0) atomicExch(a.status, 1);
+            return;
+          }
+        }
       }
+      retries += tries;
+    }
+    const long long c1 = clock64();
 #pragma unroll
-      for (int i = 0; i < 4; ++i)
+    for (int i = 0; i < 4; ++i)
 #pragma unroll
-        for (int g = 0; g < 4; ++g) acc[i][g] = 0.f;
+      for (int g = 0; g < 4; ++g) acc[i][g] = 0.f;
+    {
       const float* hrow = h_s + (bg * 4) * Kp + 4 * ks;
       const float* wrow = W_s + (u * 4) * Kp + 4 * ks;
       for (int j = 0; j < Kp; j += 32) {
@@ -141,46 +139,32 @@ __global__ void __launch_bounds__(8 * (BS / 4) * U) lstm_seq_fwd_kernel(const Se
 #pragma unroll
           for (int g = 0; g < 4; ++g) acc[i][g] = dot4(hv[i], wv[g], acc[i][g]);
       }
-      // transposing butterfly over the 8 k-slices: 16 -> 8 -> 4 values, then a pair all-reduce
-      {
-        const bool hi = ks & 4;
+    }
+    __syncthreads();                          // every read of h_s is done before the next frame's copy lands
+    const long long c2 = clock64();
+    // transposing butterfly over the 8 k-slices: 16 -> 8 -> 4 values, then a pair all-reduce
+    {
+      const bool hi = ks & 4;
 #pragma unroll
-        for (int i = 0; i < 2; ++i)
-#pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            const float send = hi ? acc[i][g] : acc[i + 2][g];
-            const float keep = hi ? acc[i + 2][g] : acc[i][g];
-            acc[i][g] = keep + __shfl_xor_sync(kFull, send, 4);
-          }
-      }
-      {
-        const bool hi = ks & 2;
+      for (int i = 0; i < 2; ++i)
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
-          const float send = hi ? acc[0][g] : acc[1][g];
-          const float keep = hi ? acc[1][g] : acc[0][g];
-          acc[0][g] = keep + __shfl_xor_sync(kFull, send, 2);
+          const float send = hi ? acc[i][g] : acc[i + 2][g];
+          const float keep = hi ? acc[i + 2][g] : acc[i][g];
+          acc[i][g] = keep + __shfl_xor_sync(kFull, send, 4);
         }
-      }
-#pragma unroll
-      for (int g = 0; g < 4; ++g) acc[0][g] += __shfl_xor_sync(kFull, acc[0][g], 1);
-      const bool bad = active && (acc[0][0] != acc[0][0] || acc[0][1] != acc[0][1] || acc[0][2] != acc[0][2] ||
-                                  acc[0][3] != acc[0][3]);
-      if (!__syncthreads_or(bad)) break;     // also orders this frame's reads of h_s before the next copy
-      // slow path: a NaN in the sums.  Retry only if a sentinel word really sits in the staged rows.
-      bool found = false;
-      for (int idx = tid; idx < rows * (H >> 2); idx += NTHR) {
-        const int b = idx / (H >> 2), k4 = idx - b * (H >> 2);
-        found |= is_sentinel4(*reinterpret_cast<const float4*>(h_s + b * Kp + 4 * k4));
-      }
-      const int st = (tid == 0) ? ld_status(a.status) : 0;
-      const int verdict = __syncthreads_or((found ? 1 : 0) | (st ? 2 : 0) | ((tid == 0 && ++tries > kSpinLimit) ? 4 : 0));
-      if (verdict & 6) {                      // a peer timed out, or we did: flag it and leave
-        if (tid == 0) atomicExch(a.status, 1);
-        return;
-      }
-      if (!(verdict & 1)) break;              // genuine NaN in the data: propagate it like the library would
     }
+    {
+      const bool hi = ks & 2;
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        const float send = hi ? acc[0][g] : acc[1][g];
+        const float keep = hi ? acc[1][g] : acc[0][g];
+        acc[0][g] = keep + __shfl_xor_sync(kFull, send, 2);
+      }
+    }
+#pragma unroll
+    for (int g = 0; g < 4; ++g) acc[0][g] += __shfl_xor_sync(kFull, acc[0][g], 1);
     if (pw) {
       float h = 0.f;
       if (active) {
@@ -197,6 +181,11 @@ __global__ void __launch_bounds__(8 * (BS / 4) * U) lstm_seq_fwd_kernel(const Se
       }
       st_cg(a.out + ((long long)gb * T + t) * ldo + dir * H + unit, h);
     }
+    cyc_wait += c1 - c0; cyc_mac += c2 - c1; cyc_rest += clock64() - c2;
+  }
+  if (tid == 0 && retries) atomicAdd(a.status + 1, retries);      // diagnostics: failed exchange polls
+  if (tid == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) {   // CTA 0's cycle split (clock64)
+    a.status[4] = (int)cyc_wait; a.status[5] = (int)cyc_mac; a.status[6] = (int)cyc_rest;
   }
 }
 
@@ -236,6 +225,8 @@ __global__ void __launch_bounds__(32 * (BS / 4)) lstm_seq_bwd_kernel(const SeqAr
   if (wrows == 0) return;                                        // no barrier below: safe
   float dc = 0.f;
   unsigned phase = 0;
+  int retries = 0;
+  long long cyc_wait = 0, cyc_mac = 0, cyc_rest = 0;
   float* mydg = dg_s + (4 * w) * Kp;
 
   for (int s = 0; s < T; ++s) {
@@ -253,9 +244,10 @@ __global__ void __launch_bounds__(32 * (BS / 4)) lstm_seq_bwd_kernel(const SeqAr
       dh = __ldg(a.d_out + ((long long)gb * T + t) * ldo + dir * H + unit);
     }
     float v[32];
-    int tries = 0;
-    while (true) {
-      if (s > 0) {
+    const long long c0 = clock64();
+    if (s > 0) {
+      int tries = 0;
+      while (true) {
         if (lane == 0) mbar_expect_tx(&bars[w], (unsigned)(wrows * H4 * 4));
         __syncwarp();
         if (lane < wrows)
@@ -263,48 +255,51 @@ __global__ void __launch_bounds__(32 * (BS / 4)) lstm_seq_bwd_kernel(const SeqAr
                    (unsigned)(H4 * 4), &bars[w]);
         mbar_wait(&bars[w], phase);
         phase ^= 1u;
-      }
-#pragma unroll
-      for (int i = 0; i < 32; ++i) v[i] = 0.f;
-      for (int j = 4 * lane; j < Kp; j += 128) {
-        float4 dv[4], wv[U];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) dv[i] = *reinterpret_cast<const float4*>(mydg + i * Kp + j);
-#pragma unroll
-        for (int q = 0; q < U; ++q) wv[q] = *reinterpret_cast<const float4*>(Wt_s + q * Kp + j);
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-#pragma unroll
-          for (int q = 0; q < U; ++q) v[i * 8 + q] = dot4(dv[i], wv[q], v[i * 8 + q]);
-      }
-      // transposing butterfly over the 32 lanes: slot (row quad index, unit) = lane afterwards
-#pragma unroll
-      for (int m = 16, n = 16; m >= 1; m >>= 1, n >>= 1) {
-        const bool hi = lane & m;
-#pragma unroll
-        for (int i = 0; i < n; ++i) {
-          if ((i & 7) < U || ((i + n) & 7) < U) {                // slots of units >= U stay zero
-            const float send = hi ? v[i] : v[i + n];
-            const float keep = hi ? v[i + n] : v[i];
-            v[i] = keep + __shfl_xor_sync(kFull, send, m);
+        unsigned m = 0u;                      // sentinel scan of this warp's four staged rows
+        for (int idx = lane; idx < Kp; idx += 32) {
+          const uint4 q = reinterpret_cast<const uint4*>(mydg)[idx];
+          m = max(m, max(max(q.x, q.y), max(q.z, q.w)));
+        }
+        if (!__any_sync(kFull, m == kSentinelBits)) break;
+        ++tries;
+        if ((tries & 63) == 0) {
+          if (ld_status(a.status) != 0 || tries > kSpinLimit) {
+            if (lane == 0) atomicExch(a.status, 1);
+            return;
           }
         }
       }
-      const bool bad = active && v[0] != v[0];
-      if (!__any_sync(kFull, bad)) break;
-      bool found = false;
-      for (int idx = lane; idx < wrows * a.H; idx += 32) {       // H4/4 float4 per row
-        const int b = idx / a.H, k4 = idx - b * a.H;
-        found |= is_sentinel4(*reinterpret_cast<const float4*>(mydg + b * Kp + 4 * k4));
+      retries += tries;
+    }
+    const long long c1 = clock64();
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = 0.f;
+    for (int j = 4 * lane; j < Kp; j += 128) {
+      float4 dv[4], wv[U];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) dv[i] = *reinterpret_cast<const float4*>(mydg + i * Kp + j);
+#pragma unroll
+      for (int q = 0; q < U; ++q) wv[q] = *reinterpret_cast<const float4*>(Wt_s + q * Kp + j);
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int q = 0; q < U; ++q) v[i * 8 + q] = dot4(dv[i], wv[q], v[i * 8 + q]);
+    }
+    // transposing butterfly over the 32 lanes: slot (row quad index, unit) = lane afterwards
+#pragma unroll
+    for (int m = 16, n = 16; m >= 1; m >>= 1, n >>= 1) {
+      const bool hi = lane & m;
+#pragma unroll
+      for (int i = 0; i < n; ++i) {
+        if ((i & 7) < U || ((i + n) & 7) < U) {                // slots of units >= U stay zero
+          const float send = hi ? v[i] : v[i + n];
+          const float keep = hi ? v[i + n] : v[i];
+          v[i] = keep + __shfl_xor_sync(kFull, send, m);
+        }
       }
-      const int st = ld_status(a.status);
-      if (st || ++tries > kSpinLimit) {
-        if (lane == 0) atomicExch(a.status, 1);
-        return;
-      }
-      if (!__any_sync(kFull, found)) break;
     }
     __syncwarp();                             // every lane is done reading the staged rows before the next copy
+    const long long c2 = clock64();
     if (pw) {
       float di = 0.f, df = 0.f, dgg = 0.f, dob = 0.f;
       if (active) {
@@ -322,6 +317,11 @@ __global__ void __launch_bounds__(32 * (BS / 4)) lstm_seq_bwd_kernel(const SeqAr
       float* o = a.d_gates + grow;
       st_cg(o, di); st_cg(o + H, df); st_cg(o + 2ll * H, dgg); st_cg(o + 3ll * H, dob);
     }
+    cyc_wait += c1 - c0; cyc_mac += c2 - c1; cyc_rest += clock64() - c2;
+  }
+  if (lane == 0 && retries) atomicAdd(a.status + 2, retries);     // diagnostics: failed exchange polls
+  if (tid == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) {   // warp 0 of CTA 0: cycle split
+    a.status[8] = (int)cyc_wait; a.status[9] = (int)cyc_mac; a.status[10] = (int)cyc_rest;
   }
 }
 
@@ -434,6 +434,11 @@ int dispatch(const b2asr_lstm_seq* io, bool backward, cudaStream_t st) {
   }
 }
 
+// H in {256, 320} takes the cluster kernels (enc_cluster.cu) unless the L2-exchange path is forced
+// (b2asr_lstm_seq_path(1), or B2ASR_ENC_PATH=l2 in the environment at load time): A/B runs and tests
+int g_path = [] { const char* e = getenv("B2ASR_ENC_PATH"); return (e && e[0] == 'l') ? 1 : 0; }();
+bool use_cluster(int H) { return g_path == 0 && lstm_cluster_supported(H); }
+
 }  // namespace
 }  // namespace b2asr
 
@@ -441,10 +446,20 @@ using namespace b2asr;
 
 extern "C" size_t b2asr_lstm_seq_size(void) { return sizeof(b2asr_lstm_seq); }
 
+extern "C" int b2asr_lstm_seq_path(int path) {
+  const int prev = g_path;
+  if (path == 0 || path == 1) g_path = path;
+  return prev;
+}
+
 extern "C" int b2asr_lstm_seq_fwd(const b2asr_lstm_seq* io, void* stream) {
   const int rc = check(io, false);
   if (rc != B2ASR_OK) return rc;
   cudaStream_t st = (cudaStream_t)stream;
+  if (use_cluster(io->H)) {
+    const int rc2 = lstm_cluster_run(to_args(io), false, st);
+    if (rc2 != B2ASR_EUNSUPPORTED) return rc2;
+  }
   B2_CUDA_TRY(cudaMemsetAsync(io->out, 0xff, (size_t)io->B * io->T * io->ND * io->H * sizeof(float), st));
   return dispatch(io, false, st);
 }
@@ -453,6 +468,10 @@ extern "C" int b2asr_lstm_seq_bwd(const b2asr_lstm_seq* io, void* stream) {
   const int rc = check(io, true);
   if (rc != B2ASR_OK) return rc;
   cudaStream_t st = (cudaStream_t)stream;
+  if (use_cluster(io->H)) {
+    const int rc2 = lstm_cluster_run(to_args(io), true, st);
+    if (rc2 != B2ASR_EUNSUPPORTED) return rc2;
+  }
   B2_CUDA_TRY(cudaMemsetAsync(io->d_gates, 0xff, (size_t)io->B * io->T * io->ND * 4 * io->H * sizeof(float), st));
   return dispatch(io, true, st);
 }

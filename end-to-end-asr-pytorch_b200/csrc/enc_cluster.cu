@@ -1,0 +1,402 @@
+// Listener recurrence, cluster variant (H = 256 or 320: the shipped timit / libri encoders).  Same contract as
+// enc.cu (reference src/asr.py:466-501), but the per-frame exchange never leaves the SMs:
+//
+//   * one 16-CTA thread-block cluster per (direction, group of BS batch rows); CTA `rank` owns hidden units
+//     [rank*H/16, (rank+1)*H/16) and keeps its 4*H/16 rows of W_hh in REGISTERS for the whole sequence
+//     (80 floats per thread at H=320), its cell state / cell gradient in registers too;
+//   * forward is an all-gather: a CTA multiplies the full h_{t-1} (BS x H, local shared memory) with its gate
+//     rows, applies the cell, and sends its BS x H/16 slice of h_t to all 16 CTAs of the cluster;
+//   * backward is a reduce-scatter: a CTA multiplies ITS OWN d_gates of the previous frame (BS x 4H/16, local)
+//     with its rows of W_hh -- partial dh for all H units -- and sends each owner its BS x H/16 slice; the owner
+//     adds the 16 partials in rank order (bit-reproducible).  The d_gates themselves never cross CTAs, so both
+//     directions of the exchange move the same bytes per CTA and frame (forward h, backward partial dh);
+//   * the exchange is 16 bulk copies (cp.async.bulk shared::cta -> shared::cluster) per CTA and frame, each
+//     completing on the DESTINATION's mbarrier: a CTA waits on its own barrier until all 16 slices have landed.
+//     No cluster barrier and no thread-issued remote stores inside the loop; staging buffers are double-buffered
+//     and the data dependence itself is the flow control (a peer cannot produce frame t+1 before it has consumed
+//     everybody's frame t);
+//   * BS in {8, 12, 16}: the device holds only ~7 clusters of 16 CTAs at once (cudaOccupancyMaxActiveClusters),
+//     so the rows are split into as many groups as fit in one wave;
+//   * clusters are independent of each other (no cooperative launch).
+// ncu/clock64 evidence and the comparison with the L2-exchange kernels: DESIGN.md section 4, profiles/.
+#include <stdlib.h>
+
+#include "enc.cuh"
+
+namespace b2asr {
+
+namespace {
+
+constexpr int NCL = 16;                       // CTAs per cluster (non-portable size, allowed on sm_100)
+constexpr unsigned kWaitLimit = 1u << 22;     // mbarrier try_wait attempts before a CTA gives up
+
+__device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+
+// local shared memory -> shared memory of CTA `rank` of the cluster, completion on THAT CTA's mbarrier
+__device__ __forceinline__ void bulk_s2cluster(void* dst_local_alias, const void* src, unsigned bytes,
+                                               unsigned long long* bar_local_alias, unsigned rank) {
+  const unsigned d = dsmem_addr(dst_local_alias, rank), m = dsmem_addr(bar_local_alias, rank);
+  asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(d), "r"(smem_u32(src)), "r"(bytes), "r"(m) : "memory");
+}
+__device__ __forceinline__ bool mbar_wait_bounded(unsigned long long* bar, unsigned parity) {
+  const unsigned addr = smem_u32(bar);
+  for (unsigned i = 0; i < kWaitLimit; ++i) {
+    unsigned ok;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(addr), "r"(parity) : "memory");
+    if (ok) return true;
+  }
+  return false;
+}
+
+// floats between two ranks' chunks in the gathered h buffer: >= BS*UC and == UC (mod 32), so the 8 float4 a
+// quarter warp reads (32 consecutive k, up to three ranks) fall into 8 different bank groups
+constexpr int chunk_stride(int UC, int BS) { return UC + 32 * ((BS * UC - UC + 31) / 32); }
+
+// ---------------------------------------------------------------------------------------------------------
+// forward.  block = H threads: (unit u = tid/16 of this CTA's H/16, k-slice ks = tid%16)
+// ---------------------------------------------------------------------------------------------------------
+template <int H, int BS>
+__global__ void __launch_bounds__(H, 1) lstm_cl_fwd_kernel(const SeqArgs a) {
+  constexpr int UC = H / NCL;                 // units per CTA
+  constexpr int KJ = H / 64;                  // float4 per lane and row: lane ks reads k = 4*(ks + 16 j)
+  constexpr int RB = BS <= 8 ? 8 : 16;        // rows the 16-lane butterfly resolves (rows >= BS are zeros)
+  constexpr int S = chunk_stride(UC, BS);
+  constexpr int CH = BS * UC;                 // floats one CTA contributes per frame
+  static_assert(H % 64 == 0 && UC % 4 == 0 && BS % 4 == 0 && BS <= 16, "slices are whole float4s");
+  extern __shared__ __align__(128) float smem[];
+  __shared__ __align__(8) unsigned long long full[2];
+  float* h_s = smem;                          // [2][NCL][S]: chunk of rank r = [BS][UC]
+  float* stage = smem + 2 * NCL * S;          // [2][BS][UC]
+  const int tid = threadIdx.x, ks = tid & 15, u = tid >> 4;
+  const unsigned rank = cluster_ctarank();
+  const int dir = blockIdx.z, b0 = blockIdx.y * BS, u0 = (int)rank * UC;
+  const int T = a.T, ND = a.ND;
+  const long long ldo = (long long)ND * H;
+
+  float4 w[4][KJ];
+  int koff[KJ];
+  {
+    const float* W = a.w_hh[dir];
+#pragma unroll
+    for (int j = 0; j < KJ; ++j) {
+      const int k = 4 * (ks + 16 * j);
+      koff[j] = (k / UC) * S + (k % UC);
+#pragma unroll
+      for (int g = 0; g < 4; ++g)
+        w[g][j] = __ldg(reinterpret_cast<const float4*>(W + ((long long)g * H + u0 + u) * H + k));
+    }
+  }
+  for (int idx = tid; idx < NCL * S; idx += H) h_s[idx] = 0.f;
+  if (tid == 0) {
+    mbar_init(&full[0], 1);
+    mbar_init(&full[1], 1);
+    mbar_fence_init();
+    mbar_expect_tx(&full[1], NCL * CH * 4);   // frame 1 reads buffer 1, frame 2 buffer 0
+    mbar_expect_tx(&full[0], NCL * CH * 4);
+  }
+
+  // cell role: RB = 8 -> even lanes own row ks/2; RB = 16 -> every lane owns row ks
+  const int row = RB == 8 ? ks >> 1 : ks;
+  const bool pw = (RB == 8 ? (ks & 1) == 0 : true) && row < BS;
+  const int gb = b0 + row, unit = u0 + u;
+  const bool valid = pw && gb < a.B;
+  const int len = valid ? a.lens[gb] : 0;
+  float bias[4] = {0.f, 0.f, 0.f, 0.f};
+  if (valid) {
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      if (a.b_ih[dir]) bias[g] += a.b_ih[dir][g * H + unit];
+      if (a.b_hh[dir]) bias[g] += a.b_hh[dir][g * H + unit];
+    }
+  }
+  float c = 0.f;
+  unsigned phase = 0;                         // bit p = parity to wait for on full[p]
+  long long cyc_wait = 0, cyc_mac = 0, cyc_rest = 0;
+  __syncthreads();
+  cluster_arrive();
+  cluster_wait();                             // every CTA's barriers are armed before the first remote copy
+
+  for (int s = 0; s < T; ++s) {
+    const int t = dir ? T - 1 - s : s;
+    const int p = s & 1;
+    const bool active = valid && t < len;
+    float pre[4] = {0.f, 0.f, 0.f, 0.f};
+    float* grow = a.gates + (((long long)gb * T + t) * ND + dir) * 4 * H + unit;
+    if (active) {
+#pragma unroll
+      for (int g = 0; g < 4; ++g) pre[g] = grow[(long long)g * H];
+    }
+    const long long c0 = clock64();
+    if (s > 0) {                              // h_{t-1}: all 16 slices have landed in h_s[p]
+      if (!mbar_wait_bounded(&full[p], (phase >> p) & 1u)) { atomicExch(a.status, 1); return; }
+      phase ^= 1u << p;
+      if (tid == 0) mbar_expect_tx(&full[p], NCL * CH * 4);     // re-arm for frame s+2
+    }
+    const long long c1 = clock64();
+    float acc[RB][4];
+#pragma unroll
+    for (int b = 0; b < RB; ++b)
+#pragma unroll
+      for (int g = 0; g < 4; ++g) acc[b][g] = 0.f;
+    {
+      const float* hb = h_s + p * (NCL * S);
+#pragma unroll
+      for (int b = 0; b < BS; ++b) {
+#pragma unroll
+        for (int j = 0; j < KJ; ++j) {
+          const float4 hv = *reinterpret_cast<const float4*>(hb + koff[j] + b * UC);
+#pragma unroll
+          for (int g = 0; g < 4; ++g) acc[b][g] = dot4(hv, w[g][j], acc[b][g]);
+        }
+      }
+    }
+    // transposing butterfly over the 16 k-slices: RB rows -> one row per lane (pair)
+#pragma unroll
+    for (int m = 8, n = RB / 2; n >= 1; m >>= 1, n >>= 1) {
+      const bool hi = ks & m;
+#pragma unroll
+      for (int i = 0; i < n; ++i)
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          const float send = hi ? acc[i][g] : acc[i + n][g];
+          const float keep = hi ? acc[i + n][g] : acc[i][g];
+          acc[i][g] = keep + __shfl_xor_sync(kFull, send, m);
+        }
+    }
+    if (RB == 8) {
+#pragma unroll
+      for (int g = 0; g < 4; ++g) acc[0][g] += __shfl_xor_sync(kFull, acc[0][g], 1);
+    }
+    const long long c2 = clock64();
+    float sv[4] = {0.f, 0.f, 0.f, 0.f}, hval = 0.f;
+    if (pw) {
+      if (active) {
+        const float gi = sigmoid_f(acc[0][0] + pre[0] + bias[0]);
+        const float gf = sigmoid_f(acc[0][1] + pre[1] + bias[1]);
+        const float gg = tanh_acc(acc[0][2] + pre[2] + bias[2]);
+        const float go = sigmoid_f(acc[0][3] + pre[3] + bias[3]);
+        c = fmaf(gf, c, gi * gg);
+        hval = go * tanh_acc(c);
+        sv[0] = gi; sv[1] = gf; sv[2] = gg; sv[3] = go;
+      } else {
+        c = 0.f;
+      }
+      stage[p * CH + row * UC + u] = hval;
+    }
+    if (s + 1 < T) {
+      fence_proxy_async_smem();               // the cell outputs above are read by the async proxy below
+      __syncthreads();
+      // this CTA's BS x UC slice of h_t -> chunk `rank` of h_s[1-p] in every CTA of the cluster
+      if (tid < NCL)
+        bulk_s2cluster(h_s + (p ^ 1) * (NCL * S) + (int)rank * S, stage + p * CH, CH * 4, &full[p ^ 1], (unsigned)tid);
+    }
+    if (active) {
+      grow[0] = sv[0]; grow[(long long)H] = sv[1]; grow[2ll * H] = sv[2]; grow[3ll * H] = sv[3];
+      a.cells[(((long long)gb * T + t) * ND + dir) * H + unit] = c;
+    }
+    if (valid) a.out[((long long)gb * T + t) * ldo + dir * H + unit] = hval;
+    cyc_wait += c1 - c0; cyc_mac += c2 - c1; cyc_rest += clock64() - c2;
+  }
+  cluster_arrive();
+  cluster_wait();                             // nobody leaves while a copy may still read or write its shared memory
+  if (tid == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) {   // CTA 0's cycle split (clock64)
+    a.status[4] = (int)cyc_wait; a.status[5] = (int)cyc_mac; a.status[6] = (int)cyc_rest;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// backward.  block = H threads: thread j owns column j of this CTA's rows of W_hh (partial dh of unit j, BS rows);
+// the first BS*UC threads double as the cell-backward owners of (row, unit).
+// ---------------------------------------------------------------------------------------------------------
+template <int H, int BS>
+__global__ void __launch_bounds__(H, 1) lstm_cl_bwd_kernel(const SeqArgs a) {
+  constexpr int UC = H / NCL, LR = 4 * UC, CH = BS * UC;
+  static_assert(BS % 4 == 0 && BS * UC <= H, "cell owners fit the block");
+  extern __shared__ __align__(128) float smem[];
+  __shared__ __align__(8) unsigned long long full[2];
+  float* dgl = smem;                          // [LR][BS]   d_gates this CTA produced last frame: [gate*UC+uu][row]
+  float* Ps = smem + LR * BS;                 // [2][NCL][BS][UC]  partial dh, grouped by owner rank
+  float* recv = Ps + 2 * NCL * CH;            // [2][NCL][BS][UC]  partials of MY units from every rank
+  const int tid = threadIdx.x;
+  const unsigned rank = cluster_ctarank();
+  const int dir = blockIdx.z, b0 = blockIdx.y * BS, u0 = (int)rank * UC;
+  const int T = a.T, ND = a.ND;
+  const long long ldo = (long long)ND * H;
+
+  float wr[LR];
+  {
+    const float* W = a.w_hh[dir];
+#pragma unroll
+    for (int g = 0; g < 4; ++g)
+#pragma unroll
+      for (int uu = 0; uu < UC; ++uu) wr[g * UC + uu] = __ldg(W + ((long long)g * H + u0 + uu) * H + tid);
+  }
+  for (int idx = tid; idx < LR * BS; idx += H) dgl[idx] = 0.f;
+  if (tid == 0) {
+    mbar_init(&full[0], 1);
+    mbar_init(&full[1], 1);
+    mbar_fence_init();
+    mbar_expect_tx(&full[1], NCL * CH * 4);   // frame 1 uses buffer 1, frame 2 buffer 0
+    mbar_expect_tx(&full[0], NCL * CH * 4);
+  }
+  const int pdst = (tid / UC) * CH + (tid % UC);              // where column j's partials go inside a Ps buffer
+  const bool pw = tid < CH;
+  const int row = tid / UC, uu = tid - row * UC;
+  const int gb = b0 + row, unit = u0 + uu;
+  const bool valid = pw && gb < a.B;
+  const int len = valid ? a.lens[gb] : 0;
+  float dc = 0.f;
+  unsigned phase = 0;
+  long long cyc_wait = 0, cyc_mac = 0, cyc_rest = 0;
+  __syncthreads();
+  cluster_arrive();
+  cluster_wait();
+
+  for (int s = 0; s < T; ++s) {
+    const int t = dir ? s : T - 1 - s;
+    const int tcp = dir ? t + 1 : t - 1;      // frame whose cell state entered frame t in the forward walk
+    const int p = s & 1;
+    const bool active = valid && t < len;
+    float gi = 0.f, gf = 0.f, gg = 0.f, go = 0.f, ct = 0.f, cp = 0.f, dh = 0.f;
+    const long long grow = (((long long)gb * T + t) * ND + dir) * 4 * H + unit;
+    if (active) {
+      const float* g = a.gates + grow;
+      gi = __ldg(g); gf = __ldg(g + H); gg = __ldg(g + 2ll * H); go = __ldg(g + 3ll * H);
+      ct = __ldg(a.cells + (((long long)gb * T + t) * ND + dir) * H + unit);
+      if (tcp >= 0 && tcp < len) cp = __ldg(a.cells + (((long long)gb * T + tcp) * ND + dir) * H + unit);
+      dh = __ldg(a.d_out + ((long long)gb * T + t) * ldo + dir * H + unit);
+    }
+    const long long c0 = clock64();
+    long long c1 = c0, c2 = c0;
+    if (s > 0) {
+      float acc[BS];
+#pragma unroll
+      for (int b = 0; b < BS; ++b) acc[b] = 0.f;
+#pragma unroll
+      for (int lr = 0; lr < LR; ++lr) {
+#pragma unroll
+        for (int q = 0; q < BS / 4; ++q) {
+          const float4 d = *reinterpret_cast<const float4*>(dgl + lr * BS + 4 * q);
+          acc[4 * q] = fmaf(d.x, wr[lr], acc[4 * q]);
+          acc[4 * q + 1] = fmaf(d.y, wr[lr], acc[4 * q + 1]);
+          acc[4 * q + 2] = fmaf(d.z, wr[lr], acc[4 * q + 2]);
+          acc[4 * q + 3] = fmaf(d.w, wr[lr], acc[4 * q + 3]);
+        }
+      }
+      float* pb = Ps + p * (NCL * CH) + pdst;
+#pragma unroll
+      for (int b = 0; b < BS; ++b) pb[b * UC] = acc[b];
+      fence_proxy_async_smem();
+      __syncthreads();
+      c1 = clock64();
+      // reduce-scatter: the owner of units [d*UC, +UC) gets this CTA's partials for them, slot `rank`
+      if (tid < NCL)
+        bulk_s2cluster(recv + p * (NCL * CH) + (int)rank * CH, Ps + p * (NCL * CH) + tid * CH, CH * 4, &full[p], (unsigned)tid);
+      if (!mbar_wait_bounded(&full[p], (phase >> p) & 1u)) { atomicExch(a.status, 1); return; }
+      phase ^= 1u << p;
+      if (tid == 0) mbar_expect_tx(&full[p], NCL * CH * 4);     // re-arm for frame s+2
+      c2 = clock64();
+      if (pw) {
+        const float* rb = recv + p * (NCL * CH) + row * UC + uu;
+        float sum = 0.f;
+#pragma unroll
+        for (int src = 0; src < NCL; ++src) sum += rb[src * CH];
+        dh += sum;
+      }
+    }
+    if (pw) {
+      float di = 0.f, df = 0.f, dgg = 0.f, dob = 0.f;
+      if (active) {
+        const float tc = tanh_acc(ct);
+        const float dct = dc + dh * go * (1.f - tc * tc);
+        di = dct * gg * gi * (1.f - gi);
+        df = dct * cp * gf * (1.f - gf);
+        dgg = dct * gi * (1.f - gg * gg);
+        dob = dh * tc * go * (1.f - go);
+        dc = dct * gf;
+      } else {
+        dc = 0.f;
+      }
+      dgl[uu * BS + row] = di; dgl[(UC + uu) * BS + row] = df;
+      dgl[(2 * UC + uu) * BS + row] = dgg; dgl[(3 * UC + uu) * BS + row] = dob;
+      if (valid) {
+        float* o = a.d_gates + grow;
+        o[0] = di; o[(long long)H] = df; o[2ll * H] = dgg; o[3ll * H] = dob;
+      }
+    }
+    __syncthreads();
+    cyc_mac += c1 - c0; cyc_wait += c2 - c1; cyc_rest += clock64() - c2;
+  }
+  cluster_arrive();
+  cluster_wait();                             // nobody leaves while a copy may still read or write its shared memory
+  if (tid == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) {
+    a.status[8] = (int)cyc_wait; a.status[9] = (int)cyc_mac; a.status[10] = (int)cyc_rest;
+  }
+}
+
+template <int H, int BS>
+int launch(const SeqArgs& a, bool backward, cudaStream_t st, bool probe_only, int* fit_out) {
+  constexpr int UC = H / NCL;
+  void (*fn)(const SeqArgs) = backward ? lstm_cl_bwd_kernel<H, BS> : lstm_cl_fwd_kernel<H, BS>;
+  const size_t smem = backward ? (size_t)(4 * UC * BS + 4 * NCL * BS * UC) * sizeof(float)
+                               : (size_t)(2 * NCL * chunk_stride(UC, BS) + 2 * BS * UC) * sizeof(float);
+  B2_CUDA_TRY(cudaFuncSetAttribute((const void*)fn, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+  B2_CUDA_TRY(cudaFuncSetAttribute((const void*)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(NCL, (a.B + BS - 1) / BS, a.ND);
+  cfg.blockDim = dim3(H);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = NCL; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  int fit = 0;
+  if (cudaOccupancyMaxActiveClusters(&fit, (const void*)fn, &cfg) != cudaSuccess || fit < 1) {
+    (void)cudaGetLastError();
+    return B2ASR_EUNSUPPORTED;               // e.g. a partition without a 16-SM GPC: caller takes the L2 path
+  }
+  *fit_out = fit;
+  if (probe_only) return B2ASR_OK;
+  static const bool dbg = getenv("B2ASR_ENC_DEBUG") != nullptr;
+  if (dbg) fprintf(stderr, "lstm_cluster: H=%d BS=%d %s grid=(%d,%d,%d) max active clusters %d\n", H, BS,
+                   backward ? "bwd" : "fwd", cfg.gridDim.x, cfg.gridDim.y, cfg.gridDim.z, fit);
+  B2_CUDA_TRY(cudaLaunchKernelEx(&cfg, fn, a));
+  return B2ASR_OK;
+}
+
+template <int H>
+int run_cluster(const SeqArgs& a, bool backward, cudaStream_t st) {
+  // rows per cluster: the smallest of {8, 12, 16} whose clusters all fit in one wave (B2ASR_ENC_BS overrides)
+  static const int forced = [] { const char* e = getenv("B2ASR_ENC_BS"); return e ? atoi(e) : 0; }();
+  int fit = 0;
+  int rc = launch<H, 8>(a, backward, st, true, &fit);
+  if (rc != B2ASR_OK) return rc;
+  int bs = 16;
+  for (int cand : {8, 12, 16})
+    if (((a.B + cand - 1) / cand) * a.ND <= fit) { bs = cand; break; }
+  if (forced == 8 || forced == 12 || forced == 16) bs = forced;
+  switch (bs) {
+    case 8: return launch<H, 8>(a, backward, st, false, &fit);
+    case 12: return launch<H, 12>(a, backward, st, false, &fit);
+    default: return launch<H, 16>(a, backward, st, false, &fit);
+  }
+}
+
+}  // namespace
+
+bool lstm_cluster_supported(int H) { return H == 256 || H == 320; }
+
+int lstm_cluster_run(const SeqArgs& a, bool backward, cudaStream_t st) {
+  switch (a.H) {
+    case 256: return run_cluster<256>(a, backward, st);
+    case 320: return run_cluster<320>(a, backward, st);
+    default: return B2ASR_EUNSUPPORTED;
+  }
+}
+
+}  // namespace b2asr

@@ -282,7 +282,9 @@ int b2asr_decoder_loop_bwd(const b2asr_decloop* io, void* stream);
  *   forward   out [B,T,ND*H] (h_t; zeros past a row's length, like pad_packed_sequence), cells [B,T,ND,H]
  *   backward  d_out [B,T,ND*H] upstream of out -> d_gates [B,T,ND,4H] (pre-activation gradients, zeros past a
  *             row's length): the caller forms dx, dW_ih, dW_hh, db with batched GEMMs over it
- *   status    [1] int32 device word the caller zeroes once; set to 1 if a launch gave up waiting for a peer CTA
+ *   status    [16] int32 device words the caller zeroes once: [0] set to 1 if a launch gave up waiting for a peer
+ *             CTA; diagnostics: [1] / [2] running counts of failed exchange polls forward / backward, [4..6] /
+ *             [8..10] CTA 0's clock64 cycles of the last forward / backward launch in {exchange, MACs, rest}
  * out (forward) and d_gates (backward) double as the exchange buffers between CTAs and are overwritten entirely.
  * ---------------------------------------------------------------------- */
 typedef struct b2asr_lstm_seq {
@@ -297,6 +299,10 @@ typedef struct b2asr_lstm_seq {
 size_t b2asr_lstm_seq_size(void);
 int b2asr_lstm_seq_fwd(const b2asr_lstm_seq* io, void* stream);
 int b2asr_lstm_seq_bwd(const b2asr_lstm_seq* io, void* stream);
+/* Two implementations sit behind the calls above: 16-CTA clusters exchanging through distributed shared memory
+ * (H = 256 or 320, csrc/enc_cluster.cu) and a cooperative grid exchanging through L2 (any H, csrc/enc.cu).
+ * path 0 = choose (default), 1 = L2 exchange only; any other value only queries.  Returns the previous setting. */
+int b2asr_lstm_seq_path(int path);
 
 /* ------------------------------------------------------------------------
  * the attention branch's sequence loss, reference src/solver.py:90,149-155

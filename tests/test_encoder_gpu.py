@@ -35,17 +35,33 @@ CASES = [
     (3, 9, 8, 8, True),            # tiny, U=4 path with 2 CTAs per direction
     (5, 37, 24, 20, True),         # H not a multiple of the CTA's unit count or of 32 (padded k-slices)
     (16, 60, 39, 256, True),       # M1 layer 0 (timit_example.yaml: 39-dim MFCC, 256 units)
+    (13, 45, 30, 320, False),      # ragged row group (13 = 8 + 5 rows), one direction
     (32, 120, 120, 320, True),     # M2 layer 0 shape, shortened in time
     (32, 50, 640, 320, True),      # M2 layers 1-4
     (7, 33, 16, 64, False),        # unidirectional ('RNN' enc_type)
     (40, 21, 12, 320, True),       # more rows than one cooperative launch holds -> two launches
     (4, 1, 8, 16, True),           # single frame
+    (9, 1, 16, 320, True),         # single frame on the cluster kernels (no exchange at all)
+    (12, 2, 16, 256, True),        # two frames: one exchange, buffer 1 only
+    (20, 3, 24, 320, True),        # three frames: both staging buffers, 12 rows per cluster
     (6, 25, 40, 512, True),        # U=8 path
 ]
 
 
+@pytest.fixture(params=["auto", "l2"])
+def path(request):
+    """auto = cluster kernels (enc_cluster.cu) for H in {256, 320}, L2-exchange kernels (enc.cu) otherwise;
+    l2 = the L2-exchange kernels for every shape."""
+    lib = importlib.import_module(PKG + "._lib").lib()
+    prev = lib.b2asr_lstm_seq_path(1 if request.param == "l2" else 0)
+    yield request.param
+    lib.b2asr_lstm_seq_path(prev)
+
+
 @pytest.mark.parametrize("B,T,n_in,H,bidir", CASES)
-def test_lstm_layer_forward_backward_match_reference_call(B, T, n_in, H, bidir):
+def test_lstm_layer_forward_backward_match_reference_call(B, T, n_in, H, bidir, path):
+    if path == "l2" and H not in (256, 320):
+        pytest.skip("already the L2-exchange path under auto")
     enc = importlib.import_module(PKG + "._enc")
     dev = torch.device("cuda:0")
     layer64 = eo.make_layer(n_in, H, bidir, seed=B * 1000 + T)

@@ -26,7 +26,10 @@ def timed(fn, n=5):
 
 
 def main():
+    os.environ.setdefault("B2ASR_ENC_DEBUG", "1")
     B = int(sys.argv[1]) if len(sys.argv) > 1 else 32
+    if len(sys.argv) > 2:
+        lib.lib().b2asr_lstm_seq_path(1 if sys.argv[2] == "l2" else 0)
     dev = torch.device("cuda:0")
     torch.manual_seed(0)
     tot = {"native": 0.0, "cudnn": 0.0}
@@ -57,17 +60,22 @@ def main():
             with torch.no_grad():
                 pad_packed_sequence(layer(pack_padded_sequence(x, lens, batch_first=True))[0], batch_first=True)
 
+        enc.status_word(dev).zero_()
         lib.profile_start()
         native()
         prof = lib.profile_stop()
+        polls = enc.status_word(dev).tolist()
         a, b = timed(native), timed(cudnn)
         af, bf = timed(native_fwd), timed(cudnn_fwd)
         enc.check_status(dev)
         mult = 3 if name == "layer2-4" else 1
         tot["native"] += a * mult
         tot["cudnn"] += b * mult
-        print("%-9s T=%4d in=%3d  fwd+bwd native %7.2f ms  cudnn %7.2f ms | fwd only native %6.2f  cudnn %6.2f | recurrence kernels: %s"
-              % (name, T, n_in, a, b, af, bf, {k: "%.2f ms" % v[1] for k, v in prof.items()}), flush=True)
+        print("%-9s T=%4d in=%3d  fwd+bwd native %7.2f ms  cudnn %7.2f ms | fwd only native %6.2f  cudnn %6.2f | recurrence kernels: %s failed polls per CTA-frame fwd %.2f bwd %.2f"
+              % (name, T, n_in, a, b, af, bf, {k: "%.2f ms" % v[1] for k, v in prof.items()},
+                 polls[1] / (256.0 * T), polls[2] / (256.0 * 4 * T)), flush=True)
+        print("          CTA 0 us per frame {exchange, MACs, rest}: fwd %s  bwd %s" % (
+            ["%.2f" % (c / 1965.0 / T) for c in polls[4:7]], ["%.2f" % (c / 1965.0 / T) for c in polls[8:11]]), flush=True)
     print("five layers: native %.1f ms, cudnn %.1f ms" % (tot["native"], tot["cudnn"]))
 
 
