@@ -51,6 +51,18 @@ __device__ __forceinline__ bool mbar_wait_bounded(unsigned long long* bar, unsig
   return false;
 }
 
+// packed fp32: two FMAs per issue slot (SASS FFMA2); the loops below are issue-bound with 2.5 warps per scheduler
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 ffma2(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d;
+}
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+  f32x2 d; asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "f"(lo), "f"(hi)); return d;
+}
+__device__ __forceinline__ float sum2(f32x2 v) {
+  float lo, hi; asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); return lo + hi;
+}
+
 // floats between two ranks' chunks in the gathered h buffer: >= BS*UC and == UC (mod 32), so the 8 float4 a
 // quarter warp reads (32 consecutive k, up to three ranks) fall into 8 different bank groups
 constexpr int chunk_stride(int UC, int BS) { return UC + 32 * ((BS * UC - UC + 31) / 32); }
@@ -76,7 +88,7 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_fwd_kernel(const SeqArgs a) {
   const int T = a.T, ND = a.ND;
   const long long ldo = (long long)ND * H;
 
-  float4 w[4][KJ];
+  ulonglong2 w[4][KJ];                        // float4 of W_hh seen as two packed pairs (k, k+1), (k+2, k+3)
   int koff[KJ];
   {
     const float* W = a.w_hh[dir];
@@ -86,7 +98,7 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_fwd_kernel(const SeqArgs a) {
       koff[j] = (k / UC) * S + (k % UC);
 #pragma unroll
       for (int g = 0; g < 4; ++g)
-        w[g][j] = __ldg(reinterpret_cast<const float4*>(W + ((long long)g * H + u0 + u) * H + k));
+        w[g][j] = __ldg(reinterpret_cast<const ulonglong2*>(W + ((long long)g * H + u0 + u) * H + k));
     }
   }
   for (int idx = tid; idx < NCL * S; idx += H) h_s[idx] = 0.f;
@@ -119,15 +131,29 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_fwd_kernel(const SeqArgs a) {
   cluster_arrive();
   cluster_wait();                             // every CTA's barriers are armed before the first remote copy
 
+  // pre-activations are fetched one frame ahead (HBM latency ~1 us would otherwise sit on the critical path)
+  float pre[4] = {0.f, 0.f, 0.f, 0.f};
+  {
+    const int t0 = dir ? T - 1 : 0;
+    if (valid && t0 < len) {
+      const float* g0 = a.gates + (((long long)gb * T + t0) * ND + dir) * 4 * H + unit;
+#pragma unroll
+      for (int g = 0; g < 4; ++g) pre[g] = g0[(long long)g * H];
+    }
+  }
   for (int s = 0; s < T; ++s) {
     const int t = dir ? T - 1 - s : s;
     const int p = s & 1;
     const bool active = valid && t < len;
-    float pre[4] = {0.f, 0.f, 0.f, 0.f};
     float* grow = a.gates + (((long long)gb * T + t) * ND + dir) * 4 * H + unit;
-    if (active) {
+    float nxt[4] = {0.f, 0.f, 0.f, 0.f};
+    {
+      const int t1 = dir ? t - 1 : t + 1;
+      if (s + 1 < T && valid && t1 < len) {
+        const float* g1 = a.gates + (((long long)gb * T + t1) * ND + dir) * 4 * H + unit;
 #pragma unroll
-      for (int g = 0; g < 4; ++g) pre[g] = grow[(long long)g * H];
+        for (int g = 0; g < 4; ++g) nxt[g] = g1[(long long)g * H];
+      }
     }
     const long long c0 = clock64();
     if (s > 0) {                              // h_{t-1}: all 16 slices have landed in h_s[p]
@@ -138,19 +164,25 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_fwd_kernel(const SeqArgs a) {
     const long long c1 = clock64();
     float acc[RB][4];
 #pragma unroll
-    for (int b = 0; b < RB; ++b)
+    for (int b = BS; b < RB; ++b)
 #pragma unroll
       for (int g = 0; g < 4; ++g) acc[b][g] = 0.f;
     {
       const float* hb = h_s + p * (NCL * S);
 #pragma unroll
       for (int b = 0; b < BS; ++b) {
+        f32x2 a2[4] = {0ull, 0ull, 0ull, 0ull};      // (even-k, odd-k) partial sums of the row's four gates
 #pragma unroll
         for (int j = 0; j < KJ; ++j) {
-          const float4 hv = *reinterpret_cast<const float4*>(hb + koff[j] + b * UC);
+          const ulonglong2 hv = *reinterpret_cast<const ulonglong2*>(hb + koff[j] + b * UC);
 #pragma unroll
-          for (int g = 0; g < 4; ++g) acc[b][g] = dot4(hv, w[g][j], acc[b][g]);
+          for (int g = 0; g < 4; ++g) {
+            a2[g] = ffma2(hv.x, w[g][j].x, a2[g]);
+            a2[g] = ffma2(hv.y, w[g][j].y, a2[g]);
+          }
         }
+#pragma unroll
+        for (int g = 0; g < 4; ++g) acc[b][g] = sum2(a2[g]);
       }
     }
     // transposing butterfly over the 16 k-slices: RB rows -> one row per lane (pair)
@@ -198,6 +230,8 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_fwd_kernel(const SeqArgs a) {
       a.cells[(((long long)gb * T + t) * ND + dir) * H + unit] = c;
     }
     if (valid) a.out[((long long)gb * T + t) * ldo + dir * H + unit] = hval;
+#pragma unroll
+    for (int g = 0; g < 4; ++g) pre[g] = nxt[g];
     cyc_wait += c1 - c0; cyc_mac += c2 - c1; cyc_rest += clock64() - c2;
   }
   cluster_arrive();
@@ -217,7 +251,7 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_bwd_kernel(const SeqArgs a) {
   static_assert(BS % 4 == 0 && BS * UC <= H, "cell owners fit the block");
   extern __shared__ __align__(128) float smem[];
   __shared__ __align__(8) unsigned long long full[2];
-  float* dgl = smem;                          // [LR][BS]   d_gates this CTA produced last frame: [gate*UC+uu][row]
+  float* dgl = smem;                          // [LR/2][BS][2]  d_gates this CTA produced last frame: lr = gate*UC+uu -> [lr/2][row][lr%2]
   float* Ps = smem + LR * BS;                 // [2][NCL][BS][UC]  partial dh, grouped by owner rank
   float* recv = Ps + 2 * NCL * CH;            // [2][NCL][BS][UC]  partials of MY units from every rank
   const int tid = threadIdx.x;
@@ -226,13 +260,15 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_bwd_kernel(const SeqArgs a) {
   const int T = a.T, ND = a.ND;
   const long long ldo = (long long)ND * H;
 
-  float wr[LR];
+  static_assert(UC % 2 == 0 && BS % 2 == 0, "local gate rows and batch rows pair up");
+  f32x2 wr2[LR / 2];                          // column `tid` of local gate rows (2i, 2i+1), row lr = gate*UC + uu
   {
     const float* W = a.w_hh[dir];
 #pragma unroll
-    for (int g = 0; g < 4; ++g)
-#pragma unroll
-      for (int uu = 0; uu < UC; ++uu) wr[g * UC + uu] = __ldg(W + ((long long)g * H + u0 + uu) * H + tid);
+    for (int i = 0; i < LR / 2; ++i) {
+      const int g = (2 * i) / UC, uu = (2 * i) % UC;
+      wr2[i] = pack2(__ldg(W + ((long long)g * H + u0 + uu) * H + tid), __ldg(W + ((long long)g * H + u0 + uu + 1) * H + tid));
+    }
   }
   for (int idx = tid; idx < LR * BS; idx += H) dgl[idx] = 0.f;
   if (tid == 0) {
@@ -272,20 +308,21 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_bwd_kernel(const SeqArgs a) {
     const long long c0 = clock64();
     long long c1 = c0, c2 = c0;
     if (s > 0) {
-      float acc[BS];
+      f32x2 acc2[BS];                          // (even, odd local gate row) partial sums per batch row
 #pragma unroll
-      for (int b = 0; b < BS; ++b) acc[b] = 0.f;
+      for (int b = 0; b < BS; ++b) acc2[b] = 0ull;
 #pragma unroll
-      for (int lr = 0; lr < LR; ++lr) {
+      for (int i = 0; i < LR / 2; ++i) {
 #pragma unroll
-        for (int q = 0; q < BS / 4; ++q) {
-          const float4 d = *reinterpret_cast<const float4*>(dgl + lr * BS + 4 * q);
-          acc[4 * q] = fmaf(d.x, wr[lr], acc[4 * q]);
-          acc[4 * q + 1] = fmaf(d.y, wr[lr], acc[4 * q + 1]);
-          acc[4 * q + 2] = fmaf(d.z, wr[lr], acc[4 * q + 2]);
-          acc[4 * q + 3] = fmaf(d.w, wr[lr], acc[4 * q + 3]);
+        for (int q = 0; q < BS / 2; ++q) {
+          const ulonglong2 d = *reinterpret_cast<const ulonglong2*>(dgl + (i * BS + 2 * q) * 2);
+          acc2[2 * q] = ffma2(d.x, wr2[i], acc2[2 * q]);
+          acc2[2 * q + 1] = ffma2(d.y, wr2[i], acc2[2 * q + 1]);
         }
       }
+      float acc[BS];
+#pragma unroll
+      for (int b = 0; b < BS; ++b) acc[b] = sum2(acc2[b]);
       float* pb = Ps + p * (NCL * CH) + pdst;
 #pragma unroll
       for (int b = 0; b < BS; ++b) pb[b * UC] = acc[b];
@@ -320,8 +357,10 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_bwd_kernel(const SeqArgs a) {
       } else {
         dc = 0.f;
       }
-      dgl[uu * BS + row] = di; dgl[(UC + uu) * BS + row] = df;
-      dgl[(2 * UC + uu) * BS + row] = dgg; dgl[(3 * UC + uu) * BS + row] = dob;
+      {
+        float* dq = dgl + ((uu >> 1) * BS + row) * 2 + (uu & 1);          // local gate row lr = gate*UC + uu
+        dq[0] = di; dq[(UC / 2) * BS * 2] = df; dq[UC * BS * 2] = dgg; dq[(3 * UC / 2) * BS * 2] = dob;
+      }
       if (valid) {
         float* o = a.d_gates + grow;
         o[0] = di; o[(long long)H] = df; o[2ll * H] = dgg; o[3ll * H] = dob;
