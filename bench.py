@@ -108,11 +108,38 @@ def algorithmic_bytes(kernel, enc_lens, B, Tp, A, D, dec, V, labels, C=10, KW1=2
         return 4 * B * Tp * (D + A) + 4 * A * (D + 1)
     if kernel == "b2asr_ce_loss_fwd_bwd":    # decoder logits read once, finished gradient written once
         return 8 * V * B * max(labels) + 16 * B * max(labels)
+    if kernel == "b2asr_decoder_loop_fwd":   # L steps of (attention step + cell); GEMM weight reads not counted
+        L = max(labels)
+        return L * (algorithmic_bytes("b2asr_attn_step_fwd", enc_lens, B, Tp, A, D, dec, V, labels, C, KW1) +
+                    algorithmic_bytes("b2asr_lstm_cell_fwd", enc_lens, B, Tp, A, D, dec, V, labels, C, KW1))
+    if kernel == "b2asr_decoder_loop_bwd":
+        L = max(labels)
+        return L * (algorithmic_bytes("b2asr_attn_step_bwd", enc_lens, B, Tp, A, D, dec, V, labels, C, KW1) +
+                    algorithmic_bytes("b2asr_lstm_cell_bwd", enc_lens, B, Tp, A, D, dec, V, labels, C, KW1))
     if kernel == "b2asr_lstm_cell_fwd":      # gates read + activations written, c_prev in, h and c out
         return 4 * B * dec * (4 + 4 + 3)
     if kernel == "b2asr_lstm_cell_bwd":      # activations, c_prev, c, d_h, d_c in; d_gates, d_c_prev out
         return 4 * B * dec * (4 + 4 + 4 + 1)
     return 0
+
+
+def encoder_layer_bytes(frame_lens, dims, rates, nd, backward):
+    """Algorithmic bytes of the Listener recurrence (csrc/enc*.cu), averaged over the layers (one launch each):
+    forward  reads the pre-activations [sum T_b, ND, 4H], writes activations (same), cells [sum T_b, ND, H] and the
+             padded output [B, T, ND*H]; backward reads activations, two cell rows and d_out, writes the padded
+             d_gates [B, T, ND, 4H]; both read W_hh once.  Also returns the layers' recurrent flops."""
+    lens = list(frame_lens)
+    tot = flops = 0.0
+    for H, r in zip(dims, rates):
+        s, B, T = sum(lens), len(lens), max(lens)
+        w = 4 * nd * 4 * H * H
+        if backward:
+            tot += 4 * nd * s * (4 * H + 2 * H + H) + 4 * B * T * nd * 4 * H + w
+        else:
+            tot += 4 * nd * s * (4 * H + 4 * H + H) + 4 * B * T * nd * H + w
+        flops += 2.0 * s * nd * 4 * H * H
+        lens = [int(n / r) for n in lens]
+    return tot / len(dims), flops / len(dims)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -359,6 +386,7 @@ def run_native(args):
         peak, how = measured_peaks()
         att = cfg["attention"]
         D = int(cfg["encoder"]["dim"].split("_")[-1]) * 2
+        enc_flops = {}
         for name, (calls, tot_ms) in prof.items():
             per = tot_ms / max(calls, 1)
             # algorithmic bytes use the first batches' actual lengths (averaged over the profiled steps)
@@ -367,17 +395,30 @@ def run_native(args):
                 _, yb, lens = host[i % N_BATCHES]
                 enc = syn.encoder_lengths(WORKLOAD, lens)
                 labels = [int(v) for v in (yb != 0).sum(-1)]
-                ab += algorithmic_bytes(name, enc, B, max(enc), att["dim"], D, cfg["decoder"]["dim"], w["vocab"], labels)
+                if name.startswith("b2asr_lstm_seq"):
+                    e = cfg["encoder"]
+                    eb, ef = encoder_layer_bytes([int(n) for n in lens], [int(v) for v in e["dim"].split("_")],
+                                                 [int(v) for v in e["sample_rate"].split("_")],
+                                                 2 if "BiRNN" in e["enc_type"] else 1, name.endswith("bwd"))
+                    ab += eb
+                    enc_flops[name] = enc_flops.get(name, 0.0) + ef / prof_steps
+                else:
+                    ab += algorithmic_bytes(name, enc, B, max(enc), att["dim"], D, cfg["decoder"]["dim"], w["vocab"], labels)
             ab /= prof_steps
             kernels[name] = {"calls_per_step": calls / prof_steps, "avg_us": per * 1e3,
                              "ms_per_step": tot_ms / prof_steps, "alg_bytes_per_launch": ab,
                              "achieved_gbs": (ab / (per * 1e-3) / 1e9) if per > 0 else None}
         top = max(kernels, key=lambda k: kernels[k]["ms_per_step"])
         k = kernels[top]
+        note = "M2 keys+features (48 MB) are L2-resident across decoder steps; see DESIGN.md"
+        if top.startswith("b2asr_lstm_seq"):
+            fp32_peak = 148 * 128 * 2 * 1.965e9 / 1e12          # B200 FFMA peak, TFLOP/s
+            note = ("serial recurrence: T dependent frames per launch, bound by the fp32 FMA pipe of the 96 SMs the "
+                    "7 resident 16-CTA clusters occupy and by the per-frame exchange; recurrent MACs run at %.1f of "
+                    "%.1f fp32 TFLOP/s; see DESIGN.md section 4" % (enc_flops[top] / (k["avg_us"] * 1e-6) / 1e12, fp32_peak))
         roofline = {"kernel": top, "bound": "hbm", "achieved": k["achieved_gbs"], "peak": peak, "unit": "GB/s",
                     "frac": k["achieved_gbs"] / peak, "traffic": None, "peak_source": how,
-                    "share_of_step": k["ms_per_step"] / ms_step,
-                    "note": "M2 keys+features (48 MB) are L2-resident across decoder steps; see DESIGN.md"}
+                    "share_of_step": k["ms_per_step"] / ms_step, "note": note}
 
     decode = None
     if not args.no_decode:
