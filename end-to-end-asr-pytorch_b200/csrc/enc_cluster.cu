@@ -80,11 +80,14 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_fwd_kernel(const SeqArgs a) {
   static_assert(H % 64 == 0 && UC % 4 == 0 && BS % 4 == 0 && BS <= 16, "slices are whole float4s");
   extern __shared__ __align__(128) float smem[];
   __shared__ __align__(8) unsigned long long full[2];
+  __shared__ int lens_s[32];                  // lengths of this cluster's rows (0 past the batch)
   float* h_s = smem;                          // [2][NCL][S]: chunk of rank r = [BS][UC]
   float* stage = smem + 2 * NCL * S;          // [2][BS][UC]
   const int tid = threadIdx.x, ks = tid & 15, u = tid >> 4;
   const unsigned rank = cluster_ctarank();
-  const int dir = blockIdx.z, b0 = blockIdx.y * BS, u0 = (int)rank * UC;
+  // rows are dealt round-robin to the row groups (row r of group y = batch row y + r*groups): with a batch sorted
+  // by length every cluster gets the same mix of long and short rows
+  const int dir = blockIdx.z, b0 = blockIdx.y, bstep = gridDim.y, u0 = (int)rank * UC;
   const int T = a.T, ND = a.ND;
   const long long ldo = (long long)ND * H;
 
@@ -102,6 +105,7 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_fwd_kernel(const SeqArgs a) {
     }
   }
   for (int idx = tid; idx < NCL * S; idx += H) h_s[idx] = 0.f;
+  if (tid < 32) lens_s[tid] = (tid < BS && b0 + tid * bstep < a.B) ? a.lens[b0 + tid * bstep] : 0;
   if (tid == 0) {
     mbar_init(&full[0], 1);
     mbar_init(&full[1], 1);
@@ -113,7 +117,7 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_fwd_kernel(const SeqArgs a) {
   // cell role: RB = 8 -> even lanes own row ks/2; RB = 16 -> every lane owns row ks
   const int row = RB == 8 ? ks >> 1 : ks;
   const bool pw = (RB == 8 ? (ks & 1) == 0 : true) && row < BS;
-  const int gb = b0 + row, unit = u0 + u;
+  const int gb = b0 + row * bstep, unit = u0 + u;
   const bool valid = pw && gb < a.B;
   const int len = valid ? a.lens[gb] : 0;
   float bias[4] = {0.f, 0.f, 0.f, 0.f};
@@ -169,9 +173,12 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_fwd_kernel(const SeqArgs a) {
       for (int g = 0; g < 4; ++g) acc[b][g] = 0.f;
     {
       const float* hb = h_s + p * (NCL * S);
+      // rows past their length at this frame are skipped (their h_t is written as zero below): CTA-uniform mask
+      const unsigned rows_on = __ballot_sync(kFull, t < lens_s[tid & 31]);
 #pragma unroll
       for (int b = 0; b < BS; ++b) {
         f32x2 a2[4] = {0ull, 0ull, 0ull, 0ull};      // (even-k, odd-k) partial sums of the row's four gates
+        if ((rows_on >> b) & 1u) {
 #pragma unroll
         for (int j = 0; j < KJ; ++j) {
           const ulonglong2 hv = *reinterpret_cast<const ulonglong2*>(hb + koff[j] + b * UC);
@@ -180,6 +187,7 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_fwd_kernel(const SeqArgs a) {
             a2[g] = ffma2(hv.x, w[g][j].x, a2[g]);
             a2[g] = ffma2(hv.y, w[g][j].y, a2[g]);
           }
+        }
         }
 #pragma unroll
         for (int g = 0; g < 4; ++g) acc[b][g] = sum2(a2[g]);
@@ -251,12 +259,15 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_bwd_kernel(const SeqArgs a) {
   static_assert(BS % 4 == 0 && BS * UC <= H, "cell owners fit the block");
   extern __shared__ __align__(128) float smem[];
   __shared__ __align__(8) unsigned long long full[2];
+  __shared__ int lens_s[32];                  // lengths of this cluster's rows (0 past the batch)
   float* dgl = smem;                          // [LR/2][BS][2]  d_gates this CTA produced last frame: lr = gate*UC+uu -> [lr/2][row][lr%2]
   float* Ps = smem + LR * BS;                 // [2][NCL][BS][UC]  partial dh, grouped by owner rank
   float* recv = Ps + 2 * NCL * CH;            // [2][NCL][BS][UC]  partials of MY units from every rank
   const int tid = threadIdx.x;
   const unsigned rank = cluster_ctarank();
-  const int dir = blockIdx.z, b0 = blockIdx.y * BS, u0 = (int)rank * UC;
+  // rows are dealt round-robin to the row groups (row r of group y = batch row y + r*groups): with a batch sorted
+  // by length every cluster gets the same mix of long and short rows
+  const int dir = blockIdx.z, b0 = blockIdx.y, bstep = gridDim.y, u0 = (int)rank * UC;
   const int T = a.T, ND = a.ND;
   const long long ldo = (long long)ND * H;
 
@@ -271,6 +282,7 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_bwd_kernel(const SeqArgs a) {
     }
   }
   for (int idx = tid; idx < LR * BS; idx += H) dgl[idx] = 0.f;
+  if (tid < 32) lens_s[tid] = (tid < BS && b0 + tid * bstep < a.B) ? a.lens[b0 + tid * bstep] : 0;
   if (tid == 0) {
     mbar_init(&full[0], 1);
     mbar_init(&full[1], 1);
@@ -281,7 +293,7 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_bwd_kernel(const SeqArgs a) {
   const int pdst = (tid / UC) * CH + (tid % UC);              // where column j's partials go inside a Ps buffer
   const bool pw = tid < CH;
   const int row = tid / UC, uu = tid - row * UC;
-  const int gb = b0 + row, unit = u0 + uu;
+  const int gb = b0 + row * bstep, unit = u0 + uu;
   const bool valid = pw && gb < a.B;
   const int len = valid ? a.lens[gb] : 0;
   float dc = 0.f;
@@ -311,13 +323,18 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_bwd_kernel(const SeqArgs a) {
       f32x2 acc2[BS];                          // (even, odd local gate row) partial sums per batch row
 #pragma unroll
       for (int b = 0; b < BS; ++b) acc2[b] = 0ull;
+      // dgl rows of batch rows that were past their length at the previous frame are zero: skip the pair
+      const int tq = dir ? t - 1 : t + 1;
+      const unsigned rows_on = __ballot_sync(kFull, tq < lens_s[tid & 31]);
 #pragma unroll
-      for (int i = 0; i < LR / 2; ++i) {
+      for (int q = 0; q < BS / 2; ++q) {
+        if ((rows_on >> (2 * q)) & 3u) {
 #pragma unroll
-        for (int q = 0; q < BS / 2; ++q) {
-          const ulonglong2 d = *reinterpret_cast<const ulonglong2*>(dgl + (i * BS + 2 * q) * 2);
-          acc2[2 * q] = ffma2(d.x, wr2[i], acc2[2 * q]);
-          acc2[2 * q + 1] = ffma2(d.y, wr2[i], acc2[2 * q + 1]);
+          for (int i = 0; i < LR / 2; ++i) {
+            const ulonglong2 d = *reinterpret_cast<const ulonglong2*>(dgl + (i * BS + 2 * q) * 2);
+            acc2[2 * q] = ffma2(d.x, wr2[i], acc2[2 * q]);
+            acc2[2 * q + 1] = ffma2(d.y, wr2[i], acc2[2 * q + 1]);
+          }
         }
       }
       float acc[BS];
