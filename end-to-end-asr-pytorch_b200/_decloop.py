@@ -14,10 +14,15 @@ Scheduled sampling (a failed teacher-forcing coin) needs the output layer and a 
 batches take the per-step path; coins are drawn exactly as the reference draws them (asr.py:96).
 """
 import ctypes
+import os
 
 import torch
 
 from . import _attn, _lib
+
+
+# one SGEMM per step over [ctx_t | h_{t-1}] x [W_ctx | W_hh] instead of two (B2ASR_DEC_CAT=0: the two-GEMM form)
+FUSED_OPERANDS = os.environ.get("B2ASR_DEC_CAT", "1") != "0"
 
 
 def _p(t):
@@ -48,7 +53,13 @@ class DecoderLoop(torch.autograd.Function):
         h0, c0 = h0.detach().contiguous(), c0.detach().contiguous()
         f32 = dict(dtype=torch.float32, device=dev)
         att = torch.empty(L, B, T, **f32)
-        cvec = torch.empty(L, B, D, **f32)
+        xcat = w_cat = None
+        if FUSED_OPERANDS:
+            xcat = torch.empty(L, B, D + H, **f32)                         # [ctx_t | h_{t-1}]
+            w_cat = torch.cat([w_ih[:, emb:], w_hh], 1).contiguous()      # [4H, D+H]
+            cvec = xcat[:, :, :D]
+        else:
+            cvec = torch.empty(L, B, D, **f32)
         q = torch.empty(L, B, A, **f32)
         gates = E.detach().clone(memory_format=torch.contiguous_format)     # [B,L,4H] -> activations in place
         hs = torch.empty(B, L, H, **f32)
@@ -61,12 +72,12 @@ class DecoderLoop(torch.autograd.Function):
         wts = dict(w_phi=phi, w_conv=conv, w_lproj=lproj, w_gen=gen_w, b_gen=gen_b, b_ih=b_ih, b_hh=b_hh)
         wts = {k: (v.detach().contiguous() if v is not None else None) for k, v in wts.items()}
         w_ctx = w_ih[:, emb:]
-        _fill(io, keys=keys, h=h, lens=lens, w_ctx=w_ctx, w_hh=w_hh, h0=h0, c0=c0, att=att, ctx=cvec, q=q,
-              gates=gates, hs=hs, cs=cs, **wts)
+        _fill(io, keys=keys, h=h, lens=lens, w_ctx=w_ctx, w_hh=w_hh, h0=h0, c0=c0, att=att,
+              ctx=None if FUSED_OPERANDS else cvec, q=q, gates=gates, hs=hs, cs=cs, xcat=xcat, w_cat=w_cat, **wts)
         io.w_ctx_ld = w_ih.stride(0)
         _lib.call("b2asr_decoder_loop_fwd", 2 * L, _lib.lib().b2asr_decoder_loop_fwd, ctypes.byref(io), _lib.stream_ptr())
         ctx.io, ctx.meta = io, meta
-        ctx.keep = (keys, h, lens, w_ih, w_hh, wts, h0, c0, att, cvec, q, gates, hs, cs)   # what io points at
+        ctx.keep = (keys, h, lens, w_ih, w_hh, wts, h0, c0, att, cvec, q, gates, hs, cs, xcat, w_cat)   # what io points at
         ctx.mark_non_differentiable(att)
         ctx.set_materialize_grads(False)
         return hs, att, hs[:, L - 1].clone(), cs[L - 1].clone()
@@ -74,7 +85,7 @@ class DecoderLoop(torch.autograd.Function):
     @staticmethod
     def backward(ctx, d_hs, _d_att, d_h_last, d_c_last):
         io, meta = ctx.io, ctx.meta
-        keys, h, lens, w_ih, w_hh, wts, h0, c0, att, cvec, q, gates, hs, cs = ctx.keep
+        keys, h, lens, w_ih, w_hh, wts, h0, c0, att, cvec, q, gates, hs, cs, xcat, w_cat = ctx.keep
         B, T, D, A, H, L = io.B, io.T, io.D, io.A, io.H, io.L
         emb = int(meta["emb_dim"])
         loc = meta["mode"] == "loc"
@@ -84,7 +95,12 @@ class DecoderLoop(torch.autograd.Function):
         d_h_last = None if d_h_last is None else d_h_last.contiguous()
         d_c_last = None if d_c_last is None else d_c_last.contiguous()
         d_gates = torch.empty(B, L, 4 * H, **f32)
-        d_ctx = torch.empty(L, B, D, **f32)
+        d_xcat = None
+        if xcat is not None:
+            d_xcat = torch.empty(L, B, D + H, **f32)                       # [d_ctx_t | recurrent d_h_{t-1}]
+            d_ctx = d_xcat[:, :, :D]
+        else:
+            d_ctx = torch.empty(L, B, D, **f32)
         d_zq = torch.empty(L, B, A, **f32)
         d_keys = torch.zeros(B, T, A, **f32)
         pgrad = None
@@ -97,15 +113,16 @@ class DecoderLoop(torch.autograd.Function):
         d_s = torch.zeros(B, H, **f32)
         d_hrec = torch.zeros(B, H, **f32)
         d_c = torch.zeros(2, B, H, **f32)
-        _fill(io, d_hs=d_hs, d_h_last=d_h_last, d_c_last=d_c_last, d_gates=d_gates, d_ctx=d_ctx, d_zq=d_zq,
-              d_keys=d_keys, pgrad=pgrad, d_prev=d_prev, d_s=d_s, d_hrec=d_hrec, d_c=d_c)
+        _fill(io, d_hs=d_hs, d_h_last=d_h_last, d_c_last=d_c_last, d_gates=d_gates,
+              d_ctx=None if d_xcat is not None else d_ctx, d_zq=d_zq, d_keys=d_keys, pgrad=pgrad, d_prev=d_prev, d_s=d_s,
+              d_hrec=d_hrec, d_c=d_c, d_xcat=d_xcat)
         _lib.call("b2asr_decoder_loop_bwd", 2 * L, _lib.lib().b2asr_decoder_loop_bwd, ctypes.byref(io), _lib.stream_ptr())
 
         need = ctx.needs_input_grad
         g_keys = d_keys if need[1] else None
         g_h = torch.bmm(att.permute(1, 2, 0), d_ctx.transpose(0, 1)) if need[2] else None       # [B,T,L] x [B,L,D]
         g_E = d_gates if need[3] else None
-        g_h0 = (d_s + d_hrec) if need[4] else None
+        g_h0 = (d_s + (d_xcat[0, :, D:] if d_xcat is not None else d_hrec)) if need[4] else None
         g_c0 = d_c[0] if need[5] else None
         g_phi = g_conv = g_lproj = g_gw = g_gb = g_wih = g_whh = g_bih = g_bhh = None
         h_prev = torch.cat([h0.unsqueeze(1), hs[:, :L - 1]], dim=1)                               # [B,L,H]: s_t = h_{t-1}
@@ -119,11 +136,17 @@ class DecoderLoop(torch.autograd.Function):
             g_gw = tot[o_wg:o_bg].view(1, A)
             g_gb = tot[o_bg:o_bg + 1]
         dG2 = d_gates.view(B * L, 4 * H)
-        if need[11]:
+        if xcat is not None and need[11] and need[12]:
+            g_cat = dG2.t().mm(xcat.transpose(0, 1).reshape(B * L, D + H))          # [4H, D+H] = [dW_ctx | dW_hh]
             g_wih = torch.zeros(4 * H, emb + D, **f32)                 # the embedding half flows through E's own autograd
-            g_wih[:, emb:] = dG2.t().mm(cvec.transpose(0, 1).reshape(B * L, D))
-        if need[12]:
-            g_whh = dG2.t().mm(h_prev.reshape(B * L, H))
+            g_wih[:, emb:] = g_cat[:, :D]
+            g_whh = g_cat[:, D:]
+        else:
+            if need[11]:
+                g_wih = torch.zeros(4 * H, emb + D, **f32)
+                g_wih[:, emb:] = dG2.t().mm(cvec.transpose(0, 1).reshape(B * L, D))
+            if need[12]:
+                g_whh = dG2.t().mm(h_prev.reshape(B * L, H))
         if wts["b_ih"] is not None and (need[13] or need[14]):
             g_bih = dG2.sum(0)
             g_bhh = g_bih

@@ -49,7 +49,7 @@ class DecLoop(ctypes.Structure):
                 [(n, c_p) for n in ("w_hh", "b_ih", "b_hh", "h0", "c0", "att", "ctx", "q", "gates", "hs", "cs",
                                     "d_hs", "d_h_last", "d_c_last", "d_gates", "d_ctx", "d_zq", "d_keys", "pgrad")] +
                 [("pgrad_stride", c_i64)] +
-                [(n, c_p) for n in ("d_prev", "d_s", "d_hrec", "d_c")])
+                [(n, c_p) for n in ("d_prev", "d_s", "d_hrec", "d_c", "xcat", "w_cat", "d_xcat")])
 
 
 class LstmSeq(ctypes.Structure):
@@ -126,6 +126,9 @@ def lib():
         if L.b2asr_beam_io_size() != ctypes.sizeof(BeamIO):
             raise B2asrError("b2asr_beam_io layout mismatch: library %d bytes, binding %d bytes"
                              % (L.b2asr_beam_io_size(), ctypes.sizeof(BeamIO)))
+        if L.b2asr_decloop_size() != ctypes.sizeof(DecLoop):
+            raise B2asrError("b2asr_decloop layout mismatch: library %d bytes, binding %d bytes"
+                             % (L.b2asr_decloop_size(), ctypes.sizeof(DecLoop)))
         if L.b2asr_lstm_seq_size() != ctypes.sizeof(LstmSeq):
             raise B2asrError("b2asr_lstm_seq layout mismatch: library %d bytes, binding %d bytes"
                              % (L.b2asr_lstm_seq_size(), ctypes.sizeof(LstmSeq)))

@@ -21,6 +21,7 @@ struct AttnArgs {
   const float* wg; const float* bg;             // [A],[1]
   float scale;
   float* att; float* ctx;                       // [B,T],[B,D]
+  long long ctx_stride, dctx_stride;            // row strides of ctx (forward out) and d_ctx (backward in)
   float* q_out;                                 // [B,A] or nullptr
   int B, T, D, A, dec;
   // launch-derived
@@ -39,6 +40,10 @@ struct AttnArgs {
   float* pgrad; long long pgrad_stride;         // [B*CS, pgrad_stride] per-CTA parameter-gradient slots
   long long* trace;                             // debug: clock64 stamps of CTA 0's phases (nullptr = off)
 };
+
+// row stride the NEXT attention launch of this host thread uses for ctx (forward) / d_ctx (backward) instead of D;
+// set by the native decoder loop, which keeps [ctx_t | h_{t-1}] side by side for one GEMM; consumed by the launch
+extern thread_local long long g_attn_row_stride;
 
 #define B2_TRACE(p, slot) do { if ((p).trace && blockIdx.x == 0 && threadIdx.x == 0) (p).trace[slot] = clock64(); } while (0)
 long long* attn_trace_buffer();                // device buffer when B2ASR_ATT_TRACE is set, else nullptr

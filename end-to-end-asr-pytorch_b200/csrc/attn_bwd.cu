@@ -119,7 +119,7 @@ __global__ void __launch_bounds__(MAXNT, MINB) attn_step_bwd_kernel(AttnArgs p) 
 
   // ---- stage small operands: asynchronous 4-byte copies, all in flight at once, one wait ------------------
   for (int a = tid; a < A; a += NT) cp_async4(q_sm + a, p.q_saved + (long long)b * A + a);
-  for (int d = tid; d < D; d += NT) cp_async4(dctx + d, p.d_ctx + (long long)b * D + d);
+  for (int d = tid; d < D; d += NT) cp_async4(dctx + d, p.d_ctx + (long long)b * p.dctx_stride + d);
   for (int j = tid; j < nf; j += NT) {
     cp_async4(al + j, p.att_saved + (long long)b * T + t0 + j);
     if (p.d_att) cp_async4(de + j, p.d_att + (long long)b * T + t0 + j); else de[j] = 0.f;
@@ -470,6 +470,8 @@ extern "C" int b2asr_attn_step_bwd(int mode, const float* Wphi, const float* key
   a.d_keys = d_keys; a.dk_bstride = dk_bstride; a.d_prev_att = d_prev_att; a.d_zq = d_zq; a.d_s = d_s;
   a.pgrad = pgrad; a.pgrad_stride = pgrad_stride;
   a.B = B; a.T = T; a.D = D; a.A = A; a.dec = dec;
+  a.dctx_stride = g_attn_row_stride ? g_attn_row_stride : D;
+  g_attn_row_stride = 0;
   a.trace = attn_trace_buffer();
   // first pass fixes CS/NT/tiles, second pass sizes the ring with the backward's extra arrays
   size_t smem = 0;

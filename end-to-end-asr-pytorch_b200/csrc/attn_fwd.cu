@@ -304,7 +304,7 @@ __global__ void __launch_bounds__(MAXNT, MINB) attn_step_fwd_kernel(AttnArgs p) 
       float v = 0.f;
       if (CS > 1) { for (int rr = 0; rr < CS; ++rr) v += ld_dsmem_f32(dsmem_addr(ctxp + d, rr)); }
       else v = ctxp[d];
-      p.ctx[(long long)b * D + d] = v;
+      p.ctx[(long long)b * p.ctx_stride + d] = v;
     }
   }
   if (CS > 1) cluster_sync_all();     // #4: nobody leaves while its shared memory is still being read
@@ -377,6 +377,8 @@ int attn_launch(void (*kern)(AttnArgs), const AttnArgs& a, size_t smem, cudaStre
   return B2ASR_OK;
 }
 
+thread_local long long g_attn_row_stride = 0;
+
 }  // namespace b2asr
 
 using namespace b2asr;
@@ -399,6 +401,8 @@ extern "C" int b2asr_attn_step_fwd(int mode, const float* s, int64_t s_stride, c
   a.h = h; a.h_bstride = h_bstride; a.lens = lens; a.prev_att = prev_att; a.Wc = Wc; a.C = C; a.Kw = Kw;
   a.Wl = Wl; a.wg = wg; a.bg = bg; a.scale = scale; a.att = att; a.ctx = ctx; a.q_out = q_out;
   a.B = B; a.T = T; a.D = D; a.A = A; a.dec = dec;
+  a.ctx_stride = g_attn_row_stride ? g_attn_row_stride : D;
+  g_attn_row_stride = 0;
   a.trace = attn_trace_buffer();
   size_t smem = 0;
   int rc = attn_configure(a, cluster, 0, &smem);

@@ -22,10 +22,12 @@
 
 namespace b2asr {
 void lstm_cell_fwd_launch(float* gates, long long g_stride, const float* b_ih, const float* b_hh, const float* c_prev,
-                          float* h, long long h_stride, float* c, int B, int H, cudaStream_t st);
+                          float* h, long long h_stride, float* c, int B, int H, cudaStream_t st, float* h2,
+                          long long h2_stride);
 void lstm_cell_bwd_launch(const float* d_h, long long dh_stride, const float* d_h2, const float* d_h3, const float* d_c,
                           const float* act, long long act_stride, const float* c_prev, const float* c, float* d_gates,
-                          long long dg_stride, float* d_c_prev, int B, int H, cudaStream_t st);
+                          long long dg_stride, float* d_c_prev, int B, int H, cudaStream_t st, long long dh2_stride);
+extern thread_local long long g_attn_row_stride;   // attn.cuh: row stride of ctx / d_ctx for the next attention launch
 }  // namespace b2asr
 
 namespace {
@@ -73,10 +75,11 @@ int check_common(const b2asr_decloop* a) {
   B2_REQUIRE(a, B2ASR_EINVAL, "decoder loop: null argument block");
   B2_REQUIRE(a->B > 0 && a->T > 0 && a->D > 0 && a->A > 0 && a->H > 0 && a->L > 0, B2ASR_EINVAL,
              "decoder loop: bad sizes B=%d T=%d D=%d A=%d H=%d L=%d", a->B, a->T, a->D, a->A, a->H, a->L);
-  B2_REQUIRE(a->keys && a->h && a->lens && a->w_ctx && a->w_hh && a->h0 && a->c0, B2ASR_EINVAL,
+  B2_REQUIRE(a->keys && a->h && a->lens && ((a->w_ctx && a->w_hh) || a->w_cat) && a->h0 && a->c0, B2ASR_EINVAL,
              "decoder loop: null operand");
-  B2_REQUIRE(a->att && a->ctx && a->q && a->gates && a->hs && a->cs, B2ASR_EINVAL, "decoder loop: null step stack");
-  B2_REQUIRE(a->w_ctx_ld >= a->D, B2ASR_EINVAL, "decoder loop: w_ctx_ld smaller than D");
+  B2_REQUIRE(a->att && (a->ctx || (a->xcat && a->w_cat)) && a->q && a->gates && a->hs && a->cs, B2ASR_EINVAL,
+             "decoder loop: null step stack");
+  B2_REQUIRE(a->w_cat || a->w_ctx_ld >= a->D, B2ASR_EINVAL, "decoder loop: w_ctx_ld smaller than D");
   return B2ASR_OK;
 }
 
@@ -93,21 +96,34 @@ extern "C" int b2asr_decoder_loop_fwd(const b2asr_decloop* a, void* stream) {
   if (int rc = blas_handle(&hd, st)) return rc;
   const int B = a->B, T = a->T, D = a->D, A = a->A, H = a->H, L = a->L;
   const int64_t gl = (int64_t)L * 4 * H, hl = (int64_t)L * H;
+  // fused operand layout: xcat[t] = [ctx_t | h_{t-1}] (row stride D+H) against w_cat = [W_ctx | W_hh]: ONE GEMM per step
+  const bool cat = a->xcat && a->w_cat;
+  const int X = D + H;
+  if (cat)
+    B2_CUDA_TRY(cudaMemcpy2DAsync(a->xcat + D, sizeof(float) * X, a->h0, sizeof(float) * H, sizeof(float) * H, B,
+                                  cudaMemcpyDeviceToDevice, st));
   for (int t = 0; t < L; ++t) {
     const float* s = t ? a->hs + (int64_t)(t - 1) * H : a->h0;
     const int64_t ss = t ? hl : H;
     const float* prev = (a->mode == 1 && t) ? a->att + (int64_t)(t - 1) * B * T : nullptr;
     float* att_t = a->att + (int64_t)t * B * T;
-    float* ctx_t = a->ctx + (int64_t)t * B * D;
+    float* ctx_t = cat ? a->xcat + (int64_t)t * B * X : a->ctx + (int64_t)t * B * D;
+    if (cat) g_attn_row_stride = X;
     if (int rc = b2asr_attn_step_fwd(a->mode, s, ss, a->w_phi, a->keys, (int64_t)T * A, a->h, (int64_t)T * D, a->lens, prev,
                                      a->w_conv, a->C, a->Kw, a->w_lproj, a->w_gen, a->b_gen, a->scale, att_t, ctx_t,
                                      a->q + (int64_t)t * B * A, B, T, D, A, H, a->cluster, stream))
       return rc;
     float* g_t = a->gates + (int64_t)t * 4 * H;
-    B2_BLAS_TRY(gemm_xwt(hd, B, 4 * H, D, ctx_t, D, a->w_ctx, a->w_ctx_ld, 1.f, g_t, gl));
-    B2_BLAS_TRY(gemm_xwt(hd, B, 4 * H, H, s, ss, a->w_hh, H, 1.f, g_t, gl));
+    float* h2 = nullptr;
+    if (cat) {
+      B2_BLAS_TRY(gemm_xwt(hd, B, 4 * H, X, ctx_t, X, a->w_cat, X, 1.f, g_t, gl));
+      if (t + 1 < L) h2 = a->xcat + (int64_t)(t + 1) * B * X + D;
+    } else {
+      B2_BLAS_TRY(gemm_xwt(hd, B, 4 * H, D, ctx_t, D, a->w_ctx, a->w_ctx_ld, 1.f, g_t, gl));
+      B2_BLAS_TRY(gemm_xwt(hd, B, 4 * H, H, s, ss, a->w_hh, H, 1.f, g_t, gl));
+    }
     lstm_cell_fwd_launch(g_t, gl, a->b_ih, a->b_hh, t ? a->cs + (int64_t)(t - 1) * B * H : a->c0, a->hs + (int64_t)t * H, hl,
-                         a->cs + (int64_t)t * B * H, B, H, st);
+                         a->cs + (int64_t)t * B * H, B, H, st, h2, X);
   }
   B2_CUDA_TRY(cudaGetLastError());
   return B2ASR_OK;
@@ -115,8 +131,8 @@ extern "C" int b2asr_decoder_loop_fwd(const b2asr_decloop* a, void* stream) {
 
 extern "C" int b2asr_decoder_loop_bwd(const b2asr_decloop* a, void* stream) {
   if (int rc = check_common(a)) return rc;
-  B2_REQUIRE(a->d_hs && a->d_gates && a->d_ctx && a->d_zq && a->d_keys && a->d_s && a->d_hrec && a->d_c, B2ASR_EINVAL,
-             "decoder loop backward: null gradient buffer");
+  B2_REQUIRE(a->d_hs && a->d_gates && ((a->d_ctx && a->d_hrec) || (a->d_xcat && a->w_cat)) && a->d_zq && a->d_keys &&
+                 a->d_s && a->d_c, B2ASR_EINVAL, "decoder loop backward: null gradient buffer");
   B2_REQUIRE(a->mode != 1 || (a->pgrad && a->d_prev), B2ASR_EINVAL, "decoder loop backward: loc mode needs pgrad and d_prev");
   cudaStream_t st = (cudaStream_t)stream;
   cublasHandle_t hd;
@@ -124,17 +140,27 @@ extern "C" int b2asr_decoder_loop_bwd(const b2asr_decloop* a, void* stream) {
   const int B = a->B, T = a->T, D = a->D, A = a->A, H = a->H, L = a->L;
   const int64_t gl = (int64_t)L * 4 * H, hl = (int64_t)L * H;
   const bool loc = a->mode == 1;
+  // fused layout: d_xcat[t] = d_gates_t [W_ctx | W_hh] = [d_ctx_t | d_h_{t-1} (recurrent path)], ONE GEMM per step
+  const bool cat = a->d_xcat && a->w_cat;
+  const int X = D + H;
   for (int t = L - 1; t >= 0; --t) {
     const bool last = t == L - 1;
     float* dc_in = a->d_c + (int64_t)((t + 1) & 1) * B * H;
     float* dc_out = a->d_c + (int64_t)(t & 1) * B * H;
     float* dg_t = a->d_gates + (int64_t)t * 4 * H;
-    lstm_cell_bwd_launch(a->d_hs + (int64_t)t * H, hl, last ? a->d_h_last : a->d_hrec, last ? nullptr : a->d_s,
+    const float* d_rec = cat ? a->d_xcat + (int64_t)(t + 1) * B * X + D : a->d_hrec;   // only read when !last
+    lstm_cell_bwd_launch(a->d_hs + (int64_t)t * H, hl, last ? a->d_h_last : d_rec, last ? nullptr : a->d_s,
                          last ? a->d_c_last : dc_in, a->gates + (int64_t)t * 4 * H, gl,
-                         t ? a->cs + (int64_t)(t - 1) * B * H : a->c0, a->cs + (int64_t)t * B * H, dg_t, gl, dc_out, B, H, st);
-    float* dctx_t = a->d_ctx + (int64_t)t * B * D;
-    B2_BLAS_TRY(gemm_gw(hd, B, 4 * H, D, dg_t, gl, a->w_ctx, a->w_ctx_ld, dctx_t, D));
-    B2_BLAS_TRY(gemm_gw(hd, B, 4 * H, H, dg_t, gl, a->w_hh, H, a->d_hrec, H));
+                         t ? a->cs + (int64_t)(t - 1) * B * H : a->c0, a->cs + (int64_t)t * B * H, dg_t, gl, dc_out, B, H, st,
+                         (cat && !last) ? X : 0);
+    float* dctx_t = cat ? a->d_xcat + (int64_t)t * B * X : a->d_ctx + (int64_t)t * B * D;
+    if (cat) {
+      B2_BLAS_TRY(gemm_gw(hd, B, 4 * H, X, dg_t, gl, a->w_cat, X, dctx_t, X));
+      g_attn_row_stride = X;
+    } else {
+      B2_BLAS_TRY(gemm_gw(hd, B, 4 * H, D, dg_t, gl, a->w_ctx, a->w_ctx_ld, dctx_t, D));
+      B2_BLAS_TRY(gemm_gw(hd, B, 4 * H, H, dg_t, gl, a->w_hh, H, a->d_hrec, H));
+    }
     const float* prev = (loc && t) ? a->att + (int64_t)(t - 1) * B * T : nullptr;
     const float* d_att = (loc && !last) ? a->d_prev + (int64_t)((t + 1) & 1) * B * T : nullptr;
     float* d_prev = (loc && t) ? a->d_prev + (int64_t)(t & 1) * B * T : nullptr;

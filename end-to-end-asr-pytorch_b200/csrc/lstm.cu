@@ -17,7 +17,8 @@ __device__ __forceinline__ float sigmoid_acc(float x) { return __fdividef(1.f, 1
 __global__ void __launch_bounds__(256) lstm_cell_fwd_kernel(float* __restrict__ gates, long long g_stride,
                                                             const float* __restrict__ b_ih, const float* __restrict__ b_hh,
                                                             const float* __restrict__ c_prev, float* __restrict__ h,
-                                                            long long h_stride, float* __restrict__ c, int B, int H) {
+                                                            long long h_stride, float* __restrict__ c, int B, int H,
+                                                            float* __restrict__ h2, long long h2_stride) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= B * H) return;
   const int b = idx / H, u = idx - b * H;
@@ -32,7 +33,9 @@ __global__ void __launch_bounds__(256) lstm_cell_fwd_kernel(float* __restrict__ 
   const float cn = fmaf(f, c_prev[idx], i * gg);
   g[u] = i; g[H + u] = f; g[2 * H + u] = gg; g[3 * H + u] = o;
   c[idx] = cn;
-  h[(long long)b * h_stride + u] = o * tanh_acc(cn);
+  const float hn = o * tanh_acc(cn);
+  h[(long long)b * h_stride + u] = hn;
+  if (h2) h2[(long long)b * h2_stride + u] = hn;       // second copy next to the next step's context (decloop.cu)
 }
 
 // d_h = d_h[b*dh_stride+u] (+ d_h2 + d_h3 when given: the recurrent and the attention-query paths of the native loop)
@@ -41,7 +44,8 @@ __global__ void __launch_bounds__(256) lstm_cell_bwd_kernel(const float* __restr
                                                             const float* __restrict__ d_c, const float* __restrict__ act,
                                                             long long act_stride, const float* __restrict__ c_prev,
                                                             const float* __restrict__ c, float* __restrict__ d_gates,
-                                                            long long dg_stride, float* __restrict__ d_c_prev, int B, int H) {
+                                                            long long dg_stride, float* __restrict__ d_c_prev, int B, int H,
+                                                            long long dh2_stride) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= B * H) return;
   const int b = idx / H, u = idx - b * H;
@@ -49,7 +53,7 @@ __global__ void __launch_bounds__(256) lstm_cell_bwd_kernel(const float* __restr
   const float i = a[u], f = a[H + u], g = a[2 * H + u], o = a[3 * H + u];
   const float tc = tanh_acc(c[idx]);
   float dh = d_h ? d_h[(long long)b * dh_stride + u] : 0.f;
-  if (d_h2) dh += d_h2[idx];
+  if (d_h2) dh += d_h2[(long long)b * dh2_stride + u];
   if (d_h3) dh += d_h3[idx];
   const float dct = (d_c ? d_c[idx] : 0.f) + dh * o * (1.f - tc * tc);
   float* dg = d_gates + (long long)b * dg_stride;
@@ -62,17 +66,19 @@ __global__ void __launch_bounds__(256) lstm_cell_bwd_kernel(const float* __restr
 
 // launchers shared with the native decoder loop (decloop.cu)
 void lstm_cell_fwd_launch(float* gates, long long g_stride, const float* b_ih, const float* b_hh, const float* c_prev,
-                          float* h, long long h_stride, float* c, int B, int H, cudaStream_t st) {
+                          float* h, long long h_stride, float* c, int B, int H, cudaStream_t st, float* h2,
+                          long long h2_stride) {
   const int n = B * H;
-  lstm_cell_fwd_kernel<<<(n + 255) / 256, 256, 0, st>>>(gates, g_stride, b_ih, b_hh, c_prev, h, h_stride, c, B, H);
+  lstm_cell_fwd_kernel<<<(n + 255) / 256, 256, 0, st>>>(gates, g_stride, b_ih, b_hh, c_prev, h, h_stride, c, B, H, h2,
+                                                        h2_stride);
 }
 
 void lstm_cell_bwd_launch(const float* d_h, long long dh_stride, const float* d_h2, const float* d_h3, const float* d_c,
                           const float* act, long long act_stride, const float* c_prev, const float* c, float* d_gates,
-                          long long dg_stride, float* d_c_prev, int B, int H, cudaStream_t st) {
+                          long long dg_stride, float* d_c_prev, int B, int H, cudaStream_t st, long long dh2_stride) {
   const int n = B * H;
   lstm_cell_bwd_kernel<<<(n + 255) / 256, 256, 0, st>>>(d_h, dh_stride, d_h2, d_h3, d_c, act, act_stride, c_prev, c,
-                                                        d_gates, dg_stride, d_c_prev, B, H);
+                                                        d_gates, dg_stride, d_c_prev, B, H, dh2_stride ? dh2_stride : H);
 }
 
 }  // namespace b2asr
@@ -83,7 +89,7 @@ extern "C" int b2asr_lstm_cell_fwd(float* gates, const float* b_ih, const float*
                                    float* h, float* c, int B, int H, void* stream) {
   B2_REQUIRE(gates && c_prev && h && c, B2ASR_EINVAL, "lstm_cell_fwd: null pointer argument");
   B2_REQUIRE(B > 0 && H > 0, B2ASR_EINVAL, "lstm_cell_fwd: bad sizes B=%d H=%d", B, H);
-  lstm_cell_fwd_launch(gates, 4ll * H, b_ih, b_hh, c_prev, h, H, c, B, H, (cudaStream_t)stream);
+  lstm_cell_fwd_launch(gates, 4ll * H, b_ih, b_hh, c_prev, h, H, c, B, H, (cudaStream_t)stream, nullptr, 0);
   B2_CUDA_TRY(cudaGetLastError());
   return B2ASR_OK;
 }
@@ -93,7 +99,7 @@ extern "C" int b2asr_lstm_cell_bwd(const float* d_h, const float* d_c, const flo
   B2_REQUIRE(act && c_prev && c && d_gates && d_c_prev, B2ASR_EINVAL, "lstm_cell_bwd: null pointer argument");
   B2_REQUIRE(B > 0 && H > 0 && dg_stride >= 4 * (int64_t)H, B2ASR_EINVAL, "lstm_cell_bwd: bad sizes B=%d H=%d stride=%lld", B, H, (long long)dg_stride);
   lstm_cell_bwd_launch(d_h, H, nullptr, nullptr, d_c, act, 4ll * H, c_prev, c, d_gates, dg_stride, d_c_prev, B, H,
-                       (cudaStream_t)stream);
+                       (cudaStream_t)stream, 0);
   B2_CUDA_TRY(cudaGetLastError());
   return B2ASR_OK;
 }

@@ -265,6 +265,11 @@ typedef struct b2asr_decloop {
   const float* d_hs; const float* d_h_last; const float* d_c_last;
   float* d_gates; float* d_ctx; float* d_zq; float* d_keys; float* pgrad; int64_t pgrad_stride;
   float* d_prev; float* d_s; float* d_hrec; float* d_c;
+  /* optional fused operand layout (all three NULL = the two-GEMM form above): xcat [L,B,D+H] holds [ctx_t | h_{t-1}]
+   * side by side (ctx may then be NULL), w_cat [4H,D+H] = [W_ctx | W_hh] contiguous (w_ctx / w_hh may then be NULL),
+   * d_xcat [L,B,D+H] receives [d_ctx_t | recurrent d_h_{t-1}] (d_ctx / d_hrec may then be NULL; the recurrent part
+   * of the gradient of h0 is d_xcat[0][:, D:]).  One SGEMM per step and direction instead of two. */
+  float* xcat; const float* w_cat; float* d_xcat;
 } b2asr_decloop;
 size_t b2asr_decloop_size(void);
 int b2asr_decoder_loop_fwd(const b2asr_decloop* io, void* stream);
