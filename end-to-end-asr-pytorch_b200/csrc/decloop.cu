@@ -16,6 +16,8 @@
 // stays for scheduled sampling (a step whose coin fails needs the output layer and a sample before the next step).
 #include <cublas_v2.h>
 
+#include <stdlib.h>
+
 #include <mutex>
 
 #include "common.cuh"
@@ -28,6 +30,11 @@ void lstm_cell_bwd_launch(const float* d_h, long long dh_stride, const float* d_
                           const float* act, long long act_stride, const float* c_prev, const float* c, float* d_gates,
                           long long dg_stride, float* d_c_prev, int B, int H, cudaStream_t st, long long dh2_stride);
 extern thread_local long long g_attn_row_stride;   // attn.cuh: row stride of ctx / d_ctx for the next attention launch
+// deccell.cu: the forward step's GEMM + cell as one hand-written launch
+bool dec_step_supported(int H, int K, long long x_ld, long long g_ld);
+int dec_step_fwd(const float* x, long long x_ld, const float* w_cat, int B, int K, int H, float* gates, long long g_ld,
+                 const float* b_ih, const float* b_hh, const float* c_prev, float* c, float* h, long long h_ld, float* h2,
+                 long long h2_ld, cudaStream_t st);
 }  // namespace b2asr
 
 namespace {
@@ -71,6 +78,12 @@ inline cublasStatus_t gemm_gw(cublasHandle_t hd, int Bn, int N, int K, const flo
   return cublasSgemm(hd, CUBLAS_OP_N, CUBLAS_OP_N, K, Bn, N, &one, W, (int)ldw, G, (int)ldg, &zero, Cm, (int)ldc);
 }
 
+// B2ASR_DEC_STEP=0 keeps the per-step products on cuBLAS (A/B runs)
+bool fused_step_enabled() {
+  static const bool on = [] { const char* e = getenv("B2ASR_DEC_STEP"); return !(e && e[0] == '0'); }();
+  return on;
+}
+
 int check_common(const b2asr_decloop* a) {
   B2_REQUIRE(a, B2ASR_EINVAL, "decoder loop: null argument block");
   B2_REQUIRE(a->B > 0 && a->T > 0 && a->D > 0 && a->A > 0 && a->H > 0 && a->L > 0, B2ASR_EINVAL,
@@ -99,6 +112,7 @@ extern "C" int b2asr_decoder_loop_fwd(const b2asr_decloop* a, void* stream) {
   // fused operand layout: xcat[t] = [ctx_t | h_{t-1}] (row stride D+H) against w_cat = [W_ctx | W_hh]: ONE GEMM per step
   const bool cat = a->xcat && a->w_cat;
   const int X = D + H;
+  const bool fused = cat && fused_step_enabled() && dec_step_supported(H, X, X, gl);
   if (cat)
     B2_CUDA_TRY(cudaMemcpy2DAsync(a->xcat + D, sizeof(float) * X, a->h0, sizeof(float) * H, sizeof(float) * H, B,
                                   cudaMemcpyDeviceToDevice, st));
@@ -116,8 +130,15 @@ extern "C" int b2asr_decoder_loop_fwd(const b2asr_decloop* a, void* stream) {
     float* g_t = a->gates + (int64_t)t * 4 * H;
     float* h2 = nullptr;
     if (cat) {
-      B2_BLAS_TRY(gemm_xwt(hd, B, 4 * H, X, ctx_t, X, a->w_cat, X, 1.f, g_t, gl));
       if (t + 1 < L) h2 = a->xcat + (int64_t)(t + 1) * B * X + D;
+      if (fused) {                              // GEMM + cell in one launch (deccell.cu)
+        if (int rc = dec_step_fwd(ctx_t, X, a->w_cat, B, X, H, g_t, gl, a->b_ih, a->b_hh,
+                                  t ? a->cs + (int64_t)(t - 1) * B * H : a->c0, a->cs + (int64_t)t * B * H,
+                                  a->hs + (int64_t)t * H, hl, h2, X, st))
+          return rc;
+        continue;
+      }
+      B2_BLAS_TRY(gemm_xwt(hd, B, 4 * H, X, ctx_t, X, a->w_cat, X, 1.f, g_t, gl));
     } else {
       B2_BLAS_TRY(gemm_xwt(hd, B, 4 * H, D, ctx_t, D, a->w_ctx, a->w_ctx_ld, 1.f, g_t, gl));
       B2_BLAS_TRY(gemm_xwt(hd, B, 4 * H, H, s, ss, a->w_hh, H, 1.f, g_t, gl));
@@ -155,6 +176,7 @@ extern "C" int b2asr_decoder_loop_bwd(const b2asr_decloop* a, void* stream) {
                          (cat && !last) ? X : 0);
     float* dctx_t = cat ? a->d_xcat + (int64_t)t * B * X : a->d_ctx + (int64_t)t * B * D;
     if (cat) {
+      // stays on cuBLAS: a hand-written kernel over the transposed weights did not beat its split-K (deccell.cu)
       B2_BLAS_TRY(gemm_gw(hd, B, 4 * H, X, dg_t, gl, a->w_cat, X, dctx_t, X));
       g_attn_row_stride = X;
     } else {

@@ -268,7 +268,8 @@ typedef struct b2asr_decloop {
   /* optional fused operand layout (all three NULL = the two-GEMM form above): xcat [L,B,D+H] holds [ctx_t | h_{t-1}]
    * side by side (ctx may then be NULL), w_cat [4H,D+H] = [W_ctx | W_hh] contiguous (w_ctx / w_hh may then be NULL),
    * d_xcat [L,B,D+H] receives [d_ctx_t | recurrent d_h_{t-1}] (d_ctx / d_hrec may then be NULL; the recurrent part
-   * of the gradient of h0 is d_xcat[0][:, D:]).  One SGEMM per step and direction instead of two. */
+   * of the gradient of h0 is d_xcat[0][:, D:]).  One product per step and direction instead of two; the forward's is
+   * fused with the cell in csrc/deccell.cu when H is a multiple of 4 (B2ASR_DEC_STEP=0: cuBLAS + cell kernel). */
   float* xcat; const float* w_cat; float* d_xcat;
 } b2asr_decloop;
 size_t b2asr_decloop_size(void);
