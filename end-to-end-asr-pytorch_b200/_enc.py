@@ -11,12 +11,55 @@ Frames past a row's length produce zero outputs and zero gradients, exactly like
 reference; there is no dependence on the rows being sorted by length.
 """
 import ctypes
+import os
 
 import torch
 
 from . import _lib
 
 _status = {}
+
+# The recurrence kernels occupy 96 of the 148 SMs (7 resident 16-CTA clusters).  A layer's weight-gradient GEMMs feed
+# nothing downstream in the backward pass, so they are held back until the NEXT (lower) layer's recurrence kernel has
+# been launched and then run on a side stream next to it; the gradients are accumulated into .grad there and the
+# main stream joins at the end of the backward pass (autograd engine callback).  B2ASR_ENC_OVERLAP=0: everything in
+# stream order, gradients returned through autograd.
+OVERLAP = os.environ.get("B2ASR_ENC_OVERLAP", "1") != "0"
+_side = {}
+_deferred = []
+_join_queued = [False]
+
+
+def _side_stream(device):
+    key = device.index if device.index is not None else torch.cuda.current_device()
+    if key not in _side:
+        _side[key] = torch.cuda.Stream(device=device)
+    return _side[key]
+
+
+def _flush(device, after=None):
+    """Enqueue the held-back weight-gradient work on the side stream; `after` = event the side stream waits for first
+    (recorded just before the recurrence launch it is meant to run next to, so it cannot start ahead of it)."""
+    if not _deferred:
+        return
+    work = list(_deferred)
+    del _deferred[:]
+    side = _side_stream(device)
+    if after is not None:
+        side.wait_event(after)
+    with torch.cuda.stream(side):
+        for fn in work:
+            fn(side)
+
+
+def _join():
+    """End of a backward pass: nothing may read .grad on the caller's stream before the side stream is done."""
+    _join_queued[0] = False
+    if not _side:
+        return
+    device = torch.device("cuda", torch.cuda.current_device())
+    _flush(device)
+    torch.cuda.current_stream(device).wait_stream(_side_stream(device))
 
 
 def status_word(device):
@@ -85,6 +128,7 @@ class LstmSeq(torch.autograd.Function):
         ctx.nd = nd
         ctx.keep = (x, lens, w_cat, w_hh, b_ih, b_hh, gates, cells, out)
         ctx.has_bias = [b is not None for b in b_ih]
+        ctx.params = weights
         return out
 
     @staticmethod
@@ -99,24 +143,60 @@ class LstmSeq(torch.autograd.Function):
         io = _descr(B, T, H, nd, gates, w_hh, b_ih, b_hh, lens, cells, dev)
         io.d_out = _p(d_out)
         io.d_gates = _p(d_gates)
+        before = None
+        if OVERLAP and _deferred:
+            before = torch.cuda.Event()
+            before.record()
         _lib.call("b2asr_lstm_seq_bwd", 1, _lib.lib().b2asr_lstm_seq_bwd, ctypes.byref(io), _lib.stream_ptr())
         need = ctx.needs_input_grad
         dG2 = d_gates.view(B * T, nd * 4 * H)
+        params = ctx.params
+        has_bias = ctx.has_bias
+
+        def weight_grads():
+            g_wcat = dG2.t().mm(x.view(B * T, n_in))                                  # [ND*4H, in]
+            g_b = dG2.sum(0)
+            grads = []
+            for d in range(nd):
+                g_wih = g_wcat[d * 4 * H:(d + 1) * 4 * H]
+                if T > 1:
+                    # h_{t-1} of the forward walk is out[:, t-1, :H]; of the reverse walk out[:, t+1, H:]
+                    dg = d_gates[:, 1:, d] if d == 0 else d_gates[:, :T - 1, d]       # [B,T-1,4H] strided
+                    hp = out[:, :T - 1, d * H:(d + 1) * H] if d == 0 else out[:, 1:, d * H:(d + 1) * H]
+                    g_whh = torch.bmm(dg.transpose(1, 2), hp).sum(0)
+                else:
+                    g_whh = torch.zeros_like(w_hh[d])
+                g_bias = g_b[d * 4 * H:(d + 1) * 4 * H]
+                grads += [g_wih, g_whh, g_bias if has_bias[d] else None, g_bias if has_bias[d] else None]
+            return grads
+
+        leaf = all(p is None or (p.is_leaf and p.requires_grad) for p in params)
+        if OVERLAP and leaf and torch.is_grad_enabled() is False:
+            ready = torch.cuda.Event()
+            ready.record()                                  # d_gates complete (this stream)
+            _flush(dev, before)                             # upper layers' weight gradients run next to THIS recurrence
+
+            def work(side):
+                side.wait_event(ready)
+                for t in (d_gates, x, out):
+                    t.record_stream(side)
+                for p, g in zip(params, weight_grads()):
+                    if p is None or g is None:
+                        continue
+                    if p.grad is None:
+                        p.grad = g.clone()
+                    else:
+                        p.grad.add_(g)
+
+            _deferred.append(work)
+            if not _join_queued[0]:
+                torch.autograd.Variable._execution_engine.queue_callback(_join)
+                _join_queued[0] = True
+            g_x = dG2.mm(w_cat).view(B, T, n_in) if need[0] else None
+            ctx.keep = None
+            return (g_x, None, None) + (None,) * len(params)
         g_x = dG2.mm(w_cat).view(B, T, n_in) if need[0] else None
-        g_wcat = dG2.t().mm(x.view(B * T, n_in))                                      # [ND*4H, in]
-        g_b = dG2.sum(0)
-        grads = []
-        for d in range(nd):
-            g_wih = g_wcat[d * 4 * H:(d + 1) * 4 * H]
-            if T > 1:
-                # h_{t-1} of the forward walk is out[:, t-1, :H]; of the reverse walk out[:, t+1, H:]
-                dg = d_gates[:, 1:, d] if d == 0 else d_gates[:, :T - 1, d]           # [B,T-1,4H] strided
-                hp = out[:, :T - 1, d * H:(d + 1) * H] if d == 0 else out[:, 1:, d * H:(d + 1) * H]
-                g_whh = torch.bmm(dg.transpose(1, 2), hp).sum(0)
-            else:
-                g_whh = torch.zeros_like(w_hh[d])
-            g_bias = g_b[d * 4 * H:(d + 1) * 4 * H]
-            grads += [g_wih, g_whh, g_bias if ctx.has_bias[d] else None, g_bias if ctx.has_bias[d] else None]
+        grads = weight_grads()
         ctx.keep = None
         return (g_x, None, None, *grads)
 
