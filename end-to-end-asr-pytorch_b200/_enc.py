@@ -55,7 +55,7 @@ def _flush(device, after=None):
 def _join():
     """End of a backward pass: nothing may read .grad on the caller's stream before the side stream is done."""
     _join_queued[0] = False
-    if not _side:
+    if not _side and not _deferred:
         return
     device = torch.device("cuda", torch.cuda.current_device())
     _flush(device)

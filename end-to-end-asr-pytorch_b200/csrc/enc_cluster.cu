@@ -130,7 +130,7 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_fwd_kernel(const SeqArgs a) {
   }
   float c = 0.f;
   unsigned phase = 0;                         // bit p = parity to wait for on full[p]
-  long long cyc_wait = 0, cyc_mac = 0, cyc_rest = 0;
+  long long cyc_wait = 0, cyc_mac = 0, cyc_rest = 0, cyc_r0 = 0, cyc_r1 = 0, cyc_r2 = 0, cyc_r3 = 0;
   __syncthreads();
   cluster_arrive();
   cluster_wait();                             // every CTA's barriers are armed before the first remote copy
@@ -226,26 +226,36 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_fwd_kernel(const SeqArgs a) {
       }
       stage[p * CH + row * UC + u] = hval;
     }
-    if (s + 1 < T) {
-      fence_proxy_async_smem();               // the cell outputs above are read by the async proxy below
-      __syncthreads();
-      // this CTA's BS x UC slice of h_t -> chunk `rank` of h_s[1-p] in every CTA of the cluster
-      if (tid < NCL)
-        bulk_s2cluster(h_s + (p ^ 1) * (NCL * S) + (int)rank * S, stage + p * CH, CH * 4, &full[p ^ 1], (unsigned)tid);
-    }
     if (active) {
       grow[0] = sv[0]; grow[(long long)H] = sv[1]; grow[2ll * H] = sv[2]; grow[3ll * H] = sv[3];
       a.cells[(((long long)gb * T + t) * ND + dir) * H + unit] = c;
     }
     if (valid) a.out[((long long)gb * T + t) * ldo + dir * H + unit] = hval;
+    const long long c3 = clock64();
+    long long c4 = c3, c5 = c3;
+    if (s + 1 < T) {
+      fence_proxy_async_smem();               // the cell outputs above are read by the async proxy below
+      __syncthreads();
+      c4 = clock64();
+      // this CTA's BS x UC slice of h_t -> chunk `rank` of h_s[1-p] in every CTA of the cluster
+      // (one elected lane per warp: the 16 lanes of one warp would issue their copies one after the other, ~60 ns
+      // each, on the critical path of every CTA of the cluster)
+      if ((tid & 31) == 0)
+        for (int d = tid >> 5; d < NCL; d += H / 32)
+          bulk_s2cluster(h_s + (p ^ 1) * (NCL * S) + (int)rank * S, stage + p * CH, CH * 4, &full[p ^ 1], (unsigned)d);
+      c5 = clock64();
+    }
 #pragma unroll
     for (int g = 0; g < 4; ++g) pre[g] = nxt[g];
-    cyc_wait += c1 - c0; cyc_mac += c2 - c1; cyc_rest += clock64() - c2;
+    const long long c6 = clock64();
+    cyc_wait += c1 - c0; cyc_mac += c2 - c1; cyc_rest += c6 - c2;
+    cyc_r0 += c3 - c2; cyc_r1 += c4 - c3; cyc_r2 += c5 - c4; cyc_r3 += c6 - c5;
   }
   cluster_arrive();
   cluster_wait();                             // nobody leaves while a copy may still read or write its shared memory
   if (tid == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) {   // CTA 0's cycle split (clock64)
     a.status[4] = (int)cyc_wait; a.status[5] = (int)cyc_mac; a.status[6] = (int)cyc_rest;
+    a.status[11] = (int)cyc_r0; a.status[12] = (int)cyc_r1; a.status[13] = (int)cyc_r2; a.status[14] = (int)cyc_r3;
   }
 }
 
@@ -347,8 +357,10 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_bwd_kernel(const SeqArgs a) {
       __syncthreads();
       c1 = clock64();
       // reduce-scatter: the owner of units [d*UC, +UC) gets this CTA's partials for them, slot `rank`
-      if (tid < NCL)
-        bulk_s2cluster(recv + p * (NCL * CH) + (int)rank * CH, Ps + p * (NCL * CH) + tid * CH, CH * 4, &full[p], (unsigned)tid);
+      // (one elected lane per warp issues: see the forward kernel)
+      if ((tid & 31) == 0)
+        for (int d = tid >> 5; d < NCL; d += H / 32)
+          bulk_s2cluster(recv + p * (NCL * CH) + (int)rank * CH, Ps + p * (NCL * CH) + d * CH, CH * 4, &full[p], (unsigned)d);
       if (!mbar_wait_bounded(&full[p], (phase >> p) & 1u)) { atomicExch(a.status, 1); return; }
       phase ^= 1u << p;
       if (tid == 0) mbar_expect_tx(&full[p], NCL * CH * 4);     // re-arm for frame s+2

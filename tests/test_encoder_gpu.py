@@ -123,3 +123,38 @@ def test_unsorted_lengths_and_listener_routes_through_kernel():
     assert lib.LAUNCHES == before + 1 and hidden is None
     assert new_len == [int(lens[i] / 2) for i in order]
     _close(y, ref_sorted[:, ::2], "RNNLayer drop output")
+
+
+def test_weight_gradients_on_side_stream_match_stream_order():
+    """_enc.OVERLAP: a layer's weight-gradient GEMMs run on a side stream next to the next recurrence kernel and are
+    accumulated into .grad directly; same numbers as the stream-ordered autograd path, also when .grad already holds
+    a value (accumulation over two backward passes) and when two layers are stacked (the second flushes the first)."""
+    enc = importlib.import_module(PKG + "._enc")
+    dev = torch.device("cuda:0")
+    torch.manual_seed(3)
+    B, T, n_in, H = 12, 40, 24, 320
+    lens = _lens(B, T, seed=5)
+    x = torch.randn(B, T, n_in, device=dev)
+    l0 = torch.nn.LSTM(n_in, H, bidirectional=True, batch_first=True).to(dev)
+    l1 = torch.nn.LSTM(2 * H, H, bidirectional=True, batch_first=True).to(dev)
+    w = torch.randn(B, T, 2 * H, device=dev)
+
+    def run(overlap):
+        prev = enc.OVERLAP
+        enc.OVERLAP = overlap
+        try:
+            for p in list(l0.parameters()) + list(l1.parameters()):
+                p.grad = None
+            xin = x.clone().requires_grad_(True)
+            for _ in range(2):                                   # second pass accumulates into existing .grad
+                y = enc.lstm_layer(l1, torch.tanh(enc.lstm_layer(l0, xin, lens)), lens)
+                (y * w).sum().backward()
+            torch.cuda.synchronize()
+            enc.check_status(dev)
+            return [p.grad.clone() for p in list(l0.parameters()) + list(l1.parameters())] + [xin.grad.clone()]
+        finally:
+            enc.OVERLAP = prev
+
+    a, b = run(True), run(False)
+    for ga, gb in zip(a, b):
+        _close(ga, gb, "overlap vs stream order", rtol=1e-6)
