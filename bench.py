@@ -25,6 +25,11 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 PKG = "end-to-end-asr-pytorch_b200"
 METRIC = "utterances/sec hybrid CTC-attn train step"
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of the kernel that dominates each call (profiles/, M2 shape)
+NCU_DRAM_BYTES = {
+    "b2asr_decoder_loop_bwd": (66.982912e6 + 0.298752e6, "profiles/r01_ncu_attn_bwd_v1.txt attn_step_bwd_kernel"),
+    "b2asr_decoder_loop_fwd": (48.697344e6 + 0.006144e6, "profiles/r01_ncu_attn_fwd_v1.txt attn_step_fwd_kernel"),
+}
 WORKLOAD = "libri_m2"
 N_BATCHES = 4                      # distinct synthetic batches rotated through the timed steps
 
@@ -416,8 +421,19 @@ def run_native(args):
             note = ("serial recurrence: T dependent frames per launch, bound by the fp32 FMA pipe of the 96 SMs the "
                     "7 resident 16-CTA clusters occupy and by the per-frame exchange; recurrent MACs run at %.1f of "
                     "%.1f fp32 TFLOP/s; see DESIGN.md section 4" % (enc_flops[top] / (k["avg_us"] * 1e-6) / 1e12, fp32_peak))
+        # DRAM bytes of the call's dominant kernel from the committed `ncu --set full` captures (cold-cache replay
+        # of one launch at the M2 shape), scaled to the launches one call makes
+        traffic = None
+        if WORKLOAD == "libri_m2" and top in NCU_DRAM_BYTES:
+            per_launch, src = NCU_DRAM_BYTES[top]
+            steps_per_call = 1.0
+            if top.startswith("b2asr_decoder_loop"):
+                steps_per_call = sum(max(int(v) for v in (host[i % N_BATCHES][1] != 0).sum(-1))
+                                     for i in range(prof_steps)) / prof_steps
+            traffic = per_launch * steps_per_call
+            note += "; traffic = %s x %.0f launches per call (cold-cache replay: in the step the operands stay in L2)" % (src, steps_per_call)
         roofline = {"kernel": top, "bound": "hbm", "achieved": k["achieved_gbs"], "peak": peak, "unit": "GB/s",
-                    "frac": k["achieved_gbs"] / peak, "traffic": None, "peak_source": how,
+                    "frac": k["achieved_gbs"] / peak, "traffic": traffic, "peak_source": how,
                     "share_of_step": k["ms_per_step"] / ms_step, "note": note}
 
     decode = None

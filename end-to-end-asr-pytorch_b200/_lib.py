@@ -59,6 +59,11 @@ class LstmSeq(ctypes.Structure):
                  ("lens", c_p), ("out", c_p), ("cells", c_p), ("d_out", c_p), ("d_gates", c_p), ("status", c_p)])
 
 
+class ParamChunk(ctypes.Structure):
+    """Mirror of `b2asr_param_chunk` (include/b2asr.h)."""
+    _fields_ = [("param", c_p), ("offset", ctypes.c_int64), ("count", ctypes.c_int32), ("reserved", ctypes.c_int32)]
+
+
 # name -> (restype, argtypes); must list every symbol include/b2asr.h declares.
 _SIGNATURES = {
     "b2asr_attn_keys": (c_i, [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_p]),
@@ -77,6 +82,8 @@ _SIGNATURES = {
     "b2asr_lstm_seq_path": (c_i, [c_i]),
     "b2asr_lstm_seq_fwd": (c_i, [ctypes.POINTER(LstmSeq), c_p]),
     "b2asr_lstm_seq_bwd": (c_i, [ctypes.POINTER(LstmSeq), c_p]),
+    "b2asr_param_chunk_size": (c_sz, []),
+    "b2asr_adadelta_step": (c_i, [c_p, c_i, c_p, c_p, c_p, c_f, c_f, c_f, c_f, c_p]),
     "b2asr_ce_loss_fwd_bwd": (c_i, [c_p, c_i64, c_p, c_i64, c_i, c_i, c_p, c_i64, c_f, c_p, c_p, c_p, c_i64, c_p, c_p]),
     "b2asr_edit_distance": (c_i64, [c_p, c_i64, c_p, c_i64]),
     "b2asr_last_error": (ctypes.c_char_p, []),
@@ -132,6 +139,9 @@ def lib():
         if L.b2asr_lstm_seq_size() != ctypes.sizeof(LstmSeq):
             raise B2asrError("b2asr_lstm_seq layout mismatch: library %d bytes, binding %d bytes"
                              % (L.b2asr_lstm_seq_size(), ctypes.sizeof(LstmSeq)))
+        if L.b2asr_param_chunk_size() != ctypes.sizeof(ParamChunk):
+            raise B2asrError("b2asr_param_chunk layout mismatch: library %d bytes, binding %d bytes"
+                             % (L.b2asr_param_chunk_size(), ctypes.sizeof(ParamChunk)))
         _lib = L
     return _lib
 

@@ -60,17 +60,18 @@ class FlatGradients:
 
     def __init__(self, params):
         self.params = [p for p in params if p.requires_grad]
-        n = sum(p.numel() for p in self.params)
+        self.offsets, n = [], 0
+        for p in self.params:                       # every tensor starts on a 16-byte boundary (float4 passes)
+            self.offsets.append(n)
+            n += (p.numel() + 3) // 4 * 4
         dev = self.params[0].device
         self.flat = torch.zeros(n, dtype=torch.float32, device=dev)
         self.rebind()
 
     def rebind(self):
         """(Re)attach every parameter's .grad as a view into the flat buffer."""
-        o = 0
-        for p in self.params:
+        for p, o in zip(self.params, self.offsets):
             p.grad = self.flat[o:o + p.numel()].view_as(p)
-            o += p.numel()
 
     def zero(self):
         self.flat.zero_()
@@ -99,6 +100,8 @@ class TrainStep:
     def __init__(self, model, optimizer, ctc_weight, grad_clip=GRAD_CLIP, group=None):
         self.model, self.opt, self.w, self.clip, self.group = model, optimizer, ctc_weight, grad_clip, group
         self.grads = FlatGradients(model.parameters())
+        if hasattr(optimizer, 'bind') and self.grads.flat.is_cuda:
+            optimizer.bind(self.grads)                              # one-launch optimizer step (_optim.py)
 
     def step(self, x, y, tf_rate=1.0):
         if not x.is_cuda:
@@ -124,6 +127,10 @@ class TrainStep:
 
 def make_optimizer(model, opt_cfg):
     """solver.py:101-106 (apex absent in this image -> the torch.optim branch)."""
+    if (opt_cfg['type'] == 'Adadelta' and next(model.parameters()).is_cuda
+            and os.environ.get('B2ASR_OPT', 'fused') != 'torch'):
+        from . import _optim
+        return _optim.Adadelta(model.parameters(), lr=opt_cfg['learning_rate'], eps=1e-8)
     cls = getattr(torch.optim, opt_cfg['type'])
     return cls(model.parameters(), lr=opt_cfg['learning_rate'], eps=1e-8)
 

@@ -337,6 +337,26 @@ int b2asr_ce_loss_fwd_bwd(const float* logits, int64_t stride_row, const int64_t
  * ---------------------------------------------------------------------- */
 int64_t b2asr_edit_distance(const int32_t* a, int64_t na, const int32_t* b, int64_t nb);
 
+/* ------------------------------------------------------------------------
+ * SURVEY.md section 8 "next" (the caller after the path): the optimizer step of the train step, reference
+ * src/solver.py:101-106 (asr_opt = torch.optim.Adadelta(params, lr, eps=1e-8)) and solver.py:178-182 (clip, NaN
+ * guard, asr_opt.step()).  One launch over the flat gradient buffer instead of torch's seven multi-tensor passes;
+ * arithmetic and order of operations of torch/optim/adadelta.py (csrc/optim.cu).
+ *   chunks      [n_chunks] DEVICE table: `count` consecutive elements of parameter tensor `param` sit at `offset`
+ *               of the three flat vectors (a tensor longer than one chunk appears several times)
+ *   grad        flat gradients (read), square_avg / acc_delta flat optimizer state (updated), parameters updated
+ *               in place through the table
+ * ---------------------------------------------------------------------- */
+typedef struct b2asr_param_chunk {
+  float*  param;     /* first element of this chunk inside its parameter tensor */
+  int64_t offset;    /* the same element's index in grad / square_avg / acc_delta */
+  int32_t count;
+  int32_t reserved;
+} b2asr_param_chunk;
+size_t b2asr_param_chunk_size(void);
+int b2asr_adadelta_step(const b2asr_param_chunk* chunks, int n_chunks, const float* grad, float* square_avg,
+                        float* acc_delta, float lr, float rho, float eps, float weight_decay, void* stream);
+
 /* Debug aid, not part of the drop-in path: with B2ASR_ATT_TRACE=1 in the environment CTA 0 of every attention
  * launch stamps clock64() at its phase boundaries (forward: slots 0-9, backward: 16-27); this copies the first n
  * slots of the last launch to the host (synchronous). */

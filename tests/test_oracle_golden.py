@@ -139,3 +139,26 @@ def test_encoder_oracle_reference_call_matches_restated_equations():
         b = eo.restated(layer, x, lens)
         assert a.shape == b.shape
         assert float((a - b).abs().max()) < 1e-12
+
+
+def test_adadelta_oracle_matches_torch_optim():
+    """oracle/optim_oracle.py against torch.optim.Adadelta (the optimizer of reference src/solver.py:101-106)."""
+    import numpy as np
+    import torch
+    from oracle import optim_oracle as oo
+    torch.manual_seed(0)
+    shapes = [(31,), (7, 13), (64, 5)]
+    params = [torch.nn.Parameter(torch.randn(*s)) for s in shapes]
+    opt = torch.optim.Adadelta(params, lr=1.0, eps=1e-8)
+    mine = [(p.detach().numpy().copy(), np.zeros(s, np.float32), np.zeros(s, np.float32)) for p, s in zip(params, shapes)]
+    for step in range(4):
+        grads = [torch.randn(*s) * (10.0 ** (step - 2)) for s in shapes]
+        for p, g in zip(params, grads):
+            p.grad = g.clone()
+        opt.step()
+        for (w, sq, acc), g in zip(mine, grads):
+            oo.adadelta_step(w, g.numpy(), sq, acc, lr=1.0, rho=0.9, eps=1e-8)
+    for p, (w, sq, acc) in zip(params, mine):
+        np.testing.assert_allclose(w, p.detach().numpy(), rtol=2e-6, atol=1e-7)
+        np.testing.assert_allclose(sq, opt.state[p]["square_avg"].numpy(), rtol=2e-6, atol=0)
+        np.testing.assert_allclose(acc, opt.state[p]["acc_delta"].numpy(), rtol=4e-6, atol=0)

@@ -44,6 +44,27 @@ for k, (c, t) in sorted(fam.items(), key=lambda kv: -kv[1][1]):
 ev.sort(key=lambda e: e.time_range.start)
 span = ev[-1].time_range.end - ev[0].time_range.start
 print("GPU activity span %.1f ms -> idle inside the span %.1f ms" % (span / 1e3, (span - tot) / 1e3))
+# union of the kernel intervals (streams overlap since the weight-gradient side stream): true idle, and where
+busy, cur_s, cur_e, gaps = 0.0, None, None, []
+for e in ev:
+    s0, e0 = e.time_range.start, e.time_range.end
+    if cur_e is None or s0 > cur_e:
+        if cur_e is not None:
+            busy += cur_e - cur_s
+            gaps.append((s0 - cur_e, prev_name, e.name))
+        cur_s, cur_e = s0, e0
+    else:
+        cur_e = max(cur_e, e0)
+    prev_name = e.name
+busy += cur_e - cur_s
+print("union of kernel intervals %.1f ms busy, %.1f ms with no kernel running (%d gaps)" % (busy / 1e3, (span - busy) / 1e3, len(gaps)))
+after = {}
+for g, a, b in gaps:
+    k = ("attn_bwd" if "attn_step_bwd" in a else "attn_fwd" if "attn_step_fwd" in a else "dec_step" if "dec_step" in a else
+         "lstm_cl" if "lstm_cl" in a else "b2asr other" if "b2asr" in a else "gemm" if ("gemm" in a or "splitK" in a) else "other")
+    v = after.setdefault(k, [0, 0.0]); v[0] += 1; v[1] += g
+for k, (c, t) in sorted(after.items(), key=lambda kv: -kv[1][1]):
+    print("  gaps after %-12s %5d x %5.2f us = %6.2f ms" % (k, c, t / c, t / 1e3))
 
 byname = {}
 for e in ev:
