@@ -51,6 +51,11 @@ __device__ __forceinline__ bool mbar_wait_bounded(unsigned long long* bar, unsig
   return false;
 }
 
+// named barriers: the compute warps arrive (do not block), the copy-issuing warp waits for all of them
+__device__ __forceinline__ void named_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+__device__ __forceinline__ void named_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+constexpr int kIssueWarp = 32;                // backward: one extra warp per CTA forwards the first part of the partials
+
 // packed fp32: two FMAs per issue slot (SASS FFMA2); the loops below are issue-bound with 2.5 warps per scheduler
 typedef unsigned long long f32x2;
 __device__ __forceinline__ f32x2 ffma2(f32x2 a, f32x2 b, f32x2 c) {
@@ -77,9 +82,11 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_fwd_kernel(const SeqArgs a) {
   constexpr int RB = BS <= 8 ? 8 : 16;        // rows the 16-lane butterfly resolves (rows >= BS are zeros)
   constexpr int S = chunk_stride(UC, BS);
   constexpr int CH = BS * UC;                 // floats one CTA contributes per frame
+  constexpr int R1 = BS / 3;                  // rows sent (and consumed) first: the MACs start on them while the rest travels
+  constexpr int CH0 = R1 * UC, CH1 = CH - CH0;
   static_assert(H % 64 == 0 && UC % 4 == 0 && BS % 4 == 0 && BS <= 16, "slices are whole float4s");
   extern __shared__ __align__(128) float smem[];
-  __shared__ __align__(8) unsigned long long full[2];
+  __shared__ __align__(8) unsigned long long full[2][2];   // [part][buffer]: rows [0,R1) and [R1,BS) of every slice
   __shared__ int lens_s[32];                  // lengths of this cluster's rows (0 past the batch)
   float* h_s = smem;                          // [2][NCL][S]: chunk of rank r = [BS][UC]
   float* stage = smem + 2 * NCL * S;          // [2][BS][UC]
@@ -107,11 +114,12 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_fwd_kernel(const SeqArgs a) {
   for (int idx = tid; idx < NCL * S; idx += H) h_s[idx] = 0.f;
   if (tid < 32) lens_s[tid] = (tid < BS && b0 + tid * bstep < a.B) ? a.lens[b0 + tid * bstep] : 0;
   if (tid == 0) {
-    mbar_init(&full[0], 1);
-    mbar_init(&full[1], 1);
+    for (int i = 0; i < 4; ++i) mbar_init(&full[i >> 1][i & 1], 1);
     mbar_fence_init();
-    mbar_expect_tx(&full[1], NCL * CH * 4);   // frame 1 reads buffer 1, frame 2 buffer 0
-    mbar_expect_tx(&full[0], NCL * CH * 4);
+    for (int q = 0; q < 2; ++q) {               // frame 1 reads buffer 1, frame 2 buffer 0
+      mbar_expect_tx(&full[0][q], NCL * CH0 * 4);
+      mbar_expect_tx(&full[1][q], NCL * CH1 * 4);
+    }
   }
 
   // cell role: RB = 8 -> even lanes own row ks/2; RB = 16 -> every lane owns row ks
@@ -129,7 +137,7 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_fwd_kernel(const SeqArgs a) {
     }
   }
   float c = 0.f;
-  unsigned phase = 0;                         // bit p = parity to wait for on full[p]
+  unsigned phase = 0;                         // bit 2*part+p = parity to wait for on full[part][p]
   long long cyc_wait = 0, cyc_mac = 0, cyc_rest = 0, cyc_r0 = 0, cyc_r1 = 0, cyc_r2 = 0, cyc_r3 = 0;
   __syncthreads();
   cluster_arrive();
@@ -160,10 +168,10 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_fwd_kernel(const SeqArgs a) {
       }
     }
     const long long c0 = clock64();
-    if (s > 0) {                              // h_{t-1}: all 16 slices have landed in h_s[p]
-      if (!mbar_wait_bounded(&full[p], (phase >> p) & 1u)) { atomicExch(a.status, 1); return; }
+    if (s > 0) {                              // h_{t-1}: rows [0,R1) of all 16 slices have landed in h_s[p]
+      if (!mbar_wait_bounded(&full[0][p], (phase >> p) & 1u)) { atomicExch(a.status, 1); return; }
       phase ^= 1u << p;
-      if (tid == 0) mbar_expect_tx(&full[p], NCL * CH * 4);     // re-arm for frame s+2
+      if (tid == 0) mbar_expect_tx(&full[0][p], NCL * CH0 * 4);  // re-arm for frame s+2
     }
     const long long c1 = clock64();
     float acc[RB][4];
@@ -177,6 +185,11 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_fwd_kernel(const SeqArgs a) {
       const unsigned rows_on = __ballot_sync(kFull, t < lens_s[tid & 31]);
 #pragma unroll
       for (int b = 0; b < BS; ++b) {
+        if (b == R1 && s > 0) {                       // the remaining rows
+          if (!mbar_wait_bounded(&full[1][p], (phase >> (2 + p)) & 1u)) { atomicExch(a.status, 1); return; }
+          phase ^= 4u << p;
+          if (tid == 0) mbar_expect_tx(&full[1][p], NCL * CH1 * 4);
+        }
         f32x2 a2[4] = {0ull, 0ull, 0ull, 0ull};      // (even-k, odd-k) partial sums of the row's four gates
         if ((rows_on >> b) & 1u) {
 #pragma unroll
@@ -238,11 +251,15 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_fwd_kernel(const SeqArgs a) {
       __syncthreads();
       c4 = clock64();
       // this CTA's BS x UC slice of h_t -> chunk `rank` of h_s[1-p] in every CTA of the cluster
-      // (one elected lane per warp: the 16 lanes of one warp would issue their copies one after the other, ~60 ns
-      // each, on the critical path of every CTA of the cluster)
-      if ((tid & 31) == 0)
-        for (int d = tid >> 5; d < NCL; d += H / 32)
-          bulk_s2cluster(h_s + (p ^ 1) * (NCL * S) + (int)rank * S, stage + p * CH, CH * 4, &full[p ^ 1], (unsigned)d);
+      // (four lanes per warp issue the 32 copies, lanes 0-1 the first rows, lanes 2-3 the rest.  How they are issued
+      // does not change the frame time -- one lane per warp looping, distinct lanes, a warp of its own were all
+      // measured: the 15 KB a CTA sends per frame share its ~21 B/clk path into the peers, ~0.4 us)
+      {
+        const int lane = tid & 31, d = (tid >> 5) + (lane & 1) * (H / 32);
+        float* dst = h_s + (p ^ 1) * (NCL * S) + (int)rank * S;
+        if (lane < 2 && d < NCL) bulk_s2cluster(dst, stage + p * CH, CH0 * 4, &full[0][p ^ 1], (unsigned)d);
+        else if (lane < 4 && d < NCL) bulk_s2cluster(dst + CH0, stage + p * CH + CH0, CH1 * 4, &full[1][p ^ 1], (unsigned)d);
+      }
       c5 = clock64();
     }
 #pragma unroll
@@ -264,7 +281,7 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_fwd_kernel(const SeqArgs a) {
 // the first BS*UC threads double as the cell-backward owners of (row, unit).
 // ---------------------------------------------------------------------------------------------------------
 template <int H, int BS>
-__global__ void __launch_bounds__(H, 1) lstm_cl_bwd_kernel(const SeqArgs a) {
+__global__ void __launch_bounds__(H + kIssueWarp, 1) lstm_cl_bwd_kernel(const SeqArgs a) {
   constexpr int UC = H / NCL, LR = 4 * UC, CH = BS * UC;
   static_assert(BS % 4 == 0 && BS * UC <= H, "cell owners fit the block");
   extern __shared__ __align__(128) float smem[];
@@ -273,7 +290,7 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_bwd_kernel(const SeqArgs a) {
   float* dgl = smem;                          // [LR/2][BS][2]  d_gates this CTA produced last frame: lr = gate*UC+uu -> [lr/2][row][lr%2]
   float* Ps = smem + LR * BS;                 // [2][NCL][BS][UC]  partial dh, grouped by owner rank
   float* recv = Ps + 2 * NCL * CH;            // [2][NCL][BS][UC]  partials of MY units from every rank
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x, wc = tid < H ? tid : tid - kIssueWarp;   // threads [H, H+32): the issue warp
   const unsigned rank = cluster_ctarank();
   // rows are dealt round-robin to the row groups (row r of group y = batch row y + r*groups): with a batch sorted
   // by length every cluster gets the same mix of long and short rows
@@ -288,7 +305,7 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_bwd_kernel(const SeqArgs a) {
 #pragma unroll
     for (int i = 0; i < LR / 2; ++i) {
       const int g = (2 * i) / UC, uu = (2 * i) % UC;
-      wr2[i] = pack2(__ldg(W + ((long long)g * H + u0 + uu) * H + tid), __ldg(W + ((long long)g * H + u0 + uu + 1) * H + tid));
+      wr2[i] = pack2(__ldg(W + ((long long)g * H + u0 + uu) * H + wc), __ldg(W + ((long long)g * H + u0 + uu + 1) * H + wc));
     }
   }
   for (int idx = tid; idx < LR * BS; idx += H) dgl[idx] = 0.f;
@@ -313,6 +330,21 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_bwd_kernel(const SeqArgs a) {
   cluster_arrive();
   cluster_wait();
 
+  bool dead = false;                          // a wait timed out: keep walking (status says so), never hang a peer
+  constexpr int Q1 = (BS + 2) / 3, NQ = BS / 2;   // row pairs of the first / of both parts of the reduce-scatter
+  if (tid >= H) {
+    // The first part of the partials (row pairs [0,Q1)) is forwarded by this warp while the compute warps multiply
+    // the rest: a thread that issues a cp.async.bulk into a peer is held until the CTA's ~21 B/clk path has taken the
+    // copy, which would stall the MACs of its whole warp.
+    const int lane = tid - H;
+    for (int s = 1; s < T; ++s) {
+      const int p = s & 1;
+      named_sync(1, H + kIssueWarp);
+      if (lane < NCL)
+        bulk_s2cluster(recv + p * (NCL * CH) + (int)rank * CH, Ps + p * (NCL * CH) + lane * CH, 2 * Q1 * UC * 4, &full[p],
+                       (unsigned)lane);
+    }
+  } else {
   for (int s = 0; s < T; ++s) {
     const int t = dir ? s : T - 1 - s;
     const int tcp = dir ? t + 1 : t - 1;      // frame whose cell state entered frame t in the forward walk
@@ -330,38 +362,46 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_bwd_kernel(const SeqArgs a) {
     const long long c0 = clock64();
     long long c1 = c0, c2 = c0;
     if (s > 0) {
-      f32x2 acc2[BS];                          // (even, odd local gate row) partial sums per batch row
-#pragma unroll
-      for (int b = 0; b < BS; ++b) acc2[b] = 0ull;
       // dgl rows of batch rows that were past their length at the previous frame are zero: skip the pair
       const int tq = dir ? t - 1 : t + 1;
       const unsigned rows_on = __ballot_sync(kFull, tq < lens_s[tid & 31]);
+      float* pb = Ps + p * (NCL * CH) + pdst;
+      // reduce-scatter in two parts: the partials of the first Q1 row pairs travel while the remaining pairs are
+      // still being multiplied (a CTA moves ~21 B/clk into its peers: 15 KB per frame would otherwise sit between
+      // the MACs and the cell); the owner of units [d*UC, +UC) gets this CTA's partials for them in slot `rank`
 #pragma unroll
-      for (int q = 0; q < BS / 2; ++q) {
-        if ((rows_on >> (2 * q)) & 3u) {
+      for (int part = 0; part < 2; ++part) {
+        const int qa = part ? Q1 : 0, qb = part ? NQ : Q1;
 #pragma unroll
-          for (int i = 0; i < LR / 2; ++i) {
-            const ulonglong2 d = *reinterpret_cast<const ulonglong2*>(dgl + (i * BS + 2 * q) * 2);
-            acc2[2 * q] = ffma2(d.x, wr2[i], acc2[2 * q]);
-            acc2[2 * q + 1] = ffma2(d.y, wr2[i], acc2[2 * q + 1]);
+        for (int q = qa; q < qb; ++q) {
+          f32x2 e = 0ull, o = 0ull;                  // (even, odd local gate row) partial sums of rows 2q, 2q+1
+          if ((rows_on >> (2 * q)) & 3u) {
+#pragma unroll
+            for (int i = 0; i < LR / 2; ++i) {
+              const ulonglong2 d = *reinterpret_cast<const ulonglong2*>(dgl + (i * BS + 2 * q) * 2);
+              e = ffma2(d.x, wr2[i], e);
+              o = ffma2(d.y, wr2[i], o);
+            }
+          }
+          pb[(2 * q) * UC] = sum2(e);
+          pb[(2 * q + 1) * UC] = sum2(o);
+        }
+        fence_proxy_async_smem();
+        if (part == 0) {
+          named_arrive(1, H + kIssueWarp);         // the issue warp forwards this part while the MACs go on
+        } else {
+          named_sync(3, H);                        // the last part: every compute warp issues one or two copies
+          c1 = clock64();
+          {                                        // two lanes per warp, one copy each (see the forward kernel)
+            const int off = 2 * Q1 * UC, bytes = 2 * (NQ - Q1) * UC * 4;
+            const int lane = tid & 31, d = (tid >> 5) + lane * (H / 32);
+            if (lane < 2 && d < NCL)
+              bulk_s2cluster(recv + p * (NCL * CH) + (int)rank * CH + off, Ps + p * (NCL * CH) + d * CH + off, bytes, &full[p],
+                             (unsigned)d);
           }
         }
       }
-      float acc[BS];
-#pragma unroll
-      for (int b = 0; b < BS; ++b) acc[b] = sum2(acc2[b]);
-      float* pb = Ps + p * (NCL * CH) + pdst;
-#pragma unroll
-      for (int b = 0; b < BS; ++b) pb[b * UC] = acc[b];
-      fence_proxy_async_smem();
-      __syncthreads();
-      c1 = clock64();
-      // reduce-scatter: the owner of units [d*UC, +UC) gets this CTA's partials for them, slot `rank`
-      // (one elected lane per warp issues: see the forward kernel)
-      if ((tid & 31) == 0)
-        for (int d = tid >> 5; d < NCL; d += H / 32)
-          bulk_s2cluster(recv + p * (NCL * CH) + (int)rank * CH, Ps + p * (NCL * CH) + d * CH, CH * 4, &full[p], (unsigned)d);
-      if (!mbar_wait_bounded(&full[p], (phase >> p) & 1u)) { atomicExch(a.status, 1); return; }
+      if (!dead && !mbar_wait_bounded(&full[p], (phase >> p) & 1u)) { atomicExch(a.status, 1); dead = true; }
       phase ^= 1u << p;
       if (tid == 0) mbar_expect_tx(&full[p], NCL * CH * 4);     // re-arm for frame s+2
       c2 = clock64();
@@ -395,8 +435,9 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_bwd_kernel(const SeqArgs a) {
         o[0] = di; o[(long long)H] = df; o[2ll * H] = dgg; o[3ll * H] = dob;
       }
     }
-    __syncthreads();
+    named_sync(3, H);                         // compute warps only: dgl is complete before the next frame's MACs
     cyc_mac += c1 - c0; cyc_wait += c2 - c1; cyc_rest += clock64() - c2;
+  }
   }
   cluster_arrive();
   cluster_wait();                             // nobody leaves while a copy may still read or write its shared memory
@@ -415,7 +456,7 @@ int launch(const SeqArgs& a, bool backward, cudaStream_t st, bool probe_only, in
   B2_CUDA_TRY(cudaFuncSetAttribute((const void*)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(NCL, (a.B + BS - 1) / BS, a.ND);
-  cfg.blockDim = dim3(H);
+  cfg.blockDim = dim3(backward ? H + kIssueWarp : H);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
   cudaLaunchAttribute at[1];
