@@ -66,6 +66,27 @@ for g, a, b in gaps:
 for k, (c, t) in sorted(after.items(), key=lambda kv: -kv[1][1]):
     print("  gaps after %-12s %5d x %5.2f us = %6.2f ms" % (k, c, t / c, t / 1e3))
 
+# the tail of the backward pass: what still runs after the last recurrence kernel until the optimizer launch
+rec = [e for e in ev if "lstm_cl_bwd" in e.name]
+opt_k = [e for e in ev if "adadelta" in e.name]
+if rec and opt_k:
+    t_end = max(e.time_range.end for e in rec)
+    t_opt = opt_k[-1].time_range.start
+    tail = [e for e in ev if e.time_range.end > t_end and e.time_range.start < t_opt]
+    print("after the last recurrence kernel: %.2f ms until the optimizer launch, %d kernels, %.2f ms summed" % (
+        (t_opt - t_end) / 1e3, len(tail), sum(min(e.time_range.end, t_opt) - max(e.time_range.start, t_end) for e in tail) / 1e3))
+    agg = {}
+    for e in tail:
+        a = agg.setdefault(e.name[:70], [0, 0.0]); a[0] += 1; a[1] += e.device_time
+    for k, (c, t) in sorted(agg.items(), key=lambda kv: -kv[1][1])[:8]:
+        print("    %3d x %8.1f us  %s" % (c, t / c, k))
+    # and per backward recurrence launch: when it ran and how much side-stream GEMM time overlapped it
+    for e in sorted(rec, key=lambda e: e.time_range.start):
+        ov = sum(max(0, min(g.time_range.end, e.time_range.end) - max(g.time_range.start, e.time_range.start))
+                 for g in ev if g is not e and ("gemm" in g.name or "cutlass" in g.name or "reduce_kernel" in g.name))
+        print("    recurrence bwd %7.2f ms long, GEMM/reduce time overlapping it %7.2f ms" % (
+            (e.time_range.end - e.time_range.start) / 1e3, ov / 1e3))
+
 byname = {}
 for e in ev:
     a = byname.setdefault(e.name[:90], [0, 0.0]); a[0] += 1; a[1] += e.device_time
