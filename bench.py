@@ -182,7 +182,16 @@ def cpu_train_step_rate(steps, warmup, budget_s, seed=1234):
     run(1)                                             # page in / thread pools (untimed)
     per_utt = run(1)
     bs = int(max(1, min(w["batch"], budget_s / max(per_utt * (steps + warmup), 1e-6))))
-    for _ in range(warmup):
+    # the one-utterance estimate can be off (cache footprint, shared host): the first full-size step doubles as a
+    # calibration, and the sample shrinks if that step alone overran its share of the budget
+    target, warmed = budget_s / max(steps + warmup, 1), 0
+    while True:
+        dt = run(bs)
+        warmed += 1
+        if dt <= 1.5 * target or bs == 1:
+            break
+        bs = max(1, int(bs * target / dt))
+    for _ in range(max(0, warmup - warmed)):
         run(bs)
     t0 = time.perf_counter()
     for _ in range(steps):
