@@ -15,6 +15,10 @@
 //     No cluster barrier and no thread-issued remote stores inside the loop; staging buffers are double-buffered
 //     and the data dependence itself is the flow control (a peer cannot produce frame t+1 before it has consumed
 //     everybody's frame t);
+//   * the exchange is bound by the ~21 B/clk one SM moves into its peers (15 KB per frame: ~0.4 us), so it travels in
+//     two parts: forward, rows [0,BS/3) of a slice go first on their own mbarrier and the receivers start multiplying
+//     them while the rest is in flight; backward, the partials of the first two thirds of the rows are forwarded by
+//     an extra warp (block = H+32 threads, named barriers) while the compute warps multiply the last third;
 //   * BS in {8, 12, 16}: the device holds only ~7 clusters of 16 CTAs at once (cudaOccupancyMaxActiveClusters),
 //     so the rows are split into as many groups as fit in one wave;
 //   * clusters are independent of each other (no cooperative launch).
