@@ -158,3 +158,34 @@ def test_weight_gradients_on_side_stream_match_stream_order():
     a, b = run(True), run(False)
     for ga, gb in zip(a, b):
         _close(ga, gb, "overlap vs stream order", rtol=1e-6)
+
+
+def test_recurrence_kernels_are_bit_reproducible():
+    """The exchanges land in any order, but every sum is formed in a fixed order (the owner adds the 16 partial dh in
+    rank order): two runs on the same inputs give identical bits, forward and backward."""
+    enc = importlib.import_module(PKG + "._enc")
+    dev = torch.device("cuda:0")
+    torch.manual_seed(11)
+    B, T, n_in, H = 32, 64, 40, 320
+    lens = _lens(B, T, seed=3)
+    layer = torch.nn.LSTM(n_in, H, bidirectional=True, batch_first=True).to(dev)
+    x = torch.randn(B, T, n_in, device=dev)
+    w = torch.randn(B, T, 2 * H, device=dev)
+    prev = enc.OVERLAP
+    enc.OVERLAP = False                                          # gradients through autograd: one stream, one order
+    try:
+        runs = []
+        for _ in range(3):
+            xin = x.clone().requires_grad_(True)
+            for p in layer.parameters():
+                p.grad = None
+            out = enc.lstm_layer(layer, xin, lens)
+            (out * w).sum().backward()
+            torch.cuda.synchronize()
+            enc.check_status(dev)
+            runs.append([out.detach().clone(), xin.grad.clone()] + [p.grad.clone() for p in layer.parameters()])
+    finally:
+        enc.OVERLAP = prev
+    for other in runs[1:]:
+        for a, b in zip(runs[0], other):
+            assert torch.equal(a, b)
