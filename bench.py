@@ -27,7 +27,7 @@ PKG = "end-to-end-asr-pytorch_b200"
 METRIC = "utterances/sec hybrid CTC-attn train step"
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the kernel that dominates each call (profiles/, M2 shape)
 NCU_DRAM_BYTES = {
-    "b2asr_decoder_loop_bwd": (66.982912e6 + 0.298752e6, "profiles/r01_ncu_attn_bwd_v1.txt attn_step_bwd_kernel"),
+    "b2asr_decoder_loop_bwd": (54.601472e6 + 0.147968e6, "profiles/r01_ncu_attn_bwd_v2.txt attn_step_bwd_kernel"),
     "b2asr_decoder_loop_fwd": (48.697344e6 + 0.006144e6, "profiles/r01_ncu_attn_fwd_v1.txt attn_step_fwd_kernel"),
 }
 WORKLOAD = "libri_m2"
