@@ -427,7 +427,7 @@ __global__ void __launch_bounds__(MAXNT, MINB) attn_step_bwd_kernel(AttnArgs p) 
   B2_TRACE(p, 27);
 }
 
-int attn_configure(AttnArgs& a, int cluster_hint, size_t extra_floats, size_t* smem_out);
+int attn_configure(AttnArgs& a, int cluster_hint, size_t extra_floats, size_t* smem_out, size_t cap_bytes = 0);
 int attn_launch(void (*kern)(AttnArgs), const AttnArgs& a, size_t smem, cudaStream_t st);
 
 }  // namespace b2asr

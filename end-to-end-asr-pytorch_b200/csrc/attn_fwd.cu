@@ -313,7 +313,7 @@ __global__ void __launch_bounds__(MAXNT, MINB) attn_step_fwd_kernel(AttnArgs p) 
 
 
 // ---------------------------------------------------------------------------------------------
-int attn_configure(AttnArgs& a, int cluster_hint, size_t extra_floats, size_t* smem_out) {
+int attn_configure(AttnArgs& a, int cluster_hint, size_t extra_floats, size_t* smem_out, size_t cap_bytes = 0) {
   B2_REQUIRE(a.A % 4 == 0 && a.D % 4 == 0, B2ASR_EUNSUPPORTED, "attn: A=%d and D=%d must be multiples of 4", a.A, a.D);
   B2_REQUIRE(a.A <= 512, B2ASR_EUNSUPPORTED, "attn: attention dim %d > 512 unsupported", a.A);
   B2_REQUIRE(a.mode == 0 || (a.C >= 1 && a.C <= kAttMaxC && a.Kw >= 0 && a.Kw <= 256), B2ASR_EUNSUPPORTED,
@@ -344,6 +344,7 @@ int attn_configure(AttnArgs& a, int cluster_hint, size_t extra_floats, size_t* s
   AttnSmem L = attn_smem_layout(a, extra_floats);
   size_t cap = 227 * 1024;
   { const char* e = getenv("B2ASR_ATT_CAP_KB"); if (e && *e) cap = (size_t)atoi(e) * 1024; }
+  if (cap_bytes) cap = cap_bytes;
   while (L.total > cap && a.NS > 2) { a.NS--; L = attn_smem_layout(a, extra_floats); }
   B2_REQUIRE(L.total <= 227 * 1024, B2ASR_EUNSUPPORTED, "attn: needs %zu bytes of shared memory (T=%d too long for cluster %d)", L.total, a.T, CS);
   *smem_out = L.total;
@@ -405,8 +406,26 @@ extern "C" int b2asr_attn_step_fwd(int mode, const float* s, int64_t s_stride, c
   g_attn_row_stride = 0;
   a.trace = attn_trace_buffer();
   size_t smem = 0;
-  int rc = attn_configure(a, cluster, 0, &smem);
+  static const int fwd_cs = [] { const char* e = getenv("B2ASR_ATT_FWD_CS"); return e && *e ? atoi(e) : 0; }();
+  static const int fwd_cap = [] { const char* e = getenv("B2ASR_ATT_FWD_CAP_KB"); return e && *e ? atoi(e) : 0; }();
+  const AttnArgs a0 = a;
+  int rc = attn_configure(a, cluster > 0 ? cluster : fwd_cs, 0, &smem, (size_t)fwd_cap * 1024);
   if (rc != B2ASR_OK) return rc;
+  // The automatic cluster size stops doubling when the grid would exceed one CTA per SM.  The forward kernel is
+  // compiled for two CTAs per SM, and twice the clusters at half the frames each -- ring capped at 113 KB so that two
+  // CTAs share an SM -- is faster when the slices stay long enough (M2: 36.4 -> 34.3 us alone, 43.3 -> 39.3 us per
+  // step inside the decoder loop).  The backward kernel keeps one CTA per SM (A/B in DESIGN.md section 5).
+  if (cluster <= 0 && fwd_cs == 0 && a.NT <= 320) {
+    const int cs2 = a.CS * 2;
+    if (cs2 <= kAttMaxCluster && a.B * cs2 > 148 && a.B * cs2 <= 2 * 148 && (a.T + cs2 * 2 - 1) / (cs2 * 2) >= 16) {
+      AttnArgs a2 = a0;
+      size_t smem2 = 0;
+      if (attn_configure(a2, cs2, 0, &smem2, (size_t)113 * 1024) == B2ASR_OK && smem2 <= (size_t)113 * 1024) {
+        a = a2;
+        smem = smem2;
+      }
+    }
+  }
   void (*kern)(AttnArgs);
   const bool small = a.NT <= 320;
   if (a.C <= 12) kern = small ? attn_step_fwd_kernel<12, 320, 2> : attn_step_fwd_kernel<12, 512, 1>;
