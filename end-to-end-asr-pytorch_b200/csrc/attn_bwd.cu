@@ -443,8 +443,12 @@ extern "C" int b2asr_attn_slots(int B, int T, int D, int A, int dec, int mode, i
   a.mode = mode; a.B = B; a.T = T; a.D = D; a.A = A; a.dec = dec; a.C = C; a.Kw = Kw;
   size_t smem = 0;
   if (attn_configure(a, cluster, 0, &smem) != B2ASR_OK) return B2ASR_EUNSUPPORTED;
-  // the backward may settle on fewer ring stages but never on another cluster size
-  return B * a.CS;
+  // the backward may settle on fewer ring stages, and on twice the clusters when two CTAs per SM fit (see
+  // b2asr_attn_step_bwd): a few unused zero slots cost nothing
+  const int cs2 = a.CS * 2;
+  const bool may_widen = cluster <= 0 && a.NT <= 320 && cs2 <= kAttMaxCluster && B * cs2 > 148 && B * cs2 <= 2 * 148 &&
+                         (T + cs2 * 2 - 1) / (cs2 * 2) >= 16;
+  return B * (may_widen ? cs2 : a.CS);
 }
 
 extern "C" int b2asr_attn_step_bwd(int mode, const float* Wphi, const float* keys, int64_t k_bstride,
@@ -475,27 +479,47 @@ extern "C" int b2asr_attn_step_bwd(int mode, const float* Wphi, const float* key
   a.trace = attn_trace_buffer();
   // first pass fixes CS/NT/tiles, second pass sizes the ring with the backward's extra arrays
   size_t smem = 0;
+  const AttnArgs a0 = a;
   int rc = attn_configure(a, cluster, 0, &smem);
   if (rc != B2ASR_OK) return rc;
-  const int cs = a.CS;
-  if (a.TFK > 32) a.TFK = 32;
-  const BwdExtra X = attn_bwd_extra(a);
-  a.NS = 4;
   size_t cap = 227 * 1024;
   { const char* e = getenv("B2ASR_ATT_CAP_KB"); if (e && *e) cap = (size_t)atoi(e) * 1024; }
-  AttnSmem L = attn_smem_layout(a, X.total);
-  while (L.total > cap && a.NS > 2) { a.NS--; L = attn_smem_layout(a, X.total); }
-  BwdExtra X2 = X;
-  while (L.total > cap && a.TFK > 2 && a.TFH > 1) {     // long slices: shrink the ring tiles
-    a.stage_bytes = (unsigned)align_up((size_t)a.stage_bytes / 2, 128);
-    const unsigned rk = (unsigned)A * 4u, rh = (unsigned)D * 4u;
-    a.TFK = (int)(a.stage_bytes / rk); if (a.TFK > 32) a.TFK = 32; if (a.TFK < 1) a.TFK = 1;
-    a.TFH = (int)(a.stage_bytes / rh); if (a.TFH < 1) a.TFH = 1;
-    const unsigned need = (rk * a.TFK > rh * a.TFH) ? rk * a.TFK : rh * a.TFH;
-    if (a.stage_bytes < need) a.stage_bytes = (unsigned)align_up((size_t)need, 128);
-    X2 = attn_bwd_extra(a);
-    L = attn_smem_layout(a, X2.total);
+  // second pass: size the ring with the backward's extra arrays under a shared-memory cap
+  auto size_ring = [&](AttnArgs& q, size_t limit) {
+    if (q.TFK > 32) q.TFK = 32;
+    q.NS = 4;
+    AttnSmem R = attn_smem_layout(q, attn_bwd_extra(q).total);
+    while (R.total > limit && q.NS > 2) { q.NS--; R = attn_smem_layout(q, attn_bwd_extra(q).total); }
+    while (R.total > limit && q.TFK > 2 && q.TFH > 1) {     // long slices: shrink the ring tiles
+      q.stage_bytes = (unsigned)align_up((size_t)q.stage_bytes / 2, 128);
+      const unsigned rk = (unsigned)A * 4u, rh = (unsigned)D * 4u;
+      q.TFK = (int)(q.stage_bytes / rk); if (q.TFK > 32) q.TFK = 32; if (q.TFK < 1) q.TFK = 1;
+      q.TFH = (int)(q.stage_bytes / rh); if (q.TFH < 1) q.TFH = 1;
+      const unsigned need = (rk * q.TFK > rh * q.TFH) ? rk * q.TFK : rh * q.TFH;
+      if (q.stage_bytes < need) q.stage_bytes = (unsigned)align_up((size_t)need, 128);
+      R = attn_smem_layout(q, attn_bwd_extra(q).total);
+    }
+    return R;
+  };
+  // Like the forward kernel (attn_fwd.cu): when the automatic cluster size stopped only at one CTA per SM, twice the
+  // clusters with the ring capped at 113 KB (two CTAs per SM, the <= 102-register build) is faster inside the decoder
+  // loop (M2: 16.0 -> 15.5 ms per batch), although the kernel timed alone is slower that way (73 -> 79 us).
+  static const bool env_cfg = (getenv("B2ASR_ATT_CS") && *getenv("B2ASR_ATT_CS")) || (getenv("B2ASR_ATT_CAP_KB") && *getenv("B2ASR_ATT_CAP_KB"));
+  bool wide = false;
+  AttnSmem L = {};
+  if (cluster <= 0 && !env_cfg && a.NT <= 320) {
+    const int cs2 = a.CS * 2;
+    if (cs2 <= kAttMaxCluster && a.B * cs2 > 148 && a.B * cs2 <= 2 * 148 && (a.T + cs2 * 2 - 1) / (cs2 * 2) >= 16) {
+      AttnArgs a2 = a0;
+      size_t smem2 = 0;
+      if (attn_configure(a2, cs2, 0, &smem2, (size_t)113 * 1024) == B2ASR_OK) {
+        const AttnSmem L2 = size_ring(a2, (size_t)113 * 1024);
+        if (L2.total <= (size_t)113 * 1024) { a = a2; L = L2; wide = true; }
+      }
+    }
   }
+  const int cs = a.CS;
+  if (!wide) L = size_ring(a, cap);
   B2_REQUIRE(L.total <= 227 * 1024, B2ASR_EUNSUPPORTED, "attn_step_bwd: needs %zu bytes of shared memory (T=%d, cluster %d)", L.total, T, cs);
   const bool two = a.NT <= 320 && L.total <= 113 * 1024;      // two CTAs per SM fit: compile for <= 102 registers
   void (*kern)(AttnArgs);
