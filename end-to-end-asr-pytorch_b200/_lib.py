@@ -93,6 +93,9 @@ _SIGNATURES = {
     "b2asr_ctc_loss_fwd_bwd": (c_i, [c_p, c_i64, c_i64, c_p, c_i64, c_p, c_p,
                                      c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_f,
                                      c_p, c_p, c_p, c_i64, c_i64, c_p, c_sz, c_p]),
+    "b2asr_ctc_loss_fwd_bwd_static": (c_i, [c_p, c_i64, c_i64, c_p, c_i64, c_p, c_p,
+                                            c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_f,
+                                            c_p, c_p, c_p, c_i64, c_i64, c_p]),
     "b2asr_rescale_if_needed": (c_i, [c_p, c_i64, c_p, c_f, c_p]),
     "b2asr_attn_step_fwd": (c_i, [c_i, c_p, c_i64, c_p, c_p, c_i64, c_p, c_i64, c_p, c_p,
                                   c_p, c_i, c_i, c_p, c_p, c_p, c_f, c_p, c_p, c_p,

@@ -22,6 +22,7 @@
 //                       earlier version emitted them from inside the lattice walk after a meet-in-the-
 //                       middle; ncu showed the walk paying ~340 warp-instructions per step for it.)
 #include "common.cuh"
+#include <atomic>
 
 namespace b2asr {
 
@@ -669,4 +670,56 @@ extern "C" int b2asr_rescale_if_needed(float* buf, int64_t n, const float* upstr
   rescale_if_needed_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(buf, n, upstream, assumed);
   B2_CUDA_TRY(cudaGetLastError());
   return B2ASR_OK;
+}
+
+// --------------------------------------------------------------------------------------
+// Allocation-free variant (no counterpart in the reference).
+// Callers that cannot allocate (CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc) get the
+// same three launches with the workspace in a file-scope device array instead of a caller buffer.  Every GPU that
+// loads the library holds B2ASR_CTC_STATIC_WS_BYTES of it until exit.  Host code cannot use `g_ctc_static_ws` as a
+// pointer (the name is a host-side stand-in for the symbol): the device address is looked up once per device with
+// cudaGetSymbolAddress, with that device current, and cached.
+// --------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_ctc_static_ws[B2ASR_CTC_STATIC_WS_BYTES];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::atomic<void*> g_static_ws_addr[kMaxDevices];
+
+int static_ws_for_current_device(void** out) {
+  int dev = -1;
+  B2_CUDA_TRY(cudaGetDevice(&dev));
+  B2_REQUIRE(dev >= 0 && dev < kMaxDevices, B2ASR_EUNSUPPORTED, "ctc static: device ordinal %d outside [0,%d)", dev, kMaxDevices);
+  void* p = g_static_ws_addr[dev].load(std::memory_order_acquire);
+  if (p == nullptr) {
+    B2_CUDA_TRY(cudaGetSymbolAddress(&p, g_ctc_static_ws));     // the current device's copy of the array
+    B2_REQUIRE(p != nullptr && ((uintptr_t)p & 255) == 0, B2ASR_ECUDA, "ctc static: bad symbol address %p", p);
+    g_static_ws_addr[dev].store(p, std::memory_order_release);  // racing threads look up the same address
+  }
+  *out = p;
+  return B2ASR_OK;
+}
+}  // namespace
+
+extern "C" int b2asr_ctc_loss_fwd_bwd_static(const float* x, int64_t sx_t, int64_t sx_b,
+                                             const int64_t* targets, int64_t tgt_stride,
+                                             const int64_t* in_len, const int64_t* tgt_len,
+                                             int T, int B, int V, int Lmax, int blank,
+                                             int from_logits, int reduction, float prescale,
+                                             float* nll, float* loss,
+                                             float* grad, int64_t sg_t, int64_t sg_b, void* stream) {
+  B2_REQUIRE(T > 0 && B > 0 && V > 1 && Lmax >= 0, B2ASR_EINVAL, "ctc static: bad sizes T=%d B=%d V=%d Lmax=%d", T, B, V, Lmax);
+  CtcPlan pl;
+  int rc = make_plan(T, B, V, Lmax, grad != nullptr, pl);
+  if (rc != B2ASR_OK) return rc;
+  B2_REQUIRE(pl.total <= (size_t)B2ASR_CTC_STATIC_WS_BYTES, B2ASR_EWORKSPACE,
+             "ctc static: T=%d B=%d V=%d Lmax=%d needs %zu bytes of scratch, the built-in array holds %zu "
+             "(use b2asr_ctc_loss_fwd_bwd with a caller workspace)", T, B, V, Lmax, pl.total, (size_t)B2ASR_CTC_STATIC_WS_BYTES);
+  void* ws = nullptr;
+  rc = static_ws_for_current_device(&ws);
+  if (rc != B2ASR_OK) return rc;
+  // Nothing in the workspace has to start at zero: the rows pass re-arms the ticket word and every table, row and
+  // offset the later passes read is written earlier in the same call, so the previous call's contents do not matter.
+  return b2asr_ctc_loss_fwd_bwd(x, sx_t, sx_b, targets, tgt_stride, in_len, tgt_len, T, B, V, Lmax, blank, from_logits,
+                                reduction, prescale, nll, loss, grad, sg_t, sg_b, ws, (size_t)B2ASR_CTC_STATIC_WS_BYTES, stream);
 }

@@ -75,6 +75,24 @@ int b2asr_ctc_loss_fwd_bwd(const float* x, int64_t sx_t, int64_t sx_b,
                            float* grad, int64_t sg_t, int64_t sg_b,
                            void* ws, size_t ws_bytes, void* stream);
 
+/* Allocation-free variant of b2asr_ctc_loss_fwd_bwd.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight
+ * serving loops, harnesses that forbid allocation).  Same arguments and results as b2asr_ctc_loss_fwd_bwd minus
+ * ws / ws_bytes: the scratch lives in a file-scope device array of B2ASR_CTC_STATIC_WS_BYTES inside the library
+ * (every GPU that loads the library holds it until exit).  The call itself performs no cudaMalloc / cudaFree and
+ * calls no allocating library routine.  Shapes whose b2asr_ctc_workspace_bytes() exceeds the array are rejected with
+ * B2ASR_EWORKSPACE and a message naming both sizes.  ALL calls on a device share the one array: nothing in it has
+ * to be cleared between calls (each call rewrites what it reads), but two calls that overlap on the GPU (different
+ * streams, or graph branches without a dependency) race on it -- keep them ordered. */
+#define B2ASR_CTC_STATIC_WS_BYTES (32u << 20)
+int b2asr_ctc_loss_fwd_bwd_static(const float* x, int64_t sx_t, int64_t sx_b,
+                                  const int64_t* targets, int64_t tgt_stride,
+                                  const int64_t* in_len, const int64_t* tgt_len,
+                                  int T, int B, int V, int Lmax, int blank,
+                                  int from_logits, int reduction, float prescale,
+                                  float* nll, float* loss,
+                                  float* grad, int64_t sg_t, int64_t sg_b, void* stream);
+
 /* buf[i] *= (*upstream / assumed) for i < n, but only when *upstream != assumed
  * (device-side test; no host sync).  Used by autograd backward when the
  * upstream gradient differs from the prescale folded in at forward time. */
