@@ -28,7 +28,7 @@ import torch.nn.functional as F
 from torch.distributions.categorical import Categorical
 from torch.nn.utils.rnn import pack_padded_sequence, pad_packed_sequence
 
-from . import _attn, _dec, _decloop, _enc
+from . import _attn, _dec, _decloop, _enc, fp32_library_math
 
 CTC_BEAM_RATIO = 1.5   # asr.py:15
 # B2ASR_ENC=cudnn keeps the Listener's LSTMs on the library's per-frame path (A/B measurements only)
@@ -397,6 +397,7 @@ class Seq2Seq(nn.Module):
 
     def __init__(self, example_input, output_dim, model_para):
         super().__init__()
+        fp32_library_math()
         enc = model_para['encoder']
         enc_out_dim = int(enc['dim'].split('_')[-1]) * (2 if 'Bi' in enc['enc_type'] else 1) \
             * (int(enc['sample_rate'].split('_')[-1]) if enc['sample_style'] == 'concat' else 1)

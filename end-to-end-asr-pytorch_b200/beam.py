@@ -276,25 +276,3 @@ def beam_decode(model, audio_feature, decode_step, state_len, decode_beam_size, 
                     one_step(t & 1)
                     bs.flip()
         return bs.results(emb=model.embed)
-
-
-def smoke(dev):
-    """Tiny beam search on random log-probs, compared token-for-token with the CPU oracle."""
-    from oracle import beam_oracle as bo
-    g = torch.Generator().manual_seed(5)
-    V, T, n, steps = 40, 30, 4, 6
-    x_ctc = F.log_softmax(torch.randn(T, V, generator=g) * 2, dim=-1)
-    table = F.log_softmax(torch.randn(steps, V, V, generator=g) * 2, dim=-1)   # logp = f(step, last token)
-    bs = BeamSearch(V, n, steps, dev, x_ctc=x_ctc, ctc_weight=0.5)
-    tab_d = table.to(dev)
-    for t in range(steps):
-        bs.step(tab_d[t].index_select(0, bs.last_tokens).contiguous())
-    got = [(o.outIndex, float(o.avgScore())) for o in bs.results()]
-
-    def step_fn(entry):
-        return table[len(entry.tokens)][entry.tokens[-1] if entry.tokens else 0], None, None
-
-    want = bo.joint_beam_search(step_fn, None, steps, n, x_ctc.numpy(), 0.5, 0.0)
-    want = [([int(t) for t in e.tokens], float(e.mean_score())) for e in want]
-    assert [a for a, _ in got] == [a for a, _ in want], (got, want)
-    assert all(abs(a - b) <= 1e-4 * abs(b) + 1e-5 for (_, a), (_, b) in zip(got, want)), (got, want)

@@ -6,10 +6,13 @@ reference's batch-1 call per hypothesis, so the LM weights are read once per dec
 import torch
 import torch.nn as nn
 
+from . import fp32_library_math
+
 
 class RNN_LM(nn.Module):
     def __init__(self, emb_dim, h_dim, out_dim, layers=1, rnn='LSTM', dropout_rate=0.0):
         super().__init__()
+        fp32_library_math()
         self.h_dim = h_dim
         self.emb = nn.Embedding(out_dim, emb_dim)
         self.drop1 = nn.Dropout(dropout_rate)

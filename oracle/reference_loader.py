@@ -17,11 +17,26 @@ import os
 import sys
 import types
 
-REFERENCE_ROOT = os.environ.get("B2ASR_REFERENCE_ROOT", "/root/reference")
+_HERE = os.path.dirname(os.path.abspath(__file__))
+# where the reference can be: the build container's read-only mount, or the copy oracle/make_ref.py places under
+# oracle/_ref/ (git-ignored, travels with the gpurun snapshot) so bench.py's CPU arm can time the real reference
+UPSTREAM_ROOT = "/root/reference"
+SHIPPED_ROOT = os.path.join(_HERE, "_ref")
+
+
+def reference_root():
+    env = os.environ.get("B2ASR_REFERENCE_ROOT")
+    for cand in ([env] if env else []) + [UPSTREAM_ROOT, SHIPPED_ROOT]:
+        if os.path.isfile(os.path.join(cand, "src", "asr.py")):
+            return os.path.realpath(cand)
+    return None
+
+
+REFERENCE_ROOT = reference_root() or UPSTREAM_ROOT
 
 
 def available() -> bool:
-    return os.path.isfile(os.path.join(REFERENCE_ROOT, "src", "asr.py"))
+    return reference_root() is not None
 
 
 def _levenshtein(a, b):
@@ -56,38 +71,63 @@ def _install_stubs():
 
 
 _cache = {}
+_MODULES = ("preprocess", "ctc", "postprocess", "dataset", "asr", "rnnlm", "clm", "solver")
 
 
-def load():
-    """Return a namespace with the reference's modules: .asr .ctc .postprocess .rnnlm .solver"""
-    if "ns" in _cache:
-        return _cache["ns"]
-    if not available():
-        raise RuntimeError("reference not mounted at %s" % REFERENCE_ROOT)
+def load(root=None):
+    """Return a namespace with the reference's modules: .asr .ctc .postprocess .rnnlm .solver ...
+
+    The reference imports itself as the top-level package `src` (a NAMESPACE package: upstream has no
+    src/__init__.py).  This repo ships a regular `src` shim package, and Python prefers a regular package anywhere on
+    sys.path over a namespace portion, so `import src.asr` with both on the path would return the B200 mirror.
+    Here the reference's files are therefore imported BY PATH: a private package object whose __path__ is the
+    reference's src/ directory stands in as sys.modules['src'] for the duration of the import, every module's
+    __file__ is asserted to lie under the reference root, and the caller's own `src` modules are put back after."""
+    root = os.path.realpath(root) if root else reference_root()
+    if root is None:
+        raise RuntimeError("reference not found at %s or %s" % (UPSTREAM_ROOT, SHIPPED_ROOT))
+    if root in _cache:
+        return _cache[root]
     import importlib
+    import importlib.machinery
+    import importlib.util
     import torch
 
     _install_stubs()
     torch.ByteTensor = torch.BoolTensor  # shim 2
-    # The reference imports itself as the top-level package `src`; our repo also
-    # ships a `src` shim package, so import the reference's under a private root.
-    saved_path = list(sys.path)
-    saved_src = {k: v for k, v in sys.modules.items() if k == "src" or k.startswith("src.")}
-    for k in saved_src:
+    src_dir = os.path.join(root, "src")
+    saved = {k: v for k, v in sys.modules.items() if k == "src" or k.startswith("src.")}
+    for k in saved:
         del sys.modules[k]
-    sys.path.insert(0, REFERENCE_ROOT)
+    private = types.ModuleType("src")
+    private.__path__ = [src_dir]
+    private.__package__ = "src"
+    private.__spec__ = importlib.machinery.ModuleSpec("src", None, is_package=True)
+    private.__spec__.submodule_search_locations = [src_dir]
+    sys.modules["src"] = private
     try:
-        ns = types.SimpleNamespace()
-        ns.ctc = importlib.import_module("src.ctc")
-        ns.postprocess = importlib.import_module("src.postprocess")
-        ns.asr = importlib.import_module("src.asr")
-        ns.rnnlm = importlib.import_module("src.rnnlm")
-        ns.solver = importlib.import_module("src.solver")
+        ns = types.SimpleNamespace(root=root)
+        for name in _MODULES:
+            path = os.path.join(src_dir, name + ".py")
+            if not os.path.isfile(path):
+                continue
+            full = "src." + name
+            mod = sys.modules.get(full)
+            if mod is None:
+                spec = importlib.util.spec_from_file_location(full, path)
+                mod = importlib.util.module_from_spec(spec)
+                sys.modules[full] = mod
+                spec.loader.exec_module(mod)
+                setattr(private, name, mod)
+            setattr(ns, name, mod)
         ns.modules = {k: v for k, v in sys.modules.items() if k == "src" or k.startswith("src.")}
+        for k, v in ns.modules.items():
+            f = getattr(v, "__file__", None)
+            if k != "src" and not (f and os.path.realpath(f).startswith(root + os.sep)):
+                raise RuntimeError("reference_loader: %s resolved to %s, outside the reference root %s" % (k, f, root))
     finally:
         for k in [k for k in sys.modules if k == "src" or k.startswith("src.")]:
             del sys.modules[k]
-        sys.modules.update(saved_src)
-        sys.path[:] = saved_path
-    _cache["ns"] = ns
+        sys.modules.update(saved)
+    _cache[root] = ns
     return ns

@@ -82,6 +82,30 @@ def test_loc_steps_match_oracle(cuda, B, T, D, A, dec, cluster):
         prev64 = att.double().cpu()  # and keep the oracle on the same trajectory
 
 
+@pytest.mark.parametrize("B,T,D,A,dec", [(4, 50, 64, 32, 48), (8, 400, 640, 300, 320)])
+def test_loc_chain_of_20_steps_against_free_running_oracle(cuda, B, T, D, A, dec):
+    """Error growth through prev_att (asr.py:456): kernel and float64 oracle each feed back THEIR OWN alignment for
+    20 steps -- nothing re-synchronises them -- and the last step's alpha / ctx still meet the 1e-4 bar."""
+    at = _attn()
+    w = make_weights(A, D, dec)
+    h, lens, states = make_batch(B, T, D, dec, seed=21, nstates=20)
+    keys64 = ao.project_keys(h.double(), w["psi_w"].double(), w["psi_b"].double())
+    w64 = {k: v.double() for k, v in w.items()}
+    wd = {k: v.to(cuda) for k, v in w.items()}
+    hd, kd = h.to(cuda), keys64.float().to(cuda)
+    ld = at.lens_i32(lens, cuda)
+    prev, prev64 = None, ao.uniform_alignment(lens, T, torch.float64)
+    worst_a = worst_c = 0.0
+    for s in states:
+        a64, c64 = ao.loc_step(s.double(), h.double(), keys64.float().double(), lens, prev64, w64)
+        att, ctx, _ = at.step_forward("loc", s.to(cuda), wd["phi"], kd, hd, ld, prev, wd["loc_conv"], wd["loc_proj"],
+                                      wd["gen_w"], wd["gen_b"], 2.0)
+        worst_a = max(worst_a, worst(att, a64, 1e-4, 1e-6))
+        worst_c = max(worst_c, worst(ctx, c64, 1e-4, 1e-5 * float(c64.abs().max())))
+        prev, prev64 = att, a64                      # two independent trajectories
+    assert worst_a <= 1.0 and worst_c <= 1.0, "over 20 free-running steps: alpha %.2f ctx %.2f (err/tol)" % (worst_a, worst_c)
+
+
 @pytest.mark.parametrize("B,T,D,A,dec", SHAPES[:3])
 def test_dot_steps_match_oracle(cuda, B, T, D, A, dec):
     at = _attn()

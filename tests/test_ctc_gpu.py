@@ -179,6 +179,31 @@ def test_long_sequence_is_closer_to_float64_than_fp32_aten(cuda):
     assert float((err / (1e-4 * g64.abs() + 5e-4 * scale.view(2, 1, 1))).max()) <= 1.0
 
 
+def test_m5_maximum_gradient_against_float64(cuda):
+    """BASELINE.json config 5 at its largest point (T'=3000, L=600, V=5000), two utterances: nll and the WHOLE
+    gradient against the float64 evaluation of the reference's call sequence (solver.py:160 + torch CTCLoss).
+    Tolerance: nll 1e-5 relative; gradient 1e-4 relative + 1e-3 of the row scale 1/(B*L_b) (3000 fp32 log-space
+    steps; the fp32 ATen kernel the reference runs is required to be at least 10x further from float64)."""
+    m = _mod()
+    x, y, il, tl = make_case(2, 3000, 5000, 600, seed=33)
+    il[1] = 2400
+    _, nll64, g64 = co.reference_call(x, y, il.tolist(), tl, torch.float64)
+    _, _, g32 = co.reference_call(x, y, il.tolist(), tl, torch.float32)
+    xd = x.to(cuda).requires_grad_(True)
+    loss, nll = m.ctc_loss(xd, y.to(cuda), il, tl, from_logits=True, batch_first=True, return_nll=True)
+    loss.backward()
+    g = xd.grad.cpu().double()
+    assert torch.allclose(nll.cpu().double(), nll64, rtol=1e-5)
+    err = (g - g64).abs()
+    scale = (1.0 / (2 * tl.double())).view(2, 1, 1)
+    ratio = float((err / (1e-4 * g64.abs() + 1e-3 * scale)).max())
+    aten = float((g32.double() - g64).abs().max())
+    print("T'=3000 gradient: worst err/tol %.3f, max abs err ours %.3e, ATen fp32 %.3e" % (ratio, float(err.max()), aten))
+    assert ratio <= 1.0, ratio
+    assert float(err.max()) <= aten / 10, (float(err.max()), aten)
+    assert float(g[1, 2400:].abs().max()) == 0.0
+
+
 def test_determinism(cuda):
     m = _mod()
     x, y, il, tl = make_case(6, 120, 31, 40, seed=9, repeats=0.4)

@@ -177,20 +177,120 @@ def seqloss_fixture(ref):
     return out
 
 
-def main():
+MID_CFG = {
+    'optimizer': {'type': 'Adadelta', 'learning_rate': 1.0, 'joint_ctc': 0.5},
+    'encoder': {'enc_type': 'BiRNN', 'sample_rate': '2_2', 'sample_style': 'drop', 'dim': '320_320',
+                'dropout': '0_0', 'rnn_cell': 'LSTM'},
+    'attention': {'att_mode': 'loc', 'dim': 300, 'proj': True, 'num_head': 1},
+    'decoder': {'dim': 320, 'layer': 1, 'dropout': 0.0, 'rnn_cell': 'LSTMCell'},
+}
+MID_SEED = 31
+
+
+def midsize_fixture(ref, att_mode):
+    """The reference's teacher-forced forward + hybrid loss + backward (asr.py:58-112, solver.py:149-163,177) at the
+    layer widths the shipped configs use (attention 300, decoder 320, D = 640 encoder features, T' = 100 frames, 30
+    decoder steps), so that the GPU test exercises the real tiling of decloop.cu / deccell.cu / attn_*.cu against the
+    reference rather than against the per-step GPU path.  Weights are oracle/seeded.reseed_parameters(MID_SEED);
+    large gradients are stored as oracle/seeded.summarise_gradient samples."""
+    from oracle import seeded
+    import copy
+    seed_all(13)
+    cfg = copy.deepcopy(MID_CFG)
+    cfg['attention']['att_mode'] = att_mode
+    B, T, D, V = 4, 400, 40, 31
+    g = torch.Generator().manual_seed(14)
+    lens = [400, 372, 316, 248]
+    x = torch.randn(B, T, D, generator=g)
+    for b, n in enumerate(lens):
+        x[b, n:] = 0
+    label_lens = [29, 26, 21, 14]                  # + <eos> -> 30 decoder steps
+    y = torch.zeros(B, max(label_lens) + 2, dtype=torch.long)
+    for b, n in enumerate(label_lens):
+        toks = torch.randint(2, V, (n,), generator=g)
+        y[b, 1:n + 1] = toks
+        y[b, n + 1] = 1
+    model = ref.asr.Seq2Seq(x, V, cfg)
+    seeded.reseed_parameters(model, MID_SEED)
+    model.train()
+    ans_len = int(torch.max(torch.sum(y != 0, dim=-1)))
+    ctc_pred, enc_len, att_pred, att_maps = model(x, ans_len, tf_rate=1.0, teacher=y, state_len=lens)
+    label = y[:, 1:ans_len + 1].contiguous()
+    b, t, c = att_pred.shape
+    seq_loss = torch.nn.CrossEntropyLoss(ignore_index=0, reduction='none')
+    att_loss = seq_loss(att_pred.view(b * t, c), label.view(-1))
+    att_loss = torch.mean(torch.sum(att_loss.view(b, t), dim=-1) / torch.sum(y != 0, dim=-1).float())
+    tl = torch.sum(y != 0, dim=-1)
+    ctc_loss = torch.nn.CTCLoss(blank=0, reduction='mean')(F.log_softmax(ctc_pred.transpose(0, 1), dim=-1), label,
+                                                           torch.LongTensor(enc_len), tl)
+    loss = 0.5 * att_loss + 0.5 * ctc_loss
+    loss.backward()
+    grads = {k: seeded.summarise_gradient(k, p.grad, MID_SEED) for k, p in model.named_parameters()}
+    return dict(cfg=cfg, vocab=V, seed=MID_SEED, x=x, y=y, lens=lens,
+                param_shapes={k: tuple(p.shape) for k, p in model.named_parameters()},
+                ctc_pred=ctc_pred.detach(), att_pred=att_pred.detach(), att_maps=att_maps[0].detach(), enc_len=enc_len,
+                att_loss=att_loss.detach(), ctc_loss=ctc_loss.detach(), loss=loss.detach(), grads=grads)
+
+
+FIXTURES = {
+    'attention_loc.pt': lambda ref: attention_fixture(ref, 'loc'),
+    'attention_dot.pt': lambda ref: attention_fixture(ref, 'dot'),
+    'prefix.pt': prefix_fixture,
+    'trainstep.pt': model_fixture,
+    'beam_joint.pt': lambda ref: beam_fixture(ref, 0.5, 0.5, 4, 21),
+    'beam_att_only.pt': lambda ref: beam_fixture(ref, 0.0, 0.0, 3, 22),
+    'beam_ctc.pt': lambda ref: beam_fixture(ref, 0.3, 0.0, 5, 23),
+    'seqloss.pt': seqloss_fixture,
+    'midsize_loc.pt': lambda ref: midsize_fixture(ref, 'loc'),
+    'midsize_dot.pt': lambda ref: midsize_fixture(ref, 'dot'),
+}
+
+
+def deep_equal(a, b):
+    if isinstance(a, dict):
+        return isinstance(b, dict) and a.keys() == b.keys() and all(deep_equal(a[k], b[k]) for k in a)
+    if isinstance(a, (list, tuple)):
+        return type(a) is type(b) and len(a) == len(b) and all(deep_equal(u, v) for u, v in zip(a, b))
+    if torch.is_tensor(a):
+        return torch.is_tensor(b) and a.dtype == b.dtype and a.shape == b.shape and \
+            bool((a.reshape(-1).view(torch.uint8) == b.reshape(-1).view(torch.uint8)).all() if a.numel() else True)
+    if isinstance(a, np.ndarray):
+        return isinstance(b, np.ndarray) and a.dtype == b.dtype and a.shape == b.shape and a.tobytes() == b.tobytes()
+    return a == b
+
+
+def check():
+    """Regenerate every fixture from the reference and compare it bit for bit with the committed file."""
     ref = reference_loader.load()
-    os.makedirs(OUT, exist_ok=True)
-    if len(sys.argv) > 1 and sys.argv[1] == 'seqloss':      # add this fixture without regenerating the others
-        torch.save(seqloss_fixture(ref), os.path.join(OUT, 'seqloss.pt'))
+    assert ref.asr.__file__.startswith(reference_loader.UPSTREAM_ROOT + os.sep), ref.asr.__file__
+    bad = []
+    for name, fn in FIXTURES.items():
+        want = torch.load(os.path.join(OUT, name), weights_only=False)
+        same = deep_equal(fn(ref), want)
+        print("%-20s %s" % (name, "bit-identical" if same else "DIFFERS"))
+        if not same:
+            bad.append(name)
+    return bad
+
+
+def main():
+    if len(sys.argv) > 1 and sys.argv[1] == '--check':
+        sys.exit(1 if check() else 0)
+    if len(sys.argv) > 1:                                    # python tools/make_golden.py midsize_loc.pt ...
+        ref = reference_loader.load()
+        for name in sys.argv[1:]:
+            torch.save(FIXTURES[name](ref), os.path.join(OUT, name))
+            print(name, os.path.getsize(os.path.join(OUT, name)))
         return
-    torch.save(attention_fixture(ref, 'loc'), os.path.join(OUT, 'attention_loc.pt'))
-    torch.save(attention_fixture(ref, 'dot'), os.path.join(OUT, 'attention_dot.pt'))
-    torch.save(prefix_fixture(ref), os.path.join(OUT, 'prefix.pt'))
-    torch.save(model_fixture(ref), os.path.join(OUT, 'trainstep.pt'))
-    torch.save(beam_fixture(ref, 0.5, 0.5, 4, 21), os.path.join(OUT, 'beam_joint.pt'))
-    torch.save(beam_fixture(ref, 0.0, 0.0, 3, 22), os.path.join(OUT, 'beam_att_only.pt'))
-    torch.save(beam_fixture(ref, 0.3, 0.0, 5, 23), os.path.join(OUT, 'beam_ctc.pt'))
-    torch.save(seqloss_fixture(ref), os.path.join(OUT, 'seqloss.pt'))
+    main_all()
+
+
+def main_all():
+    ref = reference_loader.load()
+    assert ref.asr.__file__.startswith(reference_loader.UPSTREAM_ROOT + os.sep), ref.asr.__file__
+    os.makedirs(OUT, exist_ok=True)
+    for name, fn in FIXTURES.items():
+        torch.save(fn(ref), os.path.join(OUT, name))
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 
