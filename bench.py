@@ -2,7 +2,7 @@
 """Benchmark of the hybrid CTC/attention train step (BASELINE.json metric: utterances/s).
 
     python bench.py --gpus N --steps K --warmup W            # this repo's sm_100a path
-    python bench.py --impl reference --gpus N --steps K --warmup W   # the reference's CPU path (oracle port)
+    python bench.py --impl reference --gpus N --steps K --warmup W   # the reference's own CPU path (oracle/_ref)
 
 A step = one pass of Trainer.exec's body (reference src/solver.py:132-182: forward, CE + CTC loss,
 backward, [gradient all-reduce], clip, NaN guard, optimizer step) over one synthetic
@@ -159,61 +159,73 @@ def use_all_host_threads():
     return torch.get_num_threads()
 
 
-def cpu_train_step_rate(steps, warmup, budget_s, seed=1234):
-    """Times oracle/model_oracle.train_step (restating reference solver.py:132-182 + asr.py:58-112) on a
-    bounded sample of the M2 workload: the first `bs` utterances of the synthetic batch at full length."""
-    import torch
-    from oracle import model_oracle as mo
+CPU_SAMPLE_STRIDE = 8      # the CPU arms time utterances 0, 8, 16, 24 of the 32-utterance batch (every 8th: the batch is
+                           # sorted by length, so a strided pick keeps its length distribution); always the same ones
+
+
+def cpu_sample(workload, seed=1234):
     syn = pkg("synthetic")
-    w = syn.WORKLOADS[WORKLOAD]
-    torch.manual_seed(0)
-    model = mo.OracleModel(w["d_in"], w["vocab"], w["cfg"])
-    opt = torch.optim.Adadelta(model.parameters(), lr=1.0, eps=1e-8)
-    x, y, lens = syn.make_batch(WORKLOAD, seed)
+    w = syn.WORKLOADS[workload]
+    x, y, lens = syn.make_batch(workload, seed)
+    stride = max(1, w["batch"] // 4)
+    xs, ys = x[::stride].contiguous(), y[::stride].contiguous()
+    ans = int((ys != 0).sum(-1).max())
+    ys = ys[:, :ans + 1].contiguous()
+    xs = xs[:, :lens[0]].contiguous()
+    what = "utterances %s of the %d-utterance %s batch (seed %d; T=%d frames, longest label %d)" % (
+        list(range(0, w["batch"], stride)), w["batch"], workload, seed, xs.shape[1], ans)
+    return xs, ys, what
+
+
+def cpu_train_step_rate(steps, warmup, workload=None):
+    """Times the reference's train step (oracle/reference_step.py: the reference's own Seq2Seq.forward, losses,
+    backward, clip, Adadelta step -- reference src/solver.py:132-182) on the host cores, on a FIXED sample of the
+    workload: every 8th utterance of the first synthetic batch at full length, the same 4 in every run."""
+    from oracle import reference_step
+    syn = pkg("synthetic")
+    workload = workload or WORKLOAD
+    w = syn.WORKLOADS[workload]
     cores = use_all_host_threads()
-
-    def run(bs):
-        xs = x[:bs]
-        ys = y[:bs]
-        t0 = time.perf_counter()
-        mo.train_step(model, opt, xs, ys, tf_rate=1.0)
-        return time.perf_counter() - t0
-
-    run(1)                                             # page in / thread pools (untimed)
-    per_utt = run(1)
-    bs = int(max(1, min(w["batch"], budget_s / max(per_utt * (steps + warmup), 1e-6))))
-    # the one-utterance estimate can be off (cache footprint, shared host): the first full-size step doubles as a
-    # calibration, and the sample shrinks if that step alone overran its share of the budget
-    target, warmed = budget_s / max(steps + warmup, 1), 0
-    while True:
-        dt = run(bs)
-        warmed += 1
-        if dt <= 1.5 * target or bs == 1:
-            break
-        bs = max(1, int(bs * target / dt))
-    for _ in range(max(0, warmup - warmed)):
-        run(bs)
+    ref = reference_step.ReferenceStep(w["d_in"], w["vocab"], w["cfg"], "cpu")
+    xs, ys, what = cpu_sample(workload)
+    for _ in range(warmup):
+        ref.step(xs, ys, tf_rate=1.0)
     t0 = time.perf_counter()
     for _ in range(steps):
-        run(bs)
+        ref.step(xs, ys, tf_rate=1.0)
     dt = time.perf_counter() - t0
-    sample = "first %d of %d utterances of the %s batch (T=%d frames, full label length), %d steps" % (
-        bs, w["batch"], WORKLOAD, x.shape[1], steps)
-    return bs * steps / dt, dt / steps * 1e3, cores, sample
+    sample = "%s; %d warm-up + %d timed steps" % (what, warmup, steps)
+    cpu_train_step_rate.n_params = sum(p.numel() for p in ref.model.parameters())
+    return xs.shape[0] * steps / dt, dt / steps * 1e3, cores, sample, ref.kind
+
+
+def bench_config(workload, world, n_params=None):
+    syn = pkg("synthetic")
+    w = syn.WORKLOADS[workload]
+    cfg = {"workload": workload, "batch_per_gpu": w["batch"], "global_batch": w["batch"] * world, "frames": w["t_hi"],
+           "feature_dim": w["d_in"], "vocab": w["vocab"], "parallelism": "dp%d" % world,
+           "l2": "inputs larger than L2: %d distinct batches rotate and one step touches >1 GB of "
+                 "activations (126 MB L2)" % N_BATCHES}
+    if n_params is not None:
+        cfg["params"] = n_params
+    return cfg
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    value, ms, cores, sample = cpu_train_step_rate(args.steps, args.warmup, budget_s=150.0)
+    steps, warmup = max(1, min(args.steps, 10)), max(1, min(args.warmup, 3))
+    value, ms, cores, sample, kind = cpu_train_step_rate(steps, warmup)
+    cfg = bench_config(WORKLOAD, max(1, args.gpus), cpu_train_step_rate.n_params)
+    cfg["note"] = ("the reference's own CPU path (its Seq2Seq.forward + torch.nn.CTCLoss + CrossEntropyLoss + backward + "
+                   "clip + Adadelta, imported unmodified from oracle/_ref) on the host cores of rank 0; a step = the fixed "
+                   "4-utterance sample of the workload's batch, value = utterances of the sample / time")
     out = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": "utterances/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "note": "CPU port of the reference train step (oracle/model_oracle.py); "
-                   "the reference is Python and /root/reference does not travel to the GPU box"},
-        "cpu_baseline": {"value": value, "unit": "utterances/s", "cores": cores, "kind": "port", "sample": sample},
+        "steps": steps, "warmup": warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
+        "cpu_baseline": {"value": value, "unit": "utterances/s", "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": "utterances/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -297,6 +309,153 @@ def cpu_decode_rate(n_steps=2):
     return {"rtf": rtf, "ms_per_decode_step": per_step * 1e3, "cores": torch.get_num_threads(), "kind": "port",
             "sample": "1 utterance: encoder + root step timed once, then %d full-beam decode steps; RTF extrapolated to %d steps"
                       % (n_steps, steps)}
+
+
+# ------------------------------------------------------------------------------------------------
+# the other BASELINE.json configurations, timed in the same run (reported under `workloads` / `ctc_m5`)
+# ------------------------------------------------------------------------------------------------
+def train_workload_leg(name, dev, steps, warmup, tf_rate):
+    """BASELINE.json config 1 (timit_m1) / the shipped libri yaml (libri_m2s) through the same TrainStep, one GPU:
+    -> resident and end-to-end utterances/s (the definitions of the headline's `value` and `e2e`)."""
+    import torch
+    lib, asr, solver, syn = pkg("_lib"), pkg("asr"), pkg("solver"), pkg("synthetic")
+    w = syn.WORKLOADS[name]
+    torch.manual_seed(0)
+    model = asr.Seq2Seq(torch.zeros(1, 8, w["d_in"]), w["vocab"], w["cfg"]).to(dev).train()
+    opt = solver.make_optimizer(model, w["cfg"]["optimizer"])
+    ts = solver.TrainStep(model, opt, w["cfg"]["optimizer"]["joint_ctc"])
+    host = []
+    for i in range(N_BATCHES):
+        x, y, _ = syn.make_batch(name, 1234 + 1000 * i)
+        host.append((x.pin_memory(), y.pin_memory()))
+    resident = [(x.to(dev), y.to(dev)) for x, y in host]
+
+    def timed(fn, n):
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(n):
+            fn(i)
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1)
+
+    def step_resident(i):
+        x, y = resident[i % N_BATCHES]
+        ts.step(x, y, tf_rate=tf_rate)
+
+    def step_e2e(i):
+        xh, yh = host[i % N_BATCHES]
+        out = ts.step(xh.to(dev, non_blocking=True), yh.to(dev, non_blocking=True), tf_rate=tf_rate)
+        float(out["loss"])
+
+    for i in range(warmup):
+        step_resident(i)
+    l0 = lib.LAUNCHES
+    ms = timed(step_resident, steps)
+    launches = lib.LAUNCHES - l0
+    step_e2e(0)
+    ms_e = timed(step_e2e, steps)
+    B = w["batch"]
+    out = {"value": B * steps / (ms * 1e-3), "unit": "utterances/s", "ms_per_step": ms / steps,
+           "e2e": {"value": B * steps / (ms_e * 1e-3), "unit": "utterances/s", "ms_per_step": ms_e / steps,
+                   "h2d_bytes_per_step": host[0][0].numel() * 4 + host[0][1].numel() * 8},
+           "steps": steps, "warmup": warmup, "tf_rate": tf_rate, "batch": B, "frames": w["t_hi"], "vocab": w["vocab"],
+           "feature_dim": w["d_in"], "encoder": w["cfg"]["encoder"]["enc_type"], "gpu_launches": launches,
+           "params": sum(p.numel() for p in model.parameters())}
+    del ts, opt, model, resident
+    torch.cuda.empty_cache()
+    return out
+
+
+M5_POINTS = [(500, 50), (1000, 150), (2000, 300), (3000, 600)]
+
+
+def ctc_m5_leg(dev, iters=5, warm=3):
+    """BASELINE.json config 5 (pure CTC stress sweep; main.py cannot train pure CTC, reference solver.py:188-190, so
+    kernels only): B=64, V=5000, logits ~N(0,1) [B,T',V] read through (stride_t, stride_b), input lengths
+    ~U[0.6T',T'] (max T'), label lengths ~U[0.5L,L] (max L), 10 % forced adjacent repeats.  One b2asr_ctc_loss_fwd_bwd
+    call (fused log-softmax, 'mean', loss + gradient) per iteration, CUDA events on the launching stream; the 2x
+    (0.6..3.8) GB of logits + gradient exceed the 126 MB L2, so nothing stays cached between iterations.
+    achieved = algorithmic bytes 4*V*(sum_b T'_b + B*T') + 8*sum_b L_b + 16*B  /  time."""
+    import torch
+    lib = pkg("_lib")
+    L = lib.lib()
+    peak, how = measured_peaks()
+    B, V = 64, 5000
+    points = []
+    for T, Lmax in M5_POINTS:
+        g = torch.Generator().manual_seed(T)
+        x = torch.randn(B, T, V, device=dev)
+        il = torch.randint(int(0.6 * T), T + 1, (B,), generator=g); il[0] = T
+        tl = torch.randint(Lmax // 2, Lmax + 1, (B,), generator=g); tl[0] = Lmax
+        y = torch.randint(1, V, (B, Lmax), generator=g)
+        y[:, 1::10] = y[:, 0::10][:, : y[:, 1::10].shape[1]]
+        for b in range(B):
+            y[b, tl[b]:] = 0
+        yd, ild, tld = y.to(dev), il.to(dev), tl.to(dev)
+        nbytes = L.b2asr_ctc_workspace_bytes(T, B, V, Lmax, 1)
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        nll = torch.empty(B, device=dev)
+        loss = torch.empty(1, device=dev)
+        grad = torch.empty_like(x)
+        st = lib.stream_ptr()
+
+        def call():
+            lib.call("b2asr_ctc_loss_fwd_bwd", 3, L.b2asr_ctc_loss_fwd_bwd, x.data_ptr(), x.stride(1), x.stride(0),
+                     yd.data_ptr(), yd.stride(0), ild.data_ptr(), tld.data_ptr(), T, B, V, Lmax, 0, 1, 1, 1.0,
+                     nll.data_ptr(), loss.data_ptr(), grad.data_ptr(), grad.stride(1), grad.stride(0),
+                     ws.data_ptr(), nbytes, st)
+
+        for _ in range(warm):
+            call()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            call()
+        e1.record()
+        torch.cuda.synchronize()
+        us = e0.elapsed_time(e1) / iters * 1e3
+        alg = 4 * V * (int(il.sum()) + B * T) + 8 * int(tl.sum()) + 16 * B
+        points.append({"frames": T, "label_len": Lmax, "us": us, "alg_gb": alg / 1e9, "achieved_gbs": alg / us / 1e3,
+                       "frac": alg / us / 1e3 / peak, "utterances_per_s": B / (us * 1e-6),
+                       "workspace_mb": nbytes / 1e6, "finite": bool(torch.isfinite(loss).all())})
+        del x, grad, ws
+        torch.cuda.empty_cache()
+    return {"batch": B, "vocab": V, "peak_gbs": peak, "peak_source": how, "iters": iters, "warmup": warm,
+            "kernel": "b2asr_ctc_loss_fwd_bwd (from logits, loss + gradient)", "points": points}
+
+
+def stock_torch_gpu_leg(dev, steps=3, warmup=2):
+    """The reference's OWN GPU path (reference src/solver.py:29 runs on CUDA by default): its unmodified
+    Seq2Seq.forward + torch.nn.CTCLoss + backward + Adadelta on cuda:0 through stock PyTorch ops (cuDNN LSTM, cuBLAS,
+    ATen CTC), fp32 with TF32 off, on the SAME full-size batches as the headline.  A reported baseline: the
+    like-for-like speed-up of the hand-written path over stock PyTorch on the same B200."""
+    import torch
+    from oracle import reference_step
+    syn = pkg("synthetic")
+    w = syn.WORKLOADS[WORKLOAD]
+    ref = reference_step.ReferenceStep(w["d_in"], w["vocab"], w["cfg"], dev)
+    batches = [syn.make_batch(WORKLOAD, 1234 + 1000 * i)[:2] for i in range(N_BATCHES)]
+    batches = [(x.to(dev), y.to(dev)) for x, y in batches]
+    for i in range(warmup):
+        ref.step(*batches[i % N_BATCHES], tf_rate=1.0)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        ref.step(*batches[i % N_BATCHES], tf_rate=1.0)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    out = {"value": w["batch"] / (ms * 1e-3), "unit": "utterances/s", "ms_per_step": ms, "steps": steps,
+           "warmup": warmup, "kind": ref.kind, "workload": WORKLOAD,
+           "note": "unmodified reference modules on cuda:0 (stock PyTorch/cuDNN/cuBLAS/ATen ops), inputs resident, "
+                   "fp32 (cudnn.allow_tf32 = False), full 32-utterance batches"}
+    del ref, batches
+    torch.cuda.empty_cache()
+    return out
 
 
 # ------------------------------------------------------------------------------------------------
@@ -445,16 +604,26 @@ def run_native(args):
                     "frac": k["achieved_gbs"] / peak, "traffic": traffic, "peak_source": how,
                     "share_of_step": k["ms_per_step"] / ms_step, "note": note}
 
+    del ts, opt, model, resident
+    torch.cuda.empty_cache()
+    workloads, ctc_m5, stock = None, None, None
+    if world == 1 and WORKLOAD == "libri_m2" and not args.no_extra:
+        k = max(3, min(args.steps, 5))
+        workloads = {"timit_m1": train_workload_leg("timit_m1", dev, k, 3, tf_rate=0.8),
+                     "timit_m1_tf1": train_workload_leg("timit_m1", dev, k, 3, tf_rate=1.0),
+                     "libri_m2s": train_workload_leg("libri_m2s", dev, k, 3, tf_rate=1.0)}
+        ctc_m5 = ctc_m5_leg(dev)
+        stock = stock_torch_gpu_leg(dev)
+
     decode = None
     if not args.no_decode:
-        del ts, opt, model, resident
-        torch.cuda.empty_cache()
         decode = decode_leg(dev, rank, world, args.decode_utts, dist)
 
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        v, ms, cores, sample = cpu_train_step_rate(steps=2, warmup=0, budget_s=20.0)
-        cpu_baseline = {"value": v, "unit": "utterances/s", "cores": cores, "kind": "port", "sample": sample}
+        v, ms, cores, sample, kind = cpu_train_step_rate(steps=3, warmup=1)
+        cpu_baseline = {"value": v, "unit": "utterances/s", "cores": cores, "kind": kind, "sample": sample,
+                        "ms_per_step": ms}
         if decode is not None:
             decode["cpu_baseline"] = cpu_decode_rate()
 
@@ -463,15 +632,12 @@ def run_native(args):
             "metric": METRIC, "value": value, "unit": "utterances/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "batch_per_gpu": B, "global_batch": B * world, "frames": w["t_hi"],
-                       "feature_dim": w["d_in"], "vocab": w["vocab"], "params": n_params,
-                       "parallelism": "dp%d" % world,
-                       "l2": "inputs larger than L2: %d distinct batches rotate and one step touches >1 GB of "
-                             "activations (126 MB L2)" % N_BATCHES},
+            "config": bench_config(WORKLOAD, world, n_params),
             "clocks": clocks, "gpu_launches": launches,
             "e2e": {"value": e2e_value, "unit": "utterances/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h[0], "ms_per_step": ms_e2e / args.steps},
-            "roofline": roofline, "kernels": kernels, "cpu_baseline": cpu_baseline, "decode": decode,
+            "roofline": roofline, "kernels": kernels, "cpu_baseline": cpu_baseline, "stock_torch_gpu": stock,
+            "workloads": workloads, "ctc_m5": ctc_m5, "decode": decode,
         }
         print(json.dumps(out), flush=True)
     if world > 1:
@@ -486,6 +652,8 @@ def main():
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-decode", action="store_true", help="skip the beam-decode RTF leg")
+    ap.add_argument("--no-extra", action="store_true", help="skip the other BASELINE.json configurations "
+                    "(timit_m1, libri_m2s, ctc_m5) and the stock-PyTorch GPU baseline")
     ap.add_argument("--decode-utts", type=int, default=4, help="utterances per GPU in the decode leg")
     ap.add_argument("--workload", default=WORKLOAD, help="train-step workload (synthetic.WORKLOADS); the default is the "
                     "configuration BASELINE.json's metric is quoted on, the others are reported in BASELINE.md only")
