@@ -20,7 +20,7 @@ NVCC_FLAGS = [
     "-Xcompiler", "-fPIC",
     "-DB2ASR_ARCH=100",
     "--expt-relaxed-constexpr",
-]
+] + os.environ.get("B2ASR_NVCC_EXTRA", "").split()      # e.g. -DB2ASR_CTC_TRACE for a one-off instrumented build
 
 
 def _nvcc():
