@@ -24,10 +24,36 @@ _status = {}
 # been launched and then run on a side stream next to it; the gradients are accumulated into .grad there and the
 # main stream joins at the end of the backward pass (autograd engine callback).  B2ASR_ENC_OVERLAP=0: everything in
 # stream order, gradients returned through autograd.
+# Returning None for the weight gradients and adding them to .grad from a side stream is only legitimate where the
+# caller owns .grad and nobody asks autograd for those gradients (torch.autograd.grad, backward(inputs=...), hooks, DDP
+# would all see None): the path is therefore taken only inside `deferred_weight_grads()`, which solver.TrainStep
+# enters around its backward pass; everywhere else the gradients are returned through autograd in stream order.
 OVERLAP = os.environ.get("B2ASR_ENC_OVERLAP", "1") != "0"
 _side = {}
 _deferred = []
 _join_queued = [False]
+_armed = [False]
+
+
+class deferred_weight_grads:
+    """Context manager around a backward pass whose LSTM weight gradients may be accumulated into .grad from the side
+    stream.  If the backward pass raises, the held-back closures are dropped (they would otherwise run during the next
+    backward pass on tensors of a dead graph) and the side stream is joined."""
+
+    def __enter__(self):
+        self._prev = _armed[0]
+        _armed[0] = OVERLAP
+        return self
+
+    def __exit__(self, exc_type, exc, tb):
+        _armed[0] = self._prev
+        if exc_type is not None:
+            del _deferred[:]
+            _join_queued[0] = False
+            if _side and torch.cuda.is_available():
+                device = torch.device("cuda", torch.cuda.current_device())
+                torch.cuda.current_stream(device).wait_stream(_side_stream(device))
+        return False
 
 
 def _side_stream(device):
@@ -72,11 +98,15 @@ def status_word(device):
 
 
 def check_status(device):
-    """Synchronising check used by tests and by the trainer's NaN guard."""
+    """Synchronising check: raises (and re-arms the word) if a recurrence launch gave up waiting for a peer CTA, after
+    which its outputs are undefined.  solver.TrainStep reads the word together with its NaN-skip counter
+    (`TrainStep.check()`, called wherever the trainer already reads a value back), Trainer.valid and beam_decode call
+    it after their forward passes."""
     s = status_word(device)
     if int(s[0].item()) != 0:
         s.zero_()
-        raise _lib.B2asrError("b2asr_lstm_seq: a persistent launch timed out waiting for a peer CTA")
+        raise _lib.B2asrError("b2asr_lstm_seq: a persistent launch timed out waiting for a peer CTA; its outputs "
+                              "are undefined (profiler, sanitizer or a shared GPU can cause this)")
 
 
 def supported(layer, x):
@@ -144,7 +174,7 @@ class LstmSeq(torch.autograd.Function):
         io.d_out = _p(d_out)
         io.d_gates = _p(d_gates)
         before = None
-        if OVERLAP and _deferred:
+        if _armed[0] and _deferred:
             before = torch.cuda.Event()
             before.record()
         _lib.call("b2asr_lstm_seq_bwd", 1, _lib.lib().b2asr_lstm_seq_bwd, ctypes.byref(io), _lib.stream_ptr())
@@ -171,7 +201,7 @@ class LstmSeq(torch.autograd.Function):
             return grads
 
         leaf = all(p is None or (p.is_leaf and p.requires_grad) for p in params)
-        if OVERLAP and leaf and torch.is_grad_enabled() is False:
+        if _armed[0] and leaf and torch.is_grad_enabled() is False:
             ready = torch.cuda.Event()
             ready.record()                                  # d_gates complete (this stream)
             _flush(dev, before)                             # upper layers' weight gradients run next to THIS recurrence

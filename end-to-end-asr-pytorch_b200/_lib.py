@@ -84,6 +84,7 @@ _SIGNATURES = {
     "b2asr_lstm_seq_bwd": (c_i, [ctypes.POINTER(LstmSeq), c_p]),
     "b2asr_param_chunk_size": (c_sz, []),
     "b2asr_adadelta_step": (c_i, [c_p, c_i, c_p, c_p, c_p, c_f, c_f, c_f, c_f, c_p]),
+    "b2asr_adadelta_step_clipped": (c_i, [c_p, c_i, c_p, c_p, c_p, c_f, c_f, c_f, c_f, c_p, c_f, c_f, c_p, c_p]),
     "b2asr_ce_loss_fwd_bwd": (c_i, [c_p, c_i64, c_p, c_i64, c_i, c_i, c_p, c_i64, c_f, c_p, c_p, c_p, c_i64, c_p, c_p]),
     "b2asr_edit_distance": (c_i64, [c_p, c_i64, c_p, c_i64]),
     "b2asr_last_error": (ctypes.c_char_p, []),

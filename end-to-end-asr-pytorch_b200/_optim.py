@@ -103,8 +103,13 @@ class Adadelta(torch.optim.Adadelta):
                     return False
         return True
 
+    def can_clip_on_device(self):
+        """True when step_clipped() may replace clip_grad_norm_ + NaN guard + step() (one parameter group: the clip
+        coefficient is applied inside the group's launch)."""
+        return self._flat_ok() and len(self.param_groups) == 1
+
     @torch.no_grad()
-    def step(self, closure=None):
+    def step(self, closure=None, _clip=None):
         if not self._flat_ok():
             return super().step(closure)
         loss = None
@@ -117,10 +122,23 @@ class Adadelta(torch.optim.Adadelta):
         for group, (table, n, params, _, steps) in zip(self.param_groups, self._tables):
             if group.get("maximize", False):
                 raise _lib.B2asrError("b2asr Adadelta: maximize=True is not supported")
-            _lib.call("b2asr_adadelta_step", 1, _lib.lib().b2asr_adadelta_step, table.data_ptr(), n,
-                      self._grads.flat.data_ptr(), self._sq.data_ptr(), self._acc.data_ptr(),
-                      float(group["lr"]), float(group["rho"]), float(group["eps"]), float(group["weight_decay"]),
-                      _lib.stream_ptr())
+            if _clip is None:
+                _lib.call("b2asr_adadelta_step", 1, _lib.lib().b2asr_adadelta_step, table.data_ptr(), n,
+                          self._grads.flat.data_ptr(), self._sq.data_ptr(), self._acc.data_ptr(),
+                          float(group["lr"]), float(group["rho"]), float(group["eps"]), float(group["weight_decay"]),
+                          _lib.stream_ptr())
+            else:
+                norm, pre_scale, max_norm, skipped = _clip
+                _lib.call("b2asr_adadelta_step_clipped", 1, _lib.lib().b2asr_adadelta_step_clipped, table.data_ptr(), n,
+                          self._grads.flat.data_ptr(), self._sq.data_ptr(), self._acc.data_ptr(),
+                          float(group["lr"]), float(group["rho"]), float(group["eps"]), float(group["weight_decay"]),
+                          norm.data_ptr(), float(pre_scale), float(max_norm), _lib.ptr(skipped), _lib.stream_ptr())
             if steps:
-                torch._foreach_add_(steps, 1)
+                torch._foreach_add_(steps, 1)       # (counts a skipped step too; Adadelta's update does not use it)
         return loss
+
+    def step_clipped(self, grad_norm, pre_scale, max_norm, skipped=None):
+        """clip_grad_norm_(max_norm) + NaN guard + step() of reference solver.py:178-182 in the one launch.
+        grad_norm: 0-dim/1-element fp32 DEVICE tensor, the 2-norm of the flat gradient as it stands; the gradient
+        that is clipped and applied is flat * pre_scale; skipped: int32 device counter of NaN-skipped steps."""
+        return self.step(_clip=(grad_norm, pre_scale, max_norm, skipped))

@@ -65,7 +65,18 @@ __global__ void __launch_bounds__(MAXNT, MINB) attn_step_fwd_kernel(AttnArgs p) 
   B2_TRACE(p, 1);
 
   // ---- stage the small operands: asynchronous 4-byte copies, all in flight at once, one wait ---------------
+  // Weights first: they (like the key / feature tiles requested above) do not depend on the previous kernel of the
+  // decoder loop, so with a programmatic dependent launch all of this overlaps the previous kernel's tail.
   const int KW1 = 2 * p.Kw + 1;
+  if (p.mode == 1) {
+    for (int i = tid; i < C * KW1; i += NT) {            // transposed [tap][channel] so one float4 feeds 4 channels
+      const int c = i / KW1, k = i - c * KW1;
+      cp_async4(wcT + k * CP + c, p.Wc + i);
+    }
+    for (int i = tid; i < KW1 * (CP - C); i += NT) { const int k = i / (CP - C), c = C + i - k * (CP - C); wcT[k * CP + c] = 0.f; }
+  }
+  pdl_wait();                           // decoder state and previous alignment come from the previous kernels
+  pdl_launch();
   for (int i = tid; i < p.dec; i += NT) cp_async4(s_sm + i, p.s + (long long)b * p.s_stride + i);
   if (p.mode == 1) {
     const int npa = nf + 2 * p.Kw;
@@ -75,11 +86,6 @@ __global__ void __launch_bounds__(MAXNT, MINB) attn_step_fwd_kernel(AttnArgs p) 
       if (t >= 0 && t < T && p.prev_att) cp_async4(pa + j, p.prev_att + (long long)b * T + t);
       else pa[j] = (t >= 0 && t < len) ? unif : 0.f;
     }
-    for (int i = tid; i < C * KW1; i += NT) {            // transposed [tap][channel] so one float4 feeds 4 channels
-      const int c = i / KW1, k = i - c * KW1;
-      cp_async4(wcT + k * CP + c, p.Wc + i);
-    }
-    for (int i = tid; i < KW1 * (CP - C); i += NT) { const int k = i / (CP - C), c = C + i - k * (CP - C); wcT[k * CP + c] = 0.f; }
   }
   cp_async_wait_all();
   cluster_or_cta_sync(CS);            // #0: operands staged; every CTA of the cluster is running (DSMEM is legal)
@@ -363,6 +369,12 @@ long long* attn_trace_buffer() {
   return buf;
 }
 
+// B2ASR_PDL=0 launches the decoder loop's kernels without programmatic dependent launch (A/B runs)
+bool pdl_enabled() {
+  static const bool on = [] { const char* e = getenv("B2ASR_PDL"); return !(e && e[0] == '0'); }();
+  return on;
+}
+
 int attn_launch(void (*kern)(AttnArgs), const AttnArgs& a, size_t smem, cudaStream_t st) {
   B2_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   cudaLaunchConfig_t cfg = {};
@@ -370,10 +382,12 @@ int attn_launch(void (*kern)(AttnArgs), const AttnArgs& a, size_t smem, cudaStre
   cfg.blockDim = dim3((unsigned)a.NT);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = (unsigned)a.CS; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr; cfg.numAttrs = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;      // see pdl_wait() in common.cuh
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 2 : 1;
   B2_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, a));
   return B2ASR_OK;
 }

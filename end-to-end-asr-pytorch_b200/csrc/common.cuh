@@ -66,6 +66,22 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
+// Programmatic dependent launch (the decoder loop's kernels are launched with the programmatic-serialisation
+// attribute): a kernel may be SCHEDULED before its predecessor in the stream has finished; everything it does before
+// pdl_wait() must not depend on the predecessor (weights, encoder features, barrier set-up), pdl_wait() returns once
+// the predecessor has completed and its writes are visible.  Both are no-ops in a plain launch.
+// The predecessor's trigger is left IMPLICIT (its CTAs' exit): measured at M2, triggering early
+// (griddepcontrol.launch_dependents right after the wait) made the loop slower (forward 7.4 -> 7.8 ms, backward 14.8
+// -> 15.9 ms per batch: the successor's CTAs land on every SM a CTA of the running kernel leaves and their prologue
+// competes with the stragglers the clusters are waiting for), the implicit trigger faster (6.5 / 13.4 ms).
+// -DB2ASR_PDL_TRIGGER restores the explicit trigger for A/B runs.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+#ifdef B2ASR_PDL_TRIGGER
+__device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+#else
+__device__ __forceinline__ void pdl_launch() {}
+#endif
+
 // thread-block cluster helpers
 __device__ __forceinline__ unsigned cluster_ctarank() {
   unsigned r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r;

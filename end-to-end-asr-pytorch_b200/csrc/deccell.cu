@@ -18,6 +18,8 @@
 
 namespace b2asr {
 
+bool pdl_enabled();                           // attn_fwd.cu
+
 namespace {
 
 constexpr int kRowsPerWarp = 4;
@@ -53,6 +55,8 @@ __global__ void __launch_bounds__(256) dec_step_kernel(const StepArgs a) {
     else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
   }
   cp_async_commit();
+  pdl_wait();                             // the weights above do not depend on the attention kernel before this one
+  pdl_launch();
 
   // the first two k-blocks of this warp's first rows are in flight while the weights land
   float4 x0[kRowsPerWarp], x1[kRowsPerWarp];
@@ -133,6 +137,100 @@ __global__ void __launch_bounds__(256) dec_step_kernel(const StepArgs a) {
 
 size_t step_smem(int K) { return (size_t)kCols * ((K + 127) & ~127) * sizeof(float); }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Backward product of the step: [d_ctx_t | d_h_{t-1}] = d_gates_t [W_ctx | W_hh]  (out[b][j] = sum_k dg[b][k] W[k][j]).
+//   grid = X/8 CTAs, a CTA owns 8 output columns: its 8 columns of the weight (N x 8 floats, 41 KB at M2) are staged in
+//   shared memory column-major BEFORE the dependency wait -- they are constants of the loop, so under a programmatic
+//   dependent launch the staging overlaps the previous kernel's tail -- then warp w takes batch rows 4w..4w+3, the 32
+//   lanes split N, d_gates rows are read straight from L2 two k-blocks ahead, and a 5-round transposing butterfly
+//   leaves ONE output per lane.  Replaces cuBLAS split-K SGEMM + splitKreduce (7.1 + 3.2 us and two launch gaps).
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int kBwdCols = 8;
+
+struct StepBwdArgs {
+  const float* dg; long long dg_ld;          // [B,N] rows: d_gates_t
+  const float* W; long long w_ld;            // [N,X] rows (X contiguous)
+  int B, N, X;
+  float* out; long long out_ld;              // [B,X]
+};
+
+__device__ __forceinline__ float4 ld_dg(const StepBwdArgs& a, int b, int k) {
+  return (b < a.B && k < a.N) ? __ldcg(reinterpret_cast<const float4*>(a.dg + (long long)b * a.dg_ld + k))
+                              : make_float4(0.f, 0.f, 0.f, 0.f);
+}
+
+__global__ void __launch_bounds__(256) dec_step_bwd_kernel(const StepBwdArgs a) {
+  extern __shared__ __align__(16) float W_s[];             // [8][Np + 4]: the +4 spreads a k-row's 8 columns over banks
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const int N = a.N, Np = (N + 127) & ~127, ld = Np + 4;
+  const int j0 = blockIdx.x * kBwdCols;
+  for (int idx = tid; idx < Np * kBwdCols; idx += 256) {
+    const int k = idx >> 3, c = idx & 7;
+    float* dst = W_s + c * ld + k;
+    if (k < N && j0 + c < a.X) cp_async4(dst, a.W + (long long)k * a.w_ld + j0 + c);
+    else *dst = 0.f;
+  }
+  cp_async_commit();
+  pdl_wait();                             // d_gates comes from the cell-backward kernel before this one
+  pdl_launch();
+  float4 x0[kRowsPerWarp], x1[kRowsPerWarp];
+#pragma unroll
+  for (int i = 0; i < kRowsPerWarp; ++i) {
+    x0[i] = ld_dg(a, kRowsPerWarp * w + i, 4 * lane);
+    x1[i] = ld_dg(a, kRowsPerWarp * w + i, 128 + 4 * lane);
+  }
+  cp_async_wait_all();
+  __syncthreads();
+  for (int b0 = kRowsPerWarp * w; b0 < a.B; b0 += kRowsPerWarp * 8) {
+    float acc[kRowsPerWarp][kBwdCols];
+#pragma unroll
+    for (int i = 0; i < kRowsPerWarp; ++i)
+#pragma unroll
+      for (int c = 0; c < kBwdCols; ++c) acc[i][c] = 0.f;
+    if (b0 != kRowsPerWarp * w) {
+#pragma unroll
+      for (int i = 0; i < kRowsPerWarp; ++i) {
+        x0[i] = ld_dg(a, b0 + i, 4 * lane);
+        x1[i] = ld_dg(a, b0 + i, 128 + 4 * lane);
+      }
+    }
+    for (int kb = 0; kb < Np; kb += 128) {
+      float4 x2[kRowsPerWarp];
+#pragma unroll
+      for (int i = 0; i < kRowsPerWarp; ++i) x2[i] = ld_dg(a, b0 + i, kb + 256 + 4 * lane);
+      const float* wp = W_s + kb + 4 * lane;
+#pragma unroll
+      for (int c = 0; c < kBwdCols; ++c) {
+        const float4 wv = *reinterpret_cast<const float4*>(wp + c * ld);
+#pragma unroll
+        for (int i = 0; i < kRowsPerWarp; ++i) {
+          acc[i][c] = fmaf(x0[i].x, wv.x, acc[i][c]);
+          acc[i][c] = fmaf(x0[i].y, wv.y, acc[i][c]);
+          acc[i][c] = fmaf(x0[i].z, wv.z, acc[i][c]);
+          acc[i][c] = fmaf(x0[i].w, wv.w, acc[i][c]);
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < kRowsPerWarp; ++i) { x0[i] = x1[i]; x1[i] = x2[i]; }
+    }
+    float* v = &acc[0][0];                                  // v[i*8 + c]; after the butterfly lane L holds element L
+#pragma unroll
+    for (int m = 16, n = 16; m >= 1; m >>= 1, n >>= 1) {
+      const bool hi = lane & m;
+#pragma unroll
+      for (int q = 0; q < n; ++q) {
+        const float send = hi ? v[q] : v[q + n];
+        const float keep = hi ? v[q + n] : v[q];
+        v[q] = keep + __shfl_xor_sync(kFull, send, m);
+      }
+    }
+    const int b = b0 + (lane >> 3), j = j0 + (lane & 7);
+    if (b < a.B && j < a.X) a.out[(long long)b * a.out_ld + j] = v[0];
+  }
+}
+
+size_t step_bwd_smem(int N) { return (size_t)kBwdCols * (((N + 127) & ~127) + 4) * sizeof(float); }
+
 }  // namespace
 
 // true when the fused kernel takes these shapes (whole units per CTA, 16-byte aligned rows)
@@ -154,7 +252,39 @@ int dec_step_fwd(const float* x, long long x_ld, const float* w_cat, int B, int 
     B2_CUDA_TRY(cudaFuncSetAttribute((const void*)dec_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = smem;
   }
-  dec_step_kernel<<<H / 4, 256, smem, st>>>(a);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)(H / 4)); cfg.blockDim = dim3(256); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  B2_CUDA_TRY(cudaLaunchKernelEx(&cfg, dec_step_kernel, a));
+  return B2ASR_OK;
+}
+
+bool dec_step_bwd_supported(int N, int X, long long dg_ld, long long w_ld) {
+  return N % 4 == 0 && dg_ld % 4 == 0 && X > 0 && w_ld >= X && step_bwd_smem(N) <= 200 * 1024;
+}
+
+// out[B,X] = dg[B,N] W[N,X]
+int dec_step_bwd(const float* dg, long long dg_ld, const float* W, long long w_ld, int B, int N, int X, float* out,
+                 long long out_ld, cudaStream_t st) {
+  StepBwdArgs a = {};
+  a.dg = dg; a.dg_ld = dg_ld; a.W = W; a.w_ld = w_ld; a.B = B; a.N = N; a.X = X; a.out = out; a.out_ld = out_ld;
+  const size_t smem = step_bwd_smem(N);
+  static size_t configured = 0;
+  if (smem > configured) {
+    B2_CUDA_TRY(cudaFuncSetAttribute((const void*)dec_step_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = smem;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)((X + kBwdCols - 1) / kBwdCols)); cfg.blockDim = dim3(256); cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  B2_CUDA_TRY(cudaLaunchKernelEx(&cfg, dec_step_bwd_kernel, a));
   return B2ASR_OK;
 }
 

@@ -32,6 +32,9 @@ void lstm_cell_bwd_launch(const float* d_h, long long dh_stride, const float* d_
 extern thread_local long long g_attn_row_stride;   // attn.cuh: row stride of ctx / d_ctx for the next attention launch
 // deccell.cu: the forward step's GEMM + cell as one hand-written launch
 bool dec_step_supported(int H, int K, long long x_ld, long long g_ld);
+bool dec_step_bwd_supported(int N, int X, long long dg_ld, long long w_ld);
+int dec_step_bwd(const float* dg, long long dg_ld, const float* W, long long w_ld, int B, int N, int X, float* out,
+                 long long out_ld, cudaStream_t st);
 int dec_step_fwd(const float* x, long long x_ld, const float* w_cat, int B, int K, int H, float* gates, long long g_ld,
                  const float* b_ih, const float* b_hh, const float* c_prev, float* c, float* h, long long h_ld, float* h2,
                  long long h2_ld, cudaStream_t st);
@@ -176,8 +179,11 @@ extern "C" int b2asr_decoder_loop_bwd(const b2asr_decloop* a, void* stream) {
                          (cat && !last) ? X : 0);
     float* dctx_t = cat ? a->d_xcat + (int64_t)t * B * X : a->d_ctx + (int64_t)t * B * D;
     if (cat) {
-      // stays on cuBLAS: a hand-written kernel over the transposed weights did not beat its split-K (deccell.cu)
-      B2_BLAS_TRY(gemm_gw(hd, B, 4 * H, X, dg_t, gl, a->w_cat, X, dctx_t, X));
+      if (fused_step_enabled() && dec_step_bwd_supported(4 * H, X, gl, X)) {
+        if (int rc = dec_step_bwd(dg_t, gl, a->w_cat, X, B, 4 * H, X, dctx_t, X, st)) return rc;
+      } else {
+        B2_BLAS_TRY(gemm_gw(hd, B, 4 * H, X, dg_t, gl, a->w_cat, X, dctx_t, X));
+      }
       g_attn_row_stride = X;
     } else {
       B2_BLAS_TRY(gemm_gw(hd, B, 4 * H, D, dg_t, gl, a->w_ctx, a->w_ctx_ld, dctx_t, D));

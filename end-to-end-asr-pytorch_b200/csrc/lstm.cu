@@ -12,6 +12,8 @@
 
 namespace b2asr {
 
+bool pdl_enabled();                           // attn_fwd.cu
+
 __device__ __forceinline__ float sigmoid_acc(float x) { return __fdividef(1.f, 1.f + ex2(-x * kLog2e)); }
 
 __global__ void __launch_bounds__(256) lstm_cell_fwd_kernel(float* __restrict__ gates, long long g_stride,
@@ -50,8 +52,10 @@ __global__ void __launch_bounds__(256) lstm_cell_bwd_kernel(const float* __restr
   if (idx >= B * H) return;
   const int b = idx / H, u = idx - b * H;
   const float* a = act + (long long)b * act_stride;
-  const float i = a[u], f = a[H + u], g = a[2 * H + u], o = a[3 * H + u];
+  const float i = a[u], f = a[H + u], g = a[2 * H + u], o = a[3 * H + u];      // forward products: no dependence
   const float tc = tanh_acc(c[idx]);
+  pdl_wait();                                                                    // on the previous backward kernels
+  pdl_launch();
   float dh = d_h ? d_h[(long long)b * dh_stride + u] : 0.f;
   if (d_h2) dh += d_h2[(long long)b * dh2_stride + u];
   if (d_h3) dh += d_h3[idx];
@@ -77,8 +81,14 @@ void lstm_cell_bwd_launch(const float* d_h, long long dh_stride, const float* d_
                           const float* act, long long act_stride, const float* c_prev, const float* c, float* d_gates,
                           long long dg_stride, float* d_c_prev, int B, int H, cudaStream_t st, long long dh2_stride) {
   const int n = B * H;
-  lstm_cell_bwd_kernel<<<(n + 255) / 256, 256, 0, st>>>(d_h, dh_stride, d_h2, d_h3, d_c, act, act_stride, c_prev, c,
-                                                        d_gates, dg_stride, d_c_prev, B, H, dh2_stride ? dh2_stride : H);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)((n + 255) / 256)); cfg.blockDim = dim3(256); cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  cudaLaunchKernelEx(&cfg, lstm_cell_bwd_kernel, d_h, dh_stride, d_h2, d_h3, d_c, act, act_stride, c_prev, c, d_gates,
+                     dg_stride, d_c_prev, B, H, dh2_stride ? dh2_stride : (long long)H);
 }
 
 }  // namespace b2asr

@@ -76,11 +76,18 @@ class FlatGradients:
     def zero(self):
         self.flat.zero_()
 
-    def allreduce_mean(self, group=None):
+    def allreduce_sum(self, group=None):
+        """-> world size; the flat buffer then holds the SUM over ranks (the 1/world goes into the clip coefficient)."""
         import torch.distributed as dist
         if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
             dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group)
-            self.flat.mul_(1.0 / dist.get_world_size(group))
+            return dist.get_world_size(group)
+        return 1
+
+    def allreduce_mean(self, group=None):
+        world = self.allreduce_sum(group)
+        if world > 1:
+            self.flat.mul_(1.0 / world)
 
     def clip_(self, max_norm):
         """clip_grad_norm_ (solver.py:178) on the flat buffer: same 2-norm, one reduction."""
@@ -90,20 +97,50 @@ class FlatGradients:
         return norm
 
 
+class _Stepped:
+    """Truth value of "the optimizer stepped" (reference solver.py:179: `math.isnan(grad_norm)` -> no step), read from
+    the device only when somebody asks."""
+
+    def __init__(self, owner, before):
+        self._owner, self._before, self._value = owner, before, None
+
+    def __bool__(self):
+        if self._value is None:
+            self._value = self._owner.check() == self._before
+        return self._value
+
+
 class TrainStep:
     """One hybrid CTC/attention training step (solver.py:132-182) bound to a model and an optimizer.
 
-    step(x, y, tf_rate) -> dict(loss, att_loss, ctc_loss, grad_norm) of 0-dim DEVICE tensors, plus
-    'stepped' (bool, host): the NaN guard of solver.py:179-182 needs the norm on the host, which is the
-    step's one unavoidable D2H read besides the B encoder lengths."""
+    step(x, y, tf_rate) -> dict(loss, att_loss, ctc_loss, grad_norm) of 0-dim DEVICE tensors plus 'stepped'.
+    With the one-launch Adadelta the clip and the NaN guard of solver.py:178-182 run inside the optimizer kernel
+    (`b2asr_adadelta_step_clipped`), so the step reads nothing back: 'stepped' is an object whose truth value fetches
+    the device-side skip counter on demand, and `check()` -- called by Trainer.exec where it reads the loss back
+    anyway -- also raises if a Listener recurrence launch timed out.  Other optimizers keep the host-side guard."""
 
     def __init__(self, model, optimizer, ctc_weight, grad_clip=GRAD_CLIP, group=None):
         self.model, self.opt, self.w, self.clip, self.group = model, optimizer, ctc_weight, grad_clip, group
         self.grads = FlatGradients(model.parameters())
         if hasattr(optimizer, 'bind') and self.grads.flat.is_cuda:
             optimizer.bind(self.grads)                              # one-launch optimizer step (_optim.py)
+        self.skipped = torch.zeros(1, dtype=torch.int32, device=self.grads.flat.device)
+        self._skipped_seen = 0
+
+    def check(self):
+        """One small device read: -> number of NaN-skipped steps so far; raises if an encoder kernel timed out."""
+        from . import _enc
+        dev = self.grads.flat.device
+        word = torch.cat([self.skipped, _enc.status_word(dev)[:1]]).tolist()
+        if word[1] != 0:
+            _enc.status_word(dev).zero_()
+            raise RuntimeError("b2asr_lstm_seq: a persistent launch timed out waiting for a peer CTA; the step's "
+                               "outputs are undefined")
+        self._skipped_seen = int(word[0])
+        return self._skipped_seen
 
     def step(self, x, y, tf_rate=1.0):
+        from . import _enc
         if not x.is_cuda:
             raise RuntimeError('train step runs on the sm_100a kernels only (no CPU path)')
         state_len = infer_lengths(x)
@@ -113,12 +150,20 @@ class TrainStep:
         ctc_pred, enc_len, att_pred, _ = self.model(x, ans_len, tf_rate=tf_rate, teacher=y, state_len=state_len)
         aux = {}
         loss, att_loss, ctc_loss = hybrid_loss(ctc_pred, att_pred, y, enc_len, self.w, ans_len, aux)
-        loss.backward()
-        self.grads.allreduce_mean(self.group)
-        grad_norm = self.grads.clip_(self.clip)
-        stepped = not math.isnan(float(grad_norm))                  # solver.py:179
-        if stepped:
-            self.opt.step()
+        with _enc.deferred_weight_grads():
+            loss.backward()
+        if getattr(self.opt, 'can_clip_on_device', None) and self.opt.can_clip_on_device():
+            world = self.grads.allreduce_sum(self.group)
+            raw_norm = torch.linalg.vector_norm(self.grads.flat).reshape(1)
+            self.opt.step_clipped(raw_norm, 1.0 / world, float(self.clip), self.skipped)
+            grad_norm = raw_norm[0] / world if world > 1 else raw_norm[0]
+            stepped = _Stepped(self, self._skipped_seen)
+        else:
+            self.grads.allreduce_mean(self.group)
+            grad_norm = self.grads.clip_(self.clip)
+            stepped = not math.isnan(float(grad_norm))              # solver.py:179
+            if stepped:
+                self.opt.step()
         return dict(loss=loss.detach(), att_loss=att_loss if not torch.is_tensor(att_loss) else att_loss.detach(),
                     ctc_loss=ctc_loss if not torch.is_tensor(ctc_loss) else ctc_loss.detach(),
                     grad_norm=grad_norm, stepped=stepped, att_pred=att_pred, ctc_pred=ctc_pred, enc_len=enc_len,

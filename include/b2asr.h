@@ -375,6 +375,17 @@ size_t b2asr_param_chunk_size(void);
 int b2asr_adadelta_step(const b2asr_param_chunk* chunks, int n_chunks, const float* grad, float* square_avg,
                         float* acc_delta, float lr, float rho, float eps, float weight_decay, void* stream);
 
+/* The same step with the clip and the NaN guard of reference src/solver.py:178-182 on the device, so that the train
+ * step needs no host read of the gradient norm:
+ *   grad_norm  [1] DEVICE: 2-norm of `grad` as it stands (after a data-parallel all-reduce: of the SUM over ranks)
+ *   pre_scale  1 / world size (1 on one GPU): the gradient that is clipped and applied is grad * pre_scale
+ *   NaN norm   -> nothing is updated and *skipped (DEVICE int, may be NULL) is incremented  (solver.py:179-180)
+ *   otherwise  -> grad <- grad * pre_scale * min(max_norm / (norm * pre_scale + 1e-6), 1)   (torch clip_grad_norm_,
+ *                 solver.py:178; written back, as the reference leaves the clipped gradient in .grad), then the update. */
+int b2asr_adadelta_step_clipped(const b2asr_param_chunk* chunks, int n_chunks, float* grad, float* square_avg,
+                                float* acc_delta, float lr, float rho, float eps, float weight_decay,
+                                const float* grad_norm, float pre_scale, float max_norm, int* skipped, void* stream);
+
 /* Debug aid, not part of the drop-in path: with B2ASR_ATT_TRACE=1 in the environment CTA 0 of every attention
  * launch stamps clock64() at its phase boundaries (forward: slots 0-9, backward: 16-27); this copies the first n
  * slots of the last launch to the host (synchronous). */

@@ -139,25 +139,46 @@ def test_weight_gradients_on_side_stream_match_stream_order():
     l1 = torch.nn.LSTM(2 * H, H, bidirectional=True, batch_first=True).to(dev)
     w = torch.randn(B, T, 2 * H, device=dev)
 
+    import contextlib
+
     def run(overlap):
-        prev = enc.OVERLAP
-        enc.OVERLAP = overlap
-        try:
-            for p in list(l0.parameters()) + list(l1.parameters()):
-                p.grad = None
-            xin = x.clone().requires_grad_(True)
-            for _ in range(2):                                   # second pass accumulates into existing .grad
-                y = enc.lstm_layer(l1, torch.tanh(enc.lstm_layer(l0, xin, lens)), lens)
+        for p in list(l0.parameters()) + list(l1.parameters()):
+            p.grad = None
+        xin = x.clone().requires_grad_(True)
+        for _ in range(2):                                   # second pass accumulates into existing .grad
+            y = enc.lstm_layer(l1, torch.tanh(enc.lstm_layer(l0, xin, lens)), lens)
+            # the side-stream path is taken only inside deferred_weight_grads() (solver.TrainStep enters it)
+            with (enc.deferred_weight_grads() if overlap else contextlib.nullcontext()):
                 (y * w).sum().backward()
-            torch.cuda.synchronize()
-            enc.check_status(dev)
-            return [p.grad.clone() for p in list(l0.parameters()) + list(l1.parameters())] + [xin.grad.clone()]
-        finally:
-            enc.OVERLAP = prev
+        torch.cuda.synchronize()
+        enc.check_status(dev)
+        return [p.grad.clone() for p in list(l0.parameters()) + list(l1.parameters())] + [xin.grad.clone()]
 
     a, b = run(True), run(False)
     for ga, gb in zip(a, b):
         _close(ga, gb, "overlap vs stream order", rtol=1e-6)
+
+
+def test_weight_gradients_reach_autograd_outside_the_train_step():
+    """torch.autograd.grad / backward(inputs=...) must receive the LSTM weight gradients (the side-stream
+    accumulation into .grad is armed by solver.TrainStep only), and a failed backward inside the armed region must
+    not leave closures behind for the next one."""
+    enc = importlib.import_module(PKG + "._enc")
+    dev = torch.device("cuda:0")
+    torch.manual_seed(4)
+    B, T, n_in, H = 6, 20, 16, 320
+    lens = _lens(B, T, seed=2)
+    layer = torch.nn.LSTM(n_in, H, bidirectional=True, batch_first=True).to(dev)
+    x = torch.randn(B, T, n_in, device=dev)
+    out = enc.lstm_layer(layer, x, lens)
+    grads = torch.autograd.grad(out.square().sum(), list(layer.parameters()))
+    assert all(g is not None and torch.isfinite(g).all() and float(g.abs().sum()) > 0 for g in grads)
+    assert all(p.grad is None for p in layer.parameters())          # nothing was accumulated behind autograd's back
+    with pytest.raises(RuntimeError):
+        with enc.deferred_weight_grads():
+            enc._deferred.append(lambda side: None)
+            raise RuntimeError("backward failed")
+    assert not enc._deferred and not enc._armed[0]
 
 
 def test_recurrence_kernels_are_bit_reproducible():

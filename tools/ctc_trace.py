@@ -8,7 +8,7 @@ lib = importlib.import_module("end-to-end-asr-pytorch_b200._lib")
 L = lib.lib()
 dev = torch.device("cuda:0")
 B, V = 64, 5000
-for T, Lmax in [(1000, 150), (3000, 600)]:
+for T, Lmax in [(1000, 150), (2000, 300), (3000, 600)]:
     g = torch.Generator().manual_seed(T)
     x = torch.randn(B, T, V, device=dev)
     il = torch.randint(int(0.6 * T), T + 1, (B,), generator=g); il[0] = T
@@ -17,11 +17,11 @@ for T, Lmax in [(1000, 150), (3000, 600)]:
     for b in range(B):
         y[b, tl[b]:] = 0
     yd, ild, tld = y.to(dev), il.to(dev), tl.to(dev)
-    os.environ["B2ASR_CTC_OVERLAP"] = "1"
+    os.environ["B2ASR_CTC_OVERLAP"] = "3"
     n = L.b2asr_ctc_workspace_bytes(T, B, V, Lmax, 1)
     ws = torch.empty(n, dtype=torch.uint8, device=dev)
     nll = torch.empty(B, device=dev); loss = torch.empty(1, device=dev); grad = torch.empty_like(x)
-    for mode in ("1", "1", "0"):
+    for mode in ("2", "2", "0"):
         os.environ["B2ASR_CTC_OVERLAP"] = mode
         rc = L.b2asr_ctc_loss_fwd_bwd(x.data_ptr(), x.stride(1), x.stride(0), yd.data_ptr(), yd.stride(0), ild.data_ptr(), tld.data_ptr(),
                                       T, B, V, Lmax, 0, 1, 1, 1.0, nll.data_ptr(), loss.data_ptr(), grad.data_ptr(), grad.stride(1), grad.stride(0),
