@@ -75,9 +75,8 @@ __global__ void __launch_bounds__(MAXNT, MINB) attn_step_fwd_kernel(AttnArgs p) 
     }
     for (int i = tid; i < KW1 * (CP - C); i += NT) { const int k = i / (CP - C), c = C + i - k * (CP - C); wcT[k * CP + c] = 0.f; }
   }
-  pdl_wait();                           // decoder state and previous alignment come from the previous kernels
-  pdl_launch();
-  for (int i = tid; i < p.dec; i += NT) cp_async4(s_sm + i, p.s + (long long)b * p.s_stride + i);
+  // The previous alignment was written by the PREVIOUS attention kernel, which had completed before the decoder
+  // cell between the two (the only kernel that may still be running) could start: safe before the wait.
   if (p.mode == 1) {
     const int npa = nf + 2 * p.Kw;
     const float unif = len > 0 ? 1.f / (float)len : 0.f;
@@ -86,7 +85,25 @@ __global__ void __launch_bounds__(MAXNT, MINB) attn_step_fwd_kernel(AttnArgs p) 
       if (t >= 0 && t < T && p.prev_att) cp_async4(pa + j, p.prev_att + (long long)b * T + t);
       else pa[j] = (t >= 0 && t < len) ? unif : 0.f;
     }
+    cp_async_wait_all();
+    __syncthreads();
+    // ---- location features f[t][c] = sum_k Wc[c][k] * prev_att[t+k-Kw] for my frames ---------------
+    const float4* w4 = reinterpret_cast<const float4*>(wcT);
+    for (int item = tid; item < nf * CQ; item += NT) {
+      const int cg = item / nf, fl = item - cg * nf;
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+      for (int k = 0; k < KW1; ++k) {
+        const float pv = pa[fl + k];
+        const float4 w = w4[k * CQ + cg];
+        acc.x = fmaf(pv, w.x, acc.x); acc.y = fmaf(pv, w.y, acc.y); acc.z = fmaf(pv, w.z, acc.z); acc.w = fmaf(pv, w.w, acc.w);
+      }
+      reinterpret_cast<float4*>(fsm)[fl * CQ + cg] = acc;
+    }
   }
+  pdl_wait();                           // the decoder state comes from the cell kernel before this one
+  pdl_launch();
+  for (int i = tid; i < p.dec; i += NT) cp_async4(s_sm + i, p.s + (long long)b * p.s_stride + i);
   cp_async_wait_all();
   cluster_or_cta_sync(CS);            // #0: operands staged; every CTA of the cluster is running (DSMEM is legal)
   B2_TRACE(p, 2);
@@ -147,21 +164,6 @@ __global__ void __launch_bounds__(MAXNT, MINB) attn_step_fwd_kernel(AttnArgs p) 
     for (int a = tid; a < A; a += NT) q_sm[a] = s_sm[a];
   }
 
-  // ---- location features f[t][c] = sum_k Wc[c][k] * prev_att[t+k-Kw] for my frames ---------------
-  if (p.mode == 1) {
-    const float4* w4 = reinterpret_cast<const float4*>(wcT);
-    for (int item = tid; item < nf * CQ; item += NT) {
-      const int cg = item / nf, fl = item - cg * nf;
-      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 4
-      for (int k = 0; k < KW1; ++k) {
-        const float pv = pa[fl + k];
-        const float4 w = w4[k * CQ + cg];
-        acc.x = fmaf(pv, w.x, acc.x); acc.y = fmaf(pv, w.y, acc.y); acc.z = fmaf(pv, w.z, acc.z); acc.w = fmaf(pv, w.w, acc.w);
-      }
-      reinterpret_cast<float4*>(fsm)[fl * CQ + cg] = acc;
-    }
-  }
   B2_TRACE(p, 3);
   cluster_or_cta_sync(CS);            // #1: q and f visible
   B2_TRACE(p, 4);

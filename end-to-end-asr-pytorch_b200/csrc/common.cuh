@@ -81,6 +81,16 @@ __device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.laun
 #else
 __device__ __forceinline__ void pdl_launch() {}
 #endif
+// The forward's decoder-cell kernel (80 CTAs between two attention steps) does trigger, at its very start: the next
+// attention kernel's CTAs are then scheduled next to it and run their prologue (weights, key / feature tiles, the
+// location conv over the previous alignment -- all complete before the cell kernel could start) while the cell
+// computes (M2 forward 6.53 -> 6.28 ms per batch).  The attention kernels themselves never trigger early, and neither
+// do the backward's small kernels (measured: 13.4 -> 19.6 ms).
+#ifdef B2ASR_PDL_NO_SMALL_TRIGGER
+__device__ __forceinline__ void pdl_trigger_small() {}
+#else
+__device__ __forceinline__ void pdl_trigger_small() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+#endif
 
 // thread-block cluster helpers
 __device__ __forceinline__ unsigned cluster_ctarank() {
