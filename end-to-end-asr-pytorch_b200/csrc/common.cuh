@@ -53,6 +53,21 @@ __device__ __forceinline__ float warp_sum(float v) {
   return v;
 }
 
+// packed fp32: two FMAs per issue slot (SASS FFMA2)
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 ffma2(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d;
+}
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+  f32x2 d; asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "f"(lo), "f"(hi)); return d;
+}
+__device__ __forceinline__ float sum2(f32x2 v) {
+  float lo, hi; asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); return lo + hi;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+
 // cp.async (LDGSTS) 16-byte copy global -> shared, generic proxy.
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
   unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);

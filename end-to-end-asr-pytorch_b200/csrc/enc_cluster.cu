@@ -61,16 +61,7 @@ __device__ __forceinline__ void named_sync(int id, int n) { asm volatile("bar.sy
 constexpr int kIssueWarp = 32;                // backward: one extra warp per CTA forwards the first part of the partials
 
 // packed fp32: two FMAs per issue slot (SASS FFMA2); the loops below are issue-bound with 2.5 warps per scheduler
-typedef unsigned long long f32x2;
-__device__ __forceinline__ f32x2 ffma2(f32x2 a, f32x2 b, f32x2 c) {
-  f32x2 d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d;
-}
-__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
-  f32x2 d; asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "f"(lo), "f"(hi)); return d;
-}
-__device__ __forceinline__ float sum2(f32x2 v) {
-  float lo, hi; asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); return lo + hi;
-}
+// (f32x2 / ffma2 / pack2 / sum2: common.cuh)
 
 // floats between two ranks' chunks in the gathered h buffer: >= BS*UC and == UC (mod 32), so the 8 float4 a
 // quarter warp reads (32 consecutive k, up to three ranks) fall into 8 different bank groups
