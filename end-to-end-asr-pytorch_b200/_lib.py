@@ -37,7 +37,38 @@ class BeamIO(ctypes.Structure):
         ("cand", c_p), ("psi", c_p), ("r_all", c_p), ("topv", c_p), ("topi", c_p), ("step", c_p), ("ticket", c_p),
         ("hist_parent", c_p), ("hist_tok", c_p), ("hist_score", c_p),
         ("fin_count", c_p), ("fin_step", c_p), ("fin_row", c_p), ("fin_score", c_p), ("fin_sum", c_p),
+        ("att_lse", c_p), ("lm_lse", c_p),
     ]
+
+
+class CellStep(ctypes.Structure):
+    """Mirror of `b2asr_cell_step` (include/b2asr.h)."""
+    _fields_ = ([(n, ctypes.c_int32) for n in ("B", "H", "K1", "K2")] +
+                [("x1", c_p), ("x1_ld", c_i64), ("x2", c_p), ("x2_ld", c_i64), ("map", c_p), ("W", c_p), ("w_ld", c_i64),
+                 ("base", c_p), ("base_ld", c_i64), ("base_row", c_p), ("b1", c_p), ("b2", c_p),
+                 ("c_prev", c_p), ("c", c_p), ("c_ld", c_i64), ("h", c_p), ("h_ld", c_i64),
+                 ("after_linear", ctypes.c_int32), ("pad_", ctypes.c_int32)])
+
+
+class LinearLse(ctypes.Structure):
+    """Mirror of `b2asr_linear_lse` (include/b2asr.h)."""
+    _fields_ = ([(n, ctypes.c_int32) for n in ("B", "K", "V", "pad_")] +
+                [("x", c_p), ("x_ld", c_i64), ("W", c_p), ("w_ld", c_i64), ("bias", c_p), ("logits", c_p),
+                 ("out_ld", c_i64), ("lse", c_p), ("part", c_p), ("ticket", c_p)])
+
+
+class AttnCall(ctypes.Structure):
+    """Mirror of `b2asr_attn_call` (include/b2asr.h)."""
+    _fields_ = ([(n, ctypes.c_int32) for n in ("mode", "C", "Kw", "B", "T", "D", "A", "dec", "cluster")] +
+                [("scale", c_f), ("s", c_p), ("s_stride", c_i64), ("Wphi", c_p), ("keys", c_p), ("k_bstride", c_i64),
+                 ("h", c_p), ("h_bstride", c_i64), ("lens", c_p), ("prev_att", c_p), ("row_map", c_p),
+                 ("Wc", c_p), ("Wl", c_p), ("wg", c_p), ("bg", c_p), ("att", c_p), ("ctx", c_p), ("ctx_stride", c_i64)])
+
+
+class DecodeProg(ctypes.Structure):
+    """Mirror of `b2asr_decode_prog` (include/b2asr.h)."""
+    _fields_ = [("attn", AttnCall), ("n_cells", ctypes.c_int32), ("n_linear", ctypes.c_int32),
+                ("cells", CellStep * 8), ("linear", LinearLse * 2), ("beam", ctypes.POINTER(BeamIO))]
 
 
 class DecLoop(ctypes.Structure):
@@ -71,6 +102,16 @@ _SIGNATURES = {
     "b2asr_ctc_prefix_score": (c_i, [c_p, c_i, c_i, c_i, c_i, c_p, c_p, c_i, c_p, c_p, c_p]),
     "b2asr_beam_io_size": (c_sz, []),
     "b2asr_beam_step": (c_i, [ctypes.POINTER(BeamIO), c_p]),
+    "b2asr_attn_step_fwd_rows": (c_i, [c_i, c_p, c_i64, c_p, c_p, c_i64, c_p, c_i64, c_p, c_p, c_p,
+                                       c_p, c_i, c_i, c_p, c_p, c_p, c_f, c_p, c_p, c_i64, c_p,
+                                       c_i, c_i, c_i, c_i, c_i, c_i, c_p]),
+    "b2asr_cell_step_size": (c_sz, []),
+    "b2asr_linear_lse_size": (c_sz, []),
+    "b2asr_decode_prog_size": (c_sz, []),
+    "b2asr_linear_lse_ctas": (c_i, [c_i]),
+    "b2asr_cell_step_fwd": (c_i, [ctypes.POINTER(CellStep), c_p]),
+    "b2asr_linear_lse_fwd": (c_i, [ctypes.POINTER(LinearLse), c_p]),
+    "b2asr_decode_run": (c_i, [ctypes.POINTER(DecodeProg), c_i, c_i, c_p]),
     "b2asr_debug_attn_trace": (c_i, [ctypes.POINTER(ctypes.c_longlong), c_i]),
     "b2asr_debug_beam_trace": (c_i, [ctypes.POINTER(ctypes.c_longlong), c_i]),
     "b2asr_lstm_cell_fwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_p]),
@@ -143,6 +184,11 @@ def lib():
         if L.b2asr_lstm_seq_size() != ctypes.sizeof(LstmSeq):
             raise B2asrError("b2asr_lstm_seq layout mismatch: library %d bytes, binding %d bytes"
                              % (L.b2asr_lstm_seq_size(), ctypes.sizeof(LstmSeq)))
+        for cname, cls in (("b2asr_cell_step_size", CellStep), ("b2asr_linear_lse_size", LinearLse),
+                           ("b2asr_decode_prog_size", DecodeProg)):
+            if getattr(L, cname)() != ctypes.sizeof(cls):
+                raise B2asrError("%s layout mismatch: library %d bytes, binding %d bytes"
+                                 % (cname[:-5], getattr(L, cname)(), ctypes.sizeof(cls)))
         if L.b2asr_param_chunk_size() != ctypes.sizeof(ParamChunk):
             raise B2asrError("b2asr_param_chunk layout mismatch: library %d bytes, binding %d bytes"
                              % (L.b2asr_param_chunk_size(), ctypes.sizeof(ParamChunk)))

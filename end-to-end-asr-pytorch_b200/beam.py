@@ -30,6 +30,47 @@ from .postprocess import Hypothesis
 CTC_BEAM_RATIO = 1.5   # asr.py:15
 
 
+class _Scalars:
+    """List-like view of a 1-D CPU tensor whose items are 0-dim tensors, as the reference's Hypothesis keeps its
+    tokens and scores (postprocess.py:49-50, 82-85): items are made when asked for (a beam of 20 x 160 tokens as 6 400
+    eager 0-dim tensors cost 8-20 ms per utterance), slices and concatenations give plain lists, append() works."""
+
+    def __init__(self, t):
+        self._t = t
+        self._extra = []
+
+    def __len__(self):
+        return int(self._t.shape[0]) + len(self._extra)
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            return list(self)[i]
+        n = int(self._t.shape[0])
+        if i < 0:
+            i += n + len(self._extra)
+        if i < 0 or i >= n + len(self._extra):
+            raise IndexError(i)
+        return self._t[i] if i < n else self._extra[i - n]
+
+    def __iter__(self):
+        for v in self._t.unbind(0):
+            yield v
+        for v in self._extra:
+            yield v
+
+    def append(self, v):
+        self._extra.append(v)
+
+    def __add__(self, other):
+        return list(self) + list(other)
+
+    def __eq__(self, other):
+        return list(self) == list(other)
+
+    def __repr__(self):
+        return repr(list(self))
+
+
 class BeamSearch:
     """Rows = decode_beam_size hypotheses of ONE utterance; `valid` marks the live ones."""
 
@@ -81,7 +122,7 @@ class BeamSearch:
             self.r[0][0].copy_(r0)
         self._io = [None, None]
 
-    def _make_io(self, src, att_logp, lm_logp):
+    def _make_io(self, src, att_logp, lm_logp, att_lse=None, lm_lse=None):
         dst = 1 - src
         io = _lib.BeamIO()
         p = _lib.ptr
@@ -100,6 +141,7 @@ class BeamSearch:
         io.hist_parent, io.hist_tok, io.hist_score = p(self.hist_parent), p(self.hist_tok), p(self.hist_score)
         io.fin_count, io.fin_step, io.fin_row = p(self.fin_count), p(self.fin_step), p(self.fin_row)
         io.fin_score, io.fin_sum = p(self.fin_score), p(self.fin_sum)
+        io.att_lse, io.lm_lse = p(att_lse), p(lm_lse)              # given: att_logp / lm_logp hold raw logits
         return io
 
     @property
@@ -154,6 +196,24 @@ class BeamSearch:
             step -= 1
         return toks[::-1], scs[::-1]
 
+    @staticmethod
+    def _paths(h, starts):
+        """Vectorised `_path` for many hypotheses at once: starts = [(step, row)], step -1 = the root (empty path).
+        One numpy gather per decode step instead of a Python loop per token."""
+        m = len(starts)
+        steps = np.asarray([s for s, _ in starts], dtype=np.int64)
+        cur = np.asarray([r for _, r in starts], dtype=np.int64)
+        L = int(steps.max()) + 1 if m else 0
+        toks = np.zeros((m, max(L, 1)), dtype=np.int64)
+        scs = np.zeros((m, max(L, 1)), dtype=np.float32)
+        for st in range(L - 1, -1, -1):
+            idx = np.nonzero(steps >= st)[0]
+            r = cur[idx]
+            toks[idx, st] = h['tok'][st, r]
+            scs[idx, st] = h['score'][st, r]
+            cur[idx] = h['parent'][st, r]
+        return [(toks[i, :steps[i] + 1], scs[i, :steps[i] + 1]) for i in range(m)]
+
     def results(self, emb=None):
         """asr.py:244-258: finals in finalisation order, then the survivors in rank order, one stable
         sort by mean score, best `beam`.  Returns Hypothesis objects (postprocess.py:44) whose
@@ -161,21 +221,236 @@ class BeamSearch:
         h = self.history()
 
         def hyp(toks, scs):
-            return Hypothesis(None, emb, output_seq=[torch.tensor(t) for t in toks],
-                              output_scores=[torch.tensor(float(v), dtype=torch.float32) for v in scs])
+            # 0-dim CPU tensors like the reference's, made on demand from ONE tensor per hypothesis (_Scalars)
+            seq = _Scalars(torch.from_numpy(np.ascontiguousarray(toks, dtype=np.int64)))
+            sc = _Scalars(torch.from_numpy(np.ascontiguousarray(scs, dtype=np.float32)))
+            return Hypothesis(None, emb, output_seq=seq, output_scores=sc)
 
-        outs = []
-        for i in range(h['fin_count']):
-            toks, scs = self._path(h, int(h['fin_step'][i]) - 1, int(h['fin_row'][i]))
-            outs.append(hyp(toks + [1], scs + [h['fin_score'][i]]))
-            if self.n == 1:
-                return outs[:1]                                 # asr.py:246-247
+        nfin = h['fin_count'] if self.n > 1 else min(h['fin_count'], 1)        # beam 1 returns at the first <eos>, asr.py:246-247
+        starts = [(int(h['fin_step'][i]) - 1, int(h['fin_row'][i])) for i in range(nfin)]
         last = self.steps_done - 1
-        for row in range(self.n):
-            if h['valid'][row]:
-                outs.append(hyp(*self._path(h, last, row)))
-        outs.sort(key=lambda o: o.avgScore(), reverse=True)
-        return outs[:self.n]
+        live = [] if (self.n == 1 and nfin) else [row for row in range(self.n) if h['valid'][row]]
+        starts += [(last, row) for row in live]
+        paths = self._paths(h, starts)
+        outs = []
+
+        def mean_score(scs):
+            # Hypothesis.avgScore (postprocess.py:71-74) is Python's sum() over 0-dim fp32 tensors -- a strictly
+            # left-to-right fp32 sum -- divided by the count in fp32; np.cumsum is the same sequential sum
+            return float(np.cumsum(scs, dtype=np.float32)[-1] / np.float32(len(scs)))
+
+        for i in range(nfin):
+            toks, scs = paths[i]
+            scs = np.append(scs, np.float32(h['fin_score'][i]))
+            outs.append((mean_score(scs), hyp(np.append(toks, 1), scs)))
+        if self.n == 1 and nfin:
+            return [outs[0][1]]
+        for toks, scs in paths[nfin:]:
+            outs.append((mean_score(scs), hyp(toks, scs)))
+        outs.sort(key=lambda o: o[0], reverse=True)                           # stable, like the reference's sort
+        return [o[1] for o in outs[:self.n]]
+
+
+def _pad4(n):
+    return (n + 3) // 4 * 4
+
+
+def _padded_cols(w, cols):
+    """[R, C] -> contiguous [R, cols] with zero columns appended (16-byte aligned rows for the tile kernels)."""
+    if w.shape[1] == cols:
+        return w.detach().contiguous()
+    out = torch.zeros(w.shape[0], cols, dtype=w.dtype, device=w.device)
+    out[:, :w.shape[1]] = w.detach()
+    return out
+
+
+class _DecodePack:
+    """Per-model constants of the native decode step (csrc/decode.cu), rebuilt when a parameter changes:
+    the embedding half of the first Speller / LM layer folded into a [V, 4H] table (+ both biases), and every other
+    weight matrix with its inner dimension padded to a multiple of 4 and [x1 | x2] operands side by side."""
+
+    def __init__(self, model, lm):
+        dec = model.decoder
+        self.version = _DecodePack.stamp(model, lm)
+        H = dec.dim
+        H4 = _pad4(H)
+        D = None
+        layers = [getattr(dec, 'layer' + str(i)) for i in range(dec.layer)]
+        emb_w = model.embed.weight.detach()
+        E = emb_w.shape[1]
+        l0 = layers[0]
+        D = l0.weight_ih.shape[1] - E
+        self.H, self.H4, self.D, self.D4 = H, H4, D, _pad4(D)
+        bias0 = 0
+        if l0.bias:
+            bias0 = (l0.bias_ih + l0.bias_hh).detach()
+        self.dec_table = (emb_w @ l0.weight_ih.detach()[:, :E].t() + bias0).contiguous()          # [V, 4H]
+        self.dec_w = [torch.cat([_padded_cols(l0.weight_ih.detach()[:, E:], self.D4),
+                                 _padded_cols(l0.weight_hh, H4)], 1).contiguous()]
+        self.dec_b = [(None, None)]
+        for l in layers[1:]:
+            self.dec_w.append(torch.cat([_padded_cols(l.weight_ih, H4), _padded_cols(l.weight_hh, H4)], 1).contiguous())
+            self.dec_b.append((l.bias_ih.detach().contiguous(), l.bias_hh.detach().contiguous()) if l.bias else (None, None))
+        ct = model.char_trans
+        self.char_w = _padded_cols(ct.weight, H4)
+        self.char_b = None if ct.bias is None else ct.bias.detach().contiguous()
+        self.lm = None
+        if lm is not None:
+            r = lm.rnn
+            HL = lm.h_dim
+            HL4 = _pad4(HL)
+            b0 = (r.bias_ih_l0 + r.bias_hh_l0).detach() if r.bias else 0
+            table = (lm.emb.weight.detach() @ r.weight_ih_l0.detach().t() + b0).contiguous()       # [V, 4HL]
+            ws = [_padded_cols(r.weight_hh_l0, HL4)]
+            bs = [(None, None)]
+            for l in range(1, r.num_layers):
+                ws.append(torch.cat([_padded_cols(getattr(r, 'weight_ih_l%d' % l), HL4),
+                                     _padded_cols(getattr(r, 'weight_hh_l%d' % l), HL4)], 1).contiguous())
+                bs.append((getattr(r, 'bias_ih_l%d' % l).detach().contiguous(),
+                           getattr(r, 'bias_hh_l%d' % l).detach().contiguous()) if r.bias else (None, None))
+            self.lm = dict(HL=HL, HL4=HL4, table=table, w=ws, b=bs, out_w=_padded_cols(lm.out.weight, HL4),
+                           out_b=None if lm.out.bias is None else lm.out.bias.detach().contiguous(),
+                           layers=r.num_layers)
+
+    @staticmethod
+    def stamp(model, lm):
+        ps = list(model.decoder.parameters()) + list(model.embed.parameters()) + list(model.char_trans.parameters())
+        if lm is not None:
+            ps += list(lm.parameters())
+        return tuple((p.data_ptr(), p._version) for p in ps)
+
+    @staticmethod
+    def supported(model, lm):
+        dec = model.decoder
+        layers = [getattr(dec, 'layer' + str(i)) for i in range(dec.layer)]
+        if not all(isinstance(l, torch.nn.LSTMCell) for l in layers) or len(layers) > 4:
+            return False
+        if lm is not None and (not isinstance(lm.rnn, torch.nn.LSTM) or lm.rnn.num_layers > 4 or lm.rnn.bidirectional
+                               or getattr(lm.rnn, 'proj_size', 0) != 0):
+            return False
+        return True
+
+
+def _decode_pack(model, lm):
+    pack = getattr(model, '_b2asr_decode_pack', None)
+    if pack is None or pack.version != _DecodePack.stamp(model, lm):
+        pack = _DecodePack(model, lm)
+        object.__setattr__(model, '_b2asr_decode_pack', pack)
+    return pack
+
+
+def _native_decode(model, lm, bs, h, keys, enc_len0, decode_step):
+    """All decode steps through b2asr_decode_run: two per-parity programs over double-buffered state; rows read
+    their parent's state through the survivor map the beam step wrote (bs.parent), so nothing is gathered."""
+    import ctypes
+    att = model.attention
+    pk = _decode_pack(model, lm)
+    dev = h.device
+    n, V = bs.n, bs.V
+    Tp, D = h.shape[1], h.shape[2]
+    A = keys.shape[-1]
+    loc = att.mode == 'loc'
+    pr = att._params()
+    f32 = dict(dtype=torch.float32, device=dev)
+    nl = len(pk.dec_w)
+    lens_dev = torch.full((n,), enc_len0, dtype=torch.int32, device=dev)
+    dec_h = [[torch.zeros(n, pk.H4, **f32) for _ in range(2)] for _ in range(nl)]
+    dec_c = [[torch.zeros(n, pk.H4, **f32) for _ in range(2)] for _ in range(nl)]
+    att_buf = [torch.zeros(n, Tp, **f32) for _ in range(2)]
+    if loc:
+        for b in att_buf:
+            b[:, :enc_len0] = 1.0 / enc_len0                                   # asr.py:444-449
+    ctx = torch.zeros(n, pk.D4, **f32)
+    nct = _lib.lib().b2asr_linear_lse_ctas(V)
+    char_logits = torch.empty(n, V, **f32)
+    char_lse = torch.empty(n, **f32)
+    char_part = torch.empty(n, nct, 2, **f32)
+    tickets = torch.zeros(2, dtype=torch.int32, device=dev)
+    keep = [lens_dev, dec_h, dec_c, att_buf, ctx, char_logits, char_lse, char_part, tickets]
+    if pk.lm is not None:
+        L = pk.lm
+        lm_h = [[torch.zeros(n, L['HL4'], **f32) for _ in range(2)] for _ in range(L['layers'])]
+        lm_c = [[torch.zeros(n, L['HL4'], **f32) for _ in range(2)] for _ in range(L['layers'])]
+        lm_logits = torch.empty(n, V, **f32)
+        lm_lse = torch.empty(n, **f32)
+        lm_part = torch.empty(n, nct, 2, **f32)
+        keep += [lm_h, lm_c, lm_logits, lm_lse, lm_part]
+    p = _lib.ptr
+    C, Kw = (pr['conv'].shape[0], (pr['conv'].shape[-1] - 1) // 2) if loc else (0, 0)
+    conv = pr['conv'].contiguous() if loc else None
+    lproj = pr['lproj'].contiguous() if loc else None
+    gen_w = pr['gen_w'].contiguous() if loc else None
+    keep += [conv, lproj, gen_w]
+
+    def cell(x1, K1, x2, W, base, base_row, b, c_prev, c_new, h_new, H, H4, after, mapped=True):
+        cs = _lib.CellStep()
+        cs.B, cs.H, cs.K1, cs.K2 = n, H, K1, H4
+        cs.x1, cs.x1_ld = p(x1), (x1.stride(0) if x1 is not None else 0)
+        cs.x2, cs.x2_ld = p(x2), x2.stride(0)
+        cs.map = p(bs.parent) if mapped else 0
+        cs.W, cs.w_ld = p(W), W.stride(0)
+        cs.base, cs.base_ld, cs.base_row = p(base), (base.stride(0) if base is not None else 0), p(base_row)
+        cs.b1, cs.b2 = p(b[0]), p(b[1])
+        cs.c_prev, cs.c, cs.c_ld = p(c_prev), p(c_new), H4
+        cs.h, cs.h_ld = p(h_new), H4
+        cs.after_linear = after
+        return cs
+
+    progs = (_lib.DecodeProg * 2)()
+    ios = []
+    for src in (0, 1):
+        dst = 1 - src
+        pg = progs[src]
+        a = pg.attn
+        a.mode, a.C, a.Kw, a.B, a.T, a.D, a.A, a.dec, a.cluster = _attn.MODES[att.mode], C, Kw, n, Tp, D, A, pk.H, 0
+        a.scale = 2.0
+        a.s, a.s_stride = p(dec_h[0][src]), pk.H4
+        a.Wphi, a.keys, a.k_bstride, a.h, a.h_bstride = p(pr['phi']), p(keys), 0, p(h), 0
+        a.lens, a.prev_att, a.row_map = p(lens_dev), (p(att_buf[src]) if loc else 0), p(bs.parent)
+        a.Wc, a.Wl, a.wg, a.bg = p(conv), p(lproj), p(gen_w), (p(pr['gen_b']) if loc else 0)
+        a.att, a.ctx, a.ctx_stride = p(att_buf[dst]), p(ctx), pk.D4
+        last = bs.last[src]
+        cells = []
+        for l in range(nl):                                                   # Speller (asr.py:352-357)
+            if l == 0:
+                cells.append(cell(ctx, pk.D4, dec_h[0][src], pk.dec_w[0], pk.dec_table, last, pk.dec_b[0],
+                                  dec_c[0][src], dec_c[0][dst], dec_h[0][dst], pk.H, pk.H4, 0))
+            else:
+                cells.append(cell(dec_h[l - 1][dst], pk.H4, dec_h[l][src], pk.dec_w[l], None, None, pk.dec_b[l],
+                                  dec_c[l][src], dec_c[l][dst], dec_h[l][dst], pk.H, pk.H4, 0))
+        lin = pg.linear[0]                                                    # char_trans + lse (asr.py:210)
+        lin.B, lin.K, lin.V = n, pk.H4, V
+        lin.x, lin.x_ld, lin.W, lin.w_ld, lin.bias = p(dec_h[nl - 1][dst]), pk.H4, p(pk.char_w), pk.H4, p(pk.char_b)
+        lin.logits, lin.out_ld, lin.lse, lin.part, lin.ticket = p(char_logits), V, p(char_lse), p(char_part), tickets.data_ptr()
+        pg.n_linear = 1
+        lmlog = lmlse = None
+        if pk.lm is not None:                                                 # RNN-LM step (rnnlm.py:19-25)
+            L = pk.lm
+            for l in range(L['layers']):
+                if l == 0:
+                    cells.append(cell(None, 0, lm_h[0][src], L['w'][0], L['table'], last, L['b'][0],
+                                      lm_c[0][src], lm_c[0][dst], lm_h[0][dst], L['HL'], L['HL4'], 1))
+                else:
+                    cells.append(cell(lm_h[l - 1][dst], L['HL4'], lm_h[l][src], L['w'][l], None, None, L['b'][l],
+                                      lm_c[l][src], lm_c[l][dst], lm_h[l][dst], L['HL'], L['HL4'], 1))
+            lin = pg.linear[1]
+            lin.B, lin.K, lin.V = n, L['HL4'], V
+            lin.x, lin.x_ld, lin.W, lin.w_ld, lin.bias = p(lm_h[-1][dst]), L['HL4'], p(L['out_w']), L['HL4'], p(L['out_b'])
+            lin.logits, lin.out_ld, lin.lse, lin.part, lin.ticket = p(lm_logits), V, p(lm_lse), p(lm_part), tickets.data_ptr() + 4
+            pg.n_linear = 2
+            lmlog, lmlse = lm_logits, lm_lse
+        pg.n_cells = len(cells)
+        for i, cs in enumerate(cells):
+            pg.cells[i] = cs
+        io = bs._make_io(src, char_logits, lmlog, char_lse, lmlse)
+        ios.append(io)
+        pg.beam = ctypes.pointer(io)
+    per_step = 1 + len(cells) + progs[0].n_linear + 1
+    _lib.call("b2asr_decode_run", per_step * decode_step, _lib.lib().b2asr_decode_run, progs, 0, int(decode_step),
+              _lib.stream_ptr())
+    bs.cur = decode_step & 1
+    bs.steps_done = decode_step
+    bs._keep = (keep, progs, ios, pk)                                          # alive until the results are read
 
 
 def beam_decode(model, audio_feature, decode_step, state_len, decode_beam_size, use_graph=None):
@@ -212,6 +487,14 @@ def beam_decode(model, audio_feature, decode_step, state_len, decode_beam_size, 
         h = h.contiguous()
         keys = (att.project_keys(h) if att.proj else h).contiguous()
         Tp, D = h.shape[1], h.shape[2]
+        from . import _enc
+        if _DecodePack.supported(model, lm) and os.environ.get('B2ASR_DECODE_NATIVE', '1') != '0' and decode_step > 0:
+            # every step's kernels enqueued by ONE C call (csrc/decode.cu); the per-step path below stays for cells
+            # the tile kernels do not take (GRU) and for A/B runs
+            _native_decode(model, lm, bs, h, keys, int(enc_len[0]), int(decode_step))
+            out = bs.results(emb=model.embed)
+            _enc.check_status(dev)
+            return out
         p = att._params()
         lens_dev = torch.full((n,), int(enc_len[0]), dtype=torch.int32, device=dev)
         layers = [getattr(dec, 'layer' + str(i)) for i in range(dec.layer)]

@@ -16,6 +16,8 @@ struct AttnArgs {
   const float* h; long long h_bstride;          // [*,T,D]
   const int* lens;                              // [B]
   const float* prev_att;                        // [B,T] or nullptr (uniform first step)
+  const long long* row_map;                     // forward only, or nullptr: row b reads s and prev_att of row row_map[b]
+                                                // (beam decode: the survivor's parent row; saves the state gathers)
   const float* Wc; int C; int Kw;               // [C,2Kw+1]
   const float* Wl;                              // [A,C]
   const float* wg; const float* bg;             // [A],[1]

@@ -45,6 +45,9 @@ __global__ void __launch_bounds__(MAXNT, MINB) attn_step_fwd_kernel(AttnArgs p) 
   const int tfmax = TFK > TFH ? TFK : TFH;
   const int nK = (nf + TFK - 1) / TFK, nH = (nf + TFH - 1) / TFH, ntiles = nK + nH;
   const unsigned stage_floats = p.stage_bytes / 4;
+  // NOTE: row_map is written by the kernel right before this one in the decode loop (the beam step); reading it here,
+  // before pdl_wait(), is safe only because that kernel never triggers its dependents early (common.cuh).
+  const long long bsrc = p.row_map ? p.row_map[b] : (long long)b;
 
   B2_TRACE(p, 0);
   if (tid == 0) {
@@ -82,7 +85,7 @@ __global__ void __launch_bounds__(MAXNT, MINB) attn_step_fwd_kernel(AttnArgs p) 
     const float unif = len > 0 ? 1.f / (float)len : 0.f;
     for (int j = tid; j < npa; j += NT) {
       const int t = t0 - p.Kw + j;
-      if (t >= 0 && t < T && p.prev_att) cp_async4(pa + j, p.prev_att + (long long)b * T + t);
+      if (t >= 0 && t < T && p.prev_att) cp_async4(pa + j, p.prev_att + bsrc * T + t);
       else pa[j] = (t >= 0 && t < len) ? unif : 0.f;
     }
     cp_async_wait_all();
@@ -103,7 +106,7 @@ __global__ void __launch_bounds__(MAXNT, MINB) attn_step_fwd_kernel(AttnArgs p) 
   }
   pdl_wait();                           // the decoder state comes from the cell kernel before this one
   pdl_launch();
-  for (int i = tid; i < p.dec; i += NT) cp_async4(s_sm + i, p.s + (long long)b * p.s_stride + i);
+  for (int i = tid; i < p.dec; i += NT) cp_async4(s_sm + i, p.s + bsrc * p.s_stride + i);
   cp_async_wait_all();
   cluster_or_cta_sync(CS);            // #0: operands staged; every CTA of the cluster is running (DSMEM is legal)
   B2_TRACE(p, 2);
@@ -406,6 +409,16 @@ extern "C" int b2asr_attn_step_fwd(int mode, const float* s, int64_t s_stride, c
                                    const float* Wc, int C, int Kw, const float* Wl, const float* wg, const float* bg,
                                    float scale, float* att, float* ctx, float* q_out,
                                    int B, int T, int D, int A, int dec, int cluster, void* stream) {
+  return b2asr_attn_step_fwd_rows(mode, s, s_stride, Wphi, keys, k_bstride, h, h_bstride, lens, prev_att, nullptr, Wc, C,
+                                  Kw, Wl, wg, bg, scale, att, ctx, (int64_t)0, q_out, B, T, D, A, dec, cluster, stream);
+}
+
+extern "C" int b2asr_attn_step_fwd_rows(int mode, const float* s, int64_t s_stride, const float* Wphi,
+                                        const float* keys, int64_t k_bstride, const float* h, int64_t h_bstride,
+                                        const int32_t* lens, const float* prev_att, const int64_t* row_map,
+                                        const float* Wc, int C, int Kw, const float* Wl, const float* wg, const float* bg,
+                                        float scale, float* att, float* ctx, int64_t ctx_stride, float* q_out,
+                                        int B, int T, int D, int A, int dec, int cluster, void* stream) {
   B2_REQUIRE(s && keys && h && lens && att && ctx, B2ASR_EINVAL, "attn_step_fwd: null pointer argument");
   B2_REQUIRE(mode == 0 || mode == 1, B2ASR_EINVAL, "attn_step_fwd: mode %d (0 dot, 1 loc)", mode);
   B2_REQUIRE(B > 0 && T > 0 && D > 0 && A > 0 && dec > 0, B2ASR_EINVAL, "attn_step_fwd: bad sizes");
@@ -418,8 +431,10 @@ extern "C" int b2asr_attn_step_fwd(int mode, const float* s, int64_t s_stride, c
   a.h = h; a.h_bstride = h_bstride; a.lens = lens; a.prev_att = prev_att; a.Wc = Wc; a.C = C; a.Kw = Kw;
   a.Wl = Wl; a.wg = wg; a.bg = bg; a.scale = scale; a.att = att; a.ctx = ctx; a.q_out = q_out;
   a.B = B; a.T = T; a.D = D; a.A = A; a.dec = dec;
-  a.ctx_stride = g_attn_row_stride ? g_attn_row_stride : D;
+  a.row_map = (const long long*)row_map;
+  a.ctx_stride = ctx_stride > 0 ? ctx_stride : (g_attn_row_stride ? g_attn_row_stride : D);
   g_attn_row_stride = 0;
+  B2_REQUIRE(a.ctx_stride >= D, B2ASR_EINVAL, "attn_step_fwd: ctx_stride %lld smaller than D=%d", (long long)a.ctx_stride, D);
   a.trace = attn_trace_buffer();
   size_t smem = 0;
   static const int fwd_cs = [] { const char* e = getenv("B2ASR_ATT_FWD_CS"); return e && *e ? atoi(e) : 0; }();

@@ -258,7 +258,12 @@ __global__ void __launch_bounds__(kBeamNT) beam_step_kernel(b2asr_beam_io io) {
   BT(0);
   if (live) {
     const float* att = io.att_logp + (long long)row * V;
-    for (int i = tid; i < V; i += NT) val[i] = att[i];
+    if (io.att_lse) {                                            // logits in: log_softmax = logit - lse (asr.py:210)
+      const float lse = io.att_lse[row];
+      for (int i = tid; i < V; i += NT) val[i] = __fsub_rn(att[i], lse);
+    } else {
+      for (int i = tid; i < V; i += NT) val[i] = att[i];
+    }
     __syncthreads();
     if (ctc) {
       // ---- CTC candidates: top-K of the attention log-probs (asr.py:215-216) -----------------------
@@ -294,7 +299,12 @@ __global__ void __launch_bounds__(kBeamNT) beam_step_kernel(b2asr_beam_io io) {
     }
     if (io.lm_logp != nullptr && io.w_lm > 0.f) {                               // asr.py:232-235
       const float* lm = io.lm_logp + (long long)row * V;
-      for (int i = tid; i < V; i += NT) val[i] = __fadd_rn(val[i], __fmul_rn(io.w_lm, lm[i]));
+      if (io.lm_lse) {
+        const float lse = io.lm_lse[row];
+        for (int i = tid; i < V; i += NT) val[i] = __fadd_rn(val[i], __fmul_rn(io.w_lm, __fsub_rn(lm[i], lse)));
+      } else {
+        for (int i = tid; i < V; i += NT) val[i] = __fadd_rn(val[i], __fmul_rn(io.w_lm, lm[i]));
+      }
       __syncthreads();
     }
     // ---- top-`beam` of the fused scores (asr.py:238) ---------------------------------------------------

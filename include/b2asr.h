@@ -134,6 +134,18 @@ int b2asr_attn_step_fwd(int mode, const float* s, int64_t s_stride, const float*
                         float scale, float* att, float* ctx, float* q_out,
                         int B, int T, int D, int A, int dec, int cluster, void* stream);
 
+/* The same step with two extras the beam decode uses (reference src/asr.py:201-207: every hypothesis restores ITS
+ * parent's decoder state and previous alignment before attending):
+ *   row_map    [B] int64 DEVICE or NULL: row b reads s and prev_att of row row_map[b] (the surviving child's parent
+ *              row, written by b2asr_beam_step) -- no gather of the state between steps
+ *   ctx_stride row stride of ctx in elements (0 = D): lets ctx land inside a wider row, e.g. [ctx | h] of the cell */
+int b2asr_attn_step_fwd_rows(int mode, const float* s, int64_t s_stride, const float* Wphi,
+                             const float* keys, int64_t k_bstride, const float* h, int64_t h_bstride,
+                             const int32_t* lens, const float* prev_att, const int64_t* row_map,
+                             const float* Wc, int C, int Kw, const float* Wl, const float* wg, const float* bg,
+                             float scale, float* att, float* ctx, int64_t ctx_stride, float* q_out,
+                             int B, int T, int D, int A, int dec, int cluster, void* stream);
+
 /* ------------------------------------------------------------------------
  * Backward of one attention step (the reference obtains it from autograd over
  * the ops of src/asr.py:422-457).  Activations are recomputed from q_saved
@@ -224,10 +236,78 @@ typedef struct b2asr_beam_io {
   int32_t* fin_row;        /* [max_steps*n] parent row at that step */
   float*   fin_score;      /* [max_steps*n] fused score of <eos> */
   float*   fin_sum;        /* [max_steps*n] fp32 score sum including <eos> */
+  /* optional: att_logp / lm_logp hold raw LOGITS and these the rows' log-sum-exp, so that the log_softmax of
+   * asr.py:210,235 is `logit - lse` (torch's own epilogue form) inside the kernel; NULL = the inputs are log-probs */
+  const float* att_lse;    /* [n] or NULL */
+  const float* lm_lse;     /* [n] or NULL */
 } b2asr_beam_io;
 
 size_t b2asr_beam_io_size(void);   /* sizeof(b2asr_beam_io), for binding sanity checks */
 int    b2asr_beam_step(const b2asr_beam_io* io, void* stream);
+
+/* ------------------------------------------------------------------------
+ * the neural half of a decode step, batched over the beam, and the native decode loop.
+ * Reference src/asr.py:201-235 (per hypothesis: attention -> Speller -> char_trans -> log_softmax -> RNN-LM step,
+ * src/rnnlm.py:19-25).  csrc/decode.cu.
+ *
+ * b2asr_cell_step_fwd: one LSTM(Cell) layer for B rows (torch gate order i,f,g,o):
+ *     pre = base[base_row[b]] + [x1[b] | x2[map[b]]] W^T + b1 + b2 ;  c = f*c_prev[map[b]] + i*g ;  h = o*tanh(c)
+ *   x1 [B,K1] (row stride x1_ld), x2 [*,K2] rows taken through `map` (the surviving child's parent row; NULL = identity),
+ *   W [4H, K1+K2] (row stride w_ld); K1, K2 and all strides multiples of 4, operands 16-byte aligned (pad with zeros);
+ *   base [*,4H] (row stride base_ld): e.g. the embedding half of the layer folded into a [V,4H] table, row = the
+ *   hypothesis' last token (base_row int64; NULL = row b; base NULL = none); c_prev / c rows have stride c_ld.
+ *   after_linear: position of this layer in b2asr_decode_run's step (0 = before the first output layer, 1 = after).
+ * b2asr_linear_lse_fwd: logits[b] = x[b] W^T + bias for B rows and V outputs, plus lse[b] = logsumexp(logits[b]);
+ *   part [B, b2asr_linear_lse_ctas(V), 2] scratch, ticket [1] zeroed once.
+ * b2asr_decode_run: enqueue decode steps first_step .. first_step+steps-1; step t runs prog[t & 1] (double-buffered
+ *   state): attention (b2asr_attn_step_fwd_rows), cells before the first output layer, output layer 0, remaining
+ *   cells, output layer 1, b2asr_beam_step.  No host work or synchronisation between steps.
+ * ---------------------------------------------------------------------- */
+typedef struct b2asr_cell_step {
+  int32_t B, H, K1, K2;
+  const float* x1; int64_t x1_ld;
+  const float* x2; int64_t x2_ld;
+  const int64_t* map;
+  const float* W; int64_t w_ld;
+  const float* base; int64_t base_ld; const int64_t* base_row;
+  const float* b1; const float* b2;
+  const float* c_prev; float* c; int64_t c_ld;
+  float* h; int64_t h_ld;
+  int32_t after_linear; int32_t pad_;
+} b2asr_cell_step;
+
+typedef struct b2asr_linear_lse {
+  int32_t B, K, V, pad_;
+  const float* x; int64_t x_ld;
+  const float* W; int64_t w_ld;
+  const float* bias;
+  float* logits; int64_t out_ld;
+  float* lse; float* part; uint32_t* ticket;
+} b2asr_linear_lse;
+
+typedef struct b2asr_attn_call {          /* the arguments of b2asr_attn_step_fwd_rows */
+  int32_t mode, C, Kw, B, T, D, A, dec, cluster; float scale;
+  const float* s; int64_t s_stride; const float* Wphi; const float* keys; int64_t k_bstride;
+  const float* h; int64_t h_bstride; const int32_t* lens; const float* prev_att; const int64_t* row_map;
+  const float* Wc; const float* Wl; const float* wg; const float* bg;
+  float* att; float* ctx; int64_t ctx_stride;
+} b2asr_attn_call;
+
+typedef struct b2asr_decode_prog {
+  b2asr_attn_call attn;
+  int32_t n_cells, n_linear;
+  b2asr_cell_step cells[8];
+  b2asr_linear_lse linear[2];
+  const b2asr_beam_io* beam;
+} b2asr_decode_prog;
+
+size_t b2asr_cell_step_size(void);
+size_t b2asr_linear_lse_size(void);
+size_t b2asr_decode_prog_size(void);
+int b2asr_linear_lse_ctas(int V);
+int b2asr_cell_step_fwd(const b2asr_cell_step* a, void* stream);
+int b2asr_linear_lse_fwd(const b2asr_linear_lse* a, void* stream);
+int b2asr_decode_run(const b2asr_decode_prog* prog, int first_step, int steps, void* stream);
 
 /* ------------------------------------------------------------------------
  * Decoder-loop fusion: pointwise half of the

@@ -37,3 +37,11 @@ for e in ev:
     a = byname.setdefault(e.name[:100], [0, 0.0]); a[0] += 1; a[1] += e.device_time
 for k, (c, t) in sorted(byname.items(), key=lambda kv: -kv[1][1])[:25]:
     print("  %6d x %7.1f us = %7.2f ms  %s" % (c, t / c, t / 1e3, k))
+# timeline of one decode step in the middle of the utterance: every kernel between two beam steps
+bsteps = [i for i, e in enumerate(ev) if "beam_step_kernel" in e.name]
+if len(bsteps) > 82:
+    i0, i1 = bsteps[80], bsteps[81]
+    t0 = ev[i0].time_range.end
+    print("one step (after beam step #80): start/end in us relative to the previous beam step's end")
+    for e in ev[i0 + 1:i1 + 1]:
+        print("  %7.1f .. %7.1f  (%6.1f us)  %s" % (e.time_range.start - t0, e.time_range.end - t0, e.device_time, e.name[:60]))
