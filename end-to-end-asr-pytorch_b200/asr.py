@@ -327,6 +327,16 @@ class Attention(nn.Module):
         self._token = None
         self._lens_dev = None
 
+    def __setstate__(self, state):
+        """Whole-module checkpoints written by the UPSTREAM code (torch.save(self.asr_model), reference
+        src/solver.py:283, loaded at :314) unpickle into this class through the `src` shim package; they lack the
+        per-batch caches this mirror adds, and may hold a cached mask / key projection of the last training batch."""
+        super().__setstate__(state)
+        for name in ('comp_listener_feature', 'state_mask', '_session', '_token', '_lens_dev'):
+            self.__dict__[name] = None
+        if self.mode == 'loc':
+            self.__dict__['prev_att'] = None
+
     def reset_enc_mem(self):
         self.comp_listener_feature = None
         self.state_mask = None

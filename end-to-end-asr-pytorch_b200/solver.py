@@ -459,18 +459,35 @@ class Tester(Solver):
         self.verbose('Start decoding with beam search, beam size = ' + str(self.decode_beam_size))
         self.verbose('Number of utts to decode : {}, sharded over {} GPU(s).'.format(len(self.test_set), world))
         mine = []
+        journal = None
+        if world > 1:                       # rank-local journal, appended per utterance: an abort loses nothing decoded
+            import json
+            journal = open(os.path.join(self.ckpdir, self.decode_file + '.rank%d.jsonl' % rank), 'w')
         for i, (x, y) in enumerate(self.test_set):
             if i % world != rank:
                 continue
-            mine.append((i, self.beam_decode(x[0], y[0].tolist()[0], write=False)))
+            ref = y[0].tolist()[0]
+            try:
+                item = self.beam_decode(x[0], ref, write=False)
+            except ValueError as e:         # a shape the kernels refuse (e.g. an over-long utterance): report, go on
+                self.verbose('Utterance {} skipped: {}'.format(i, e))
+                item = (self.mapper.translate(ref, return_string=True), [''])
+            if world == 1:
+                self._write(*item)          # appended utterance by utterance, like the reference (solver.py:360-367)
+            else:
+                mine.append((i, item))
+                journal.write(json.dumps([i, item[0], item[1]]) + '\n')
+                journal.flush()
         if world > 1:
             import torch.distributed as dist
+            journal.close()
             gathered = [None] * world
             dist.all_gather_object(gathered, mine)                 # host-side gather of strings, not a GPU collective
-            mine = [item for part in gathered for item in part]
-        if rank == 0:
-            for _, (gt, hyps) in sorted(mine, key=lambda t: t[0]):
-                self._write(gt, hyps)
+            if rank == 0:
+                for _, (gt, hyps) in sorted((item for part in gathered for item in part), key=lambda t: t[0]):
+                    self._write(gt, hyps)
+            dist.barrier()
+            os.remove(os.path.join(self.ckpdir, self.decode_file + '.rank%d.jsonl' % rank))
         self.verbose('Decode done, best results at {}.'.format(str(os.path.join(self.ckpdir, self.decode_file + '.txt'))))
         self.verbose('Top {} results at {}.'.format(self.decode_beam_size,
                                                     str(os.path.join(self.ckpdir, self.decode_file + '_nbest.txt'))))

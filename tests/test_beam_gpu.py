@@ -141,10 +141,13 @@ def _load_model(g, cuda):
 
 
 @pytest.mark.parametrize("name", ["beam_joint.pt", "beam_att_only.pt", "beam_ctc.pt"])
-@pytest.mark.parametrize("graph", [False, True])
-def test_full_beam_decode_matches_reference_golden(cuda, name, graph):
+@pytest.mark.parametrize("path", ["native_loop", "per_step", "per_step_graph"])
+def test_full_beam_decode_matches_reference_golden(cuda, monkeypatch, name, path):
     """Whole Seq2Seq.beam_decode on the tiny reference model: tokens identical to what the unmodified
-    reference decoded, mean scores within 1e-4 (the neural parts run batched over the beam here)."""
+    reference decoded, mean scores within 1e-4 (the neural parts run batched over the beam here).  All three
+    routes: the native decode loop (csrc/decode.cu, the default), and the per-step library path eager / graph-replayed."""
+    monkeypatch.setenv("B2ASR_DECODE_NATIVE", "1" if path == "native_loop" else "0")
+    graph = path == "per_step_graph"
     g = torch.load(os.path.join(G, name), weights_only=False)
     model = _load_model(g, cuda)
     beam = _m("beam")
@@ -155,3 +158,40 @@ def test_full_beam_decode_matches_reference_golden(cuda, name, graph):
         assert abs(float(h.avgScore()) - r["avg"]) <= 1e-4 * abs(r["avg"]) + 1e-5
     again = model.beam_decode(g["x"].to(cuda), g["decode_step"], g["state_len"], g["beam"])     # module API
     assert [h.outIndex for h in again] == [r["tokens"] for r in g["hyps"]]
+
+
+def test_upstream_pickled_model_decodes_on_the_gpu(cuda, tmp_path):
+    """A whole-module checkpoint written by the UNMODIFIED reference (torch.save(model), solver.py:283) loads through
+    the `src` shim into the mirror classes, moves to the GPU and decodes the golden utterance token for token.
+    Needs the reference's sources (oracle/_ref on the GPU box, /root/reference in the build container)."""
+    import sys
+    from oracle import reference_loader as rl
+    if not rl.available():
+        pytest.skip("reference sources not present (oracle/_ref)")
+    ref = rl.load()
+    g = torch.load(os.path.join(G, "beam_joint.pt"), weights_only=False)
+    up = ref.asr.Seq2Seq(g["x"], g["vocab"], g["cfg"])
+    up.load_state_dict(g["state_dict"])
+    lm = ref.rnnlm.RNN_LM(*g["lm_dims"][:3], layers=g["lm_dims"][3])
+    lm.load_state_dict(g["lm_state_dict"])
+    saved = {k: v for k, v in sys.modules.items() if k == "src" or k.startswith("src.")}
+    try:
+        for k in saved:
+            del sys.modules[k]
+        sys.modules.update(ref.modules)
+        torch.save(up, str(tmp_path / "asr"))
+        torch.save(lm, str(tmp_path / "rnnlm"))
+    finally:
+        for k in [k for k in sys.modules if k == "src" or k.startswith("src.")]:
+            del sys.modules[k]
+        sys.modules.update(saved)
+    import src.asr  # noqa: F401  (the shim the unpickler resolves `src.asr.Seq2Seq` through)
+    model = torch.load(str(tmp_path / "asr"), weights_only=False, map_location="cpu")
+    assert type(model).__module__.startswith("end-to-end-asr-pytorch_b200")
+    model.load_lm(decode_lm_weight=g["lm_weight"], decode_lm_path=str(tmp_path / "rnnlm"))      # asr.py:50-53
+    model.joint_ctc, model.ctc_weight, model.decode_lm_weight = g["ctc_weight"] > 0, g["ctc_weight"], g["lm_weight"]
+    model = model.to(cuda).eval()
+    model.clear_att()
+    with torch.no_grad():
+        hyps = model.beam_decode(g["x"].to(cuda), g["decode_step"], g["state_len"], g["beam"])
+    assert [h.outIndex for h in hyps] == [r["tokens"] for r in g["hyps"]]

@@ -227,3 +227,46 @@ def test_golden_recipe_reproduces_a_committed_fixture_bit_for_bit():
     ref = rl.load(rl.UPSTREAM_ROOT)
     for name in ("attention_loc.pt", "seqloss.pt", "prefix.pt"):
         assert mg.deep_equal(mg.FIXTURES[name](ref), load(name)), name
+
+
+def test_upstream_whole_module_checkpoint_loads_through_the_src_shim(tmp_path):
+    """Reference src/solver.py:283 pickles the whole module (`torch.save(self.asr_model, path)`, class path
+    `src.asr.Seq2Seq`) and :314 / asr.py:52 unpickle it.  A checkpoint written by the UNMODIFIED reference must load
+    into the mirror classes through this repo's `src` package, with identical parameters and a usable object."""
+    import sys
+    from oracle import reference_loader as rl
+    if not rl.available():
+        pytest.skip("reference not present")
+    ref = rl.load()
+    g = load("trainstep.pt")
+    torch.manual_seed(0)
+    up = ref.asr.Seq2Seq(g["x"], g["vocab"], g["cfg"])
+    up.load_state_dict(g["state_dict"])
+    with torch.no_grad():
+        up(g["x"][:2], 3, tf_rate=1.0, teacher=g["y"][:2], state_len=g["lens"][:2])   # leaves cached attention state behind
+    lm = ref.rnnlm.RNN_LM(8, 8, g["vocab"], layers=2)
+    saved = {k: v for k, v in sys.modules.items() if k == "src" or k.startswith("src.")}
+    try:                                              # pickle looks the classes up as `src.asr.*`: the reference's, for saving
+        for k in saved:
+            del sys.modules[k]
+        sys.modules.update(ref.modules)
+        torch.save(up, str(tmp_path / "asr"))
+        torch.save(lm, str(tmp_path / "rnnlm"))
+    finally:
+        for k in [k for k in sys.modules if k == "src" or k.startswith("src.")]:
+            del sys.modules[k]
+        sys.modules.update(saved)
+    import src.asr as mirror                          # this repo's shim
+    import src.rnnlm as mirror_lm
+    got = torch.load(str(tmp_path / "asr"), weights_only=False)
+    assert type(got) is mirror.Seq2Seq and type(got.attention) is mirror.Attention and type(got.decoder) is mirror.Speller
+    assert type(got).__module__.startswith("end-to-end-asr-pytorch_b200")
+    sd = got.state_dict()
+    assert sd.keys() == g["state_dict"].keys()
+    assert all(torch.equal(sd[k], g["state_dict"][k]) for k in sd)
+    assert got.attention.comp_listener_feature is None and got.attention._session is None
+    got.clear_att()
+    fresh = mirror.Seq2Seq(g["x"], g["vocab"], g["cfg"])
+    assert set(vars(fresh)) <= set(vars(got)) and set(vars(fresh.attention)) <= set(vars(got.attention))
+    got_lm = torch.load(str(tmp_path / "rnnlm"), weights_only=False)
+    assert type(got_lm) is mirror_lm.RNN_LM and got_lm.state_dict().keys() == lm.state_dict().keys()
