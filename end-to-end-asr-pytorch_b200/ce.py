@@ -64,8 +64,14 @@ class _SeqLossMean(torch.autograd.Function):
     def backward(ctx, g_out, _g_rows, _g_argmax):
         (grad,) = ctx.saved_tensors
         g_out = g_out.reshape(1).to(torch.float32).contiguous()
+        last = getattr(ctx, 'folded', None)
+        if last is not None:
+            # a second backward over the same graph (retain_graph, a loss term used twice): the buffer already holds
+            # the FIRST call's upstream, so scale a copy by the ratio instead of rescaling the buffer again
+            return (grad * (g_out / last)).view(ctx.shape), None, None, None, None
         _lib.call("b2asr_rescale_if_needed", 1, _lib.lib().b2asr_rescale_if_needed, grad.data_ptr(),
                   grad.numel(), g_out.data_ptr(), ctx.prescale, _lib.stream_ptr())
+        ctx.folded = g_out.clone()                        # the upstream gradient now folded into the buffer
         return grad.view(ctx.shape), None, None, None, None
 
 

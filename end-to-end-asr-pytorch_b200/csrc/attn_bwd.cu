@@ -473,6 +473,8 @@ extern "C" int b2asr_attn_step_bwd(int mode, const float* Wphi, const float* key
                                    float* d_keys, int64_t dk_bstride, float* d_prev_att, float* d_zq, float* d_s,
                                    float* pgrad, int64_t pgrad_stride,
                                    int B, int T, int D, int A, int dec, int cluster, void* stream) {
+  const long long tl_stride = g_attn_row_stride;       // consumed before any early return (see attn_fwd.cu)
+  g_attn_row_stride = 0;
   B2_REQUIRE(keys && h && lens && q_saved && att_saved && d_ctx && d_keys, B2ASR_EINVAL, "attn_step_bwd: null pointer argument");
   B2_REQUIRE(mode == 0 || mode == 1, B2ASR_EINVAL, "attn_step_bwd: mode %d (0 dot, 1 loc)", mode);
   B2_REQUIRE(B > 0 && T > 0 && D > 0 && A > 0 && dec > 0, B2ASR_EINVAL, "attn_step_bwd: bad sizes");
@@ -489,8 +491,7 @@ extern "C" int b2asr_attn_step_bwd(int mode, const float* Wphi, const float* key
   a.d_keys = d_keys; a.dk_bstride = dk_bstride; a.d_prev_att = d_prev_att; a.d_zq = d_zq; a.d_s = d_s;
   a.pgrad = pgrad; a.pgrad_stride = pgrad_stride;
   a.B = B; a.T = T; a.D = D; a.A = A; a.dec = dec;
-  a.dctx_stride = g_attn_row_stride ? g_attn_row_stride : D;
-  g_attn_row_stride = 0;
+  a.dctx_stride = tl_stride ? tl_stride : D;
   a.trace = attn_trace_buffer();
   // first pass fixes CS/NT/tiles, second pass sizes the ring with the backward's extra arrays
   size_t smem = 0;

@@ -419,6 +419,8 @@ extern "C" int b2asr_attn_step_fwd_rows(int mode, const float* s, int64_t s_stri
                                         const float* Wc, int C, int Kw, const float* Wl, const float* wg, const float* bg,
                                         float scale, float* att, float* ctx, int64_t ctx_stride, float* q_out,
                                         int B, int T, int D, int A, int dec, int cluster, void* stream) {
+  const long long tl_stride = g_attn_row_stride;       // consumed before any early return: a failed
+  g_attn_row_stride = 0;                               // check must not leave the stride behind for the next call
   B2_REQUIRE(s && keys && h && lens && att && ctx, B2ASR_EINVAL, "attn_step_fwd: null pointer argument");
   B2_REQUIRE(mode == 0 || mode == 1, B2ASR_EINVAL, "attn_step_fwd: mode %d (0 dot, 1 loc)", mode);
   B2_REQUIRE(B > 0 && T > 0 && D > 0 && A > 0 && dec > 0, B2ASR_EINVAL, "attn_step_fwd: bad sizes");
@@ -432,8 +434,7 @@ extern "C" int b2asr_attn_step_fwd_rows(int mode, const float* s, int64_t s_stri
   a.Wl = Wl; a.wg = wg; a.bg = bg; a.scale = scale; a.att = att; a.ctx = ctx; a.q_out = q_out;
   a.B = B; a.T = T; a.D = D; a.A = A; a.dec = dec;
   a.row_map = (const long long*)row_map;
-  a.ctx_stride = ctx_stride > 0 ? ctx_stride : (g_attn_row_stride ? g_attn_row_stride : D);
-  g_attn_row_stride = 0;
+  a.ctx_stride = ctx_stride > 0 ? ctx_stride : (tl_stride ? tl_stride : D);
   B2_REQUIRE(a.ctx_stride >= D, B2ASR_EINVAL, "attn_step_fwd: ctx_stride %lld smaller than D=%d", (long long)a.ctx_stride, D);
   a.trace = attn_trace_buffer();
   size_t smem = 0;

@@ -79,9 +79,14 @@ class _CTCFunction(torch.autograd.Function):
             g = grad * (g_out.reshape(shape) / ctx.prescale)
         else:
             g_out = g_out.reshape(1).to(torch.float32).contiguous()
-            _lib.call("b2asr_rescale_if_needed", 1, _lib.lib().b2asr_rescale_if_needed, grad.data_ptr(),
-                      grad.numel(), g_out.data_ptr(), ctx.prescale, _lib.stream_ptr())
-            g = grad
+            last = getattr(ctx, 'folded', None)
+            if last is not None:                           # second backward over the graph: see ce.py
+                g = grad * (g_out / last)
+            else:
+                _lib.call("b2asr_rescale_if_needed", 1, _lib.lib().b2asr_rescale_if_needed, grad.data_ptr(),
+                          grad.numel(), g_out.data_ptr(), ctx.prescale, _lib.stream_ptr())
+                ctx.folded = g_out.clone()
+                g = grad
         return g, None, None, None, None, None, None, None, None
 
 

@@ -213,3 +213,29 @@ def test_determinism(cuda):
         m.ctc_loss(xd, y.to(cuda), il, tl, from_logits=True, batch_first=True).backward()
         outs.append(xd.grad.clone())
     assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+
+
+def test_second_backward_over_the_same_graph_rescales_a_copy(cuda):
+    """the stored gradient is rescaled in place when the upstream gradient differs from the prescale
+    folded in at forward time; a SECOND backward (retain_graph) with yet another upstream must not compound it."""
+    m = _mod()
+    ce = importlib.import_module("end-to-end-asr-pytorch_b200.ce")
+    x, y, il, tl = make_case(3, 40, 20, 8, seed=12)
+    _, _, g1 = co.reference_call(x, y, il.tolist(), tl, torch.float64, weight=1.0)
+    xd = x.to(cuda).requires_grad_(True)
+    loss = m.ctc_loss(xd, y.to(cuda), il, tl, from_logits=True, batch_first=True, grad_prescale=1.0)
+    (0.3 * loss).backward(retain_graph=True)
+    first = xd.grad.clone()
+    xd.grad = None
+    (2.0 * loss).backward()
+    assert float((first.cpu().double() - 0.3 * g1).abs().max()) <= 1e-4 * float(g1.abs().max())
+    assert float((xd.grad.cpu().double() - 2.0 * g1).abs().max()) <= 2e-4 * float(g1.abs().max())
+    # the sequence loss takes the same route
+    logits = torch.randn(2, 5, 9, device=cuda, requires_grad=True)
+    lab = torch.randint(1, 9, (2, 5), device=cuda)
+    tlen = torch.tensor([5, 5], device=cuda)
+    l2 = ce.seq_loss_mean(logits, lab, tlen, grad_prescale=0.5)
+    (0.5 * l2).backward(retain_graph=True)
+    a = logits.grad.clone(); logits.grad = None
+    (1.5 * l2).backward()
+    assert torch.allclose(logits.grad, 3.0 * a, rtol=1e-5, atol=1e-8)
