@@ -33,38 +33,41 @@ def edit_distance(a, b):
     return int(d)
 
 
+_SPECIAL = ('<sos>', '<eos>')
+_UNITS = (('subword', lambda keys, n: any('▁' in k for k in keys)),      # unit detection, postprocess.py:14-22:
+          ('phone', lambda keys, n: any('#' in k for k in keys)),         # sentencepiece marker, TIMIT's 'h#',
+          ('char', lambda keys, n: n < 50),                               # a small table, else words
+          ('word', lambda keys, n: True))
+
+
 class Mapper():
-    '''Mapper for index2token'''
+    """index -> token table of a corpus directory (`<data_path>/mapping.pkl`, token -> index with <sos>=0, <eos>=1;
+    reference postprocess.py:7-41).  Attributes kept: mapping, r_mapping, unit."""
 
     def __init__(self, file_path):
         with open(os.path.join(file_path, 'mapping.pkl'), 'rb') as fp:
             self.mapping = pickle.load(fp)
-        self.r_mapping = {v: k for k, v in self.mapping.items()}
-        symbols = ''.join(list(self.mapping.keys()))
-        if '▁' in symbols:
-            self.unit = 'subword'
-        elif '#' in symbols:
-            self.unit = 'phone'
-        elif len(self.mapping) < 50:
-            self.unit = 'char'
-        else:
-            self.unit = 'word'
+        self.r_mapping = dict((idx, tok) for tok, idx in self.mapping.items())
+        keys = list(self.mapping.keys())
+        self.unit = next(name for name, test in _UNITS if test(keys, len(keys)))
 
     def get_dim(self):
         return len(self.mapping)
 
     def translate(self, seq, return_string=False):
-        new_seq = [self.r_mapping[c] for c in trim_eos(seq)]
-        if return_string:
-            if self.unit == 'subword':
-                new_seq = ''.join(new_seq).replace('<sos>', '').replace('<eos>', '').replace('▁', ' ').lstrip()
-            elif self.unit == 'word':
-                new_seq = ' '.join(new_seq).replace('<sos>', '').replace('<eos>', '').lstrip()
-            elif self.unit == 'phone':
-                new_seq = ' '.join(collapse_phn(new_seq)).replace('<sos>', '').replace('<eos>', '')
-            elif self.unit == 'char':
-                new_seq = ''.join(new_seq).replace('<sos>', '').replace('<eos>', '')
-        return new_seq
+        """Tokens of `seq` up to and including the first <eos>; with return_string the text the unit implies
+        (subwords glued with '▁' -> ' ', words / folded phones space-separated, characters concatenated)."""
+        tokens = [self.r_mapping[i] for i in trim_eos(seq)]
+        if not return_string:
+            return tokens
+        if self.unit == 'phone':
+            tokens = collapse_phn(tokens)
+        text = (' ' if self.unit in ('word', 'phone') else '').join(tokens)
+        for sp in _SPECIAL:
+            text = text.replace(sp, '')
+        if self.unit == 'subword':
+            text = text.replace('▁', ' ')
+        return text.lstrip() if self.unit in ('subword', 'word') else text
 
 
 class Hypothesis:
@@ -90,30 +93,29 @@ class Hypothesis:
 
     def addTopk(self, topi, topv, decoder_state, att_map=None,
                 lm_state=None, ctc_state=None, ctc_prob=0.0, ctc_candidates=[]):
-        '''Expand with the given top-k: <eos>(=1) finalises THIS hypothesis in place, every other token
-        spawns a child (postprocess.py:76-106).  Returns (self or None, children).'''
-        new_hypothesis = []
-        term_score = None
-        ctc_s, ctc_p = None, None
-        for i in range(len(topi[0])):
-            if topi[0][i].item() == 1:
-                term_score = topv[0][i].cpu()
+        """Expand by the picks (topi, topv of shape [1, k]): <eos> (= 1) finalises THIS hypothesis in place, every
+        other token becomes a child that copies the history and, with joint CTC, takes the prefix state of its
+        candidate slot (postprocess.py:76-106).  Returns (self if finalised else None, children).
+        Host path kept for API compatibility; the device beam search does not call it (beam.py)."""
+        children, eos_score = [], None
+        for tok, score in zip(topi[0], topv[0]):
+            t = int(tok.item())
+            if t == 1:
+                eos_score = score.cpu()
                 continue
-            idxes = self.output_seq[:]
-            scores = self.output_scores[:]
-            idxes.append(topi[0][i].cpu())
-            scores.append(topv[0][i].cpu())
+            state_c = prob_c = None
             if ctc_state is not None:
-                idx = ctc_candidates.index(topi[0][i].item())
-                ctc_s = ctc_state[idx, :, :]
-                ctc_p = ctc_prob[idx]
-            new_hypothesis.append(Hypothesis(decoder_state, self.emb, output_seq=idxes, output_scores=scores,
-                                             lm_state=lm_state, ctc_state=ctc_s, ctc_prob=ctc_p, att_map=att_map))
-        if term_score is not None:
-            self.output_seq.append(torch.tensor(1))
-            self.output_scores.append(term_score)
-            return self, new_hypothesis
-        return None, new_hypothesis
+                slot = ctc_candidates.index(t)
+                state_c, prob_c = ctc_state[slot, :, :], ctc_prob[slot]
+            children.append(Hypothesis(decoder_state, self.emb,
+                                       output_seq=list(self.output_seq) + [tok.cpu()],
+                                       output_scores=list(self.output_scores) + [score.cpu()],
+                                       lm_state=lm_state, ctc_state=state_c, ctc_prob=prob_c, att_map=att_map))
+        if eos_score is None:
+            return None, children
+        self.output_seq.append(torch.tensor(1))
+        self.output_scores.append(eos_score)
+        return self, children
 
     @property
     def outIndex(self):
@@ -145,25 +147,30 @@ def cal_acc(pred, label, hyp=None):
 
 
 def cal_cer(pred, label, mapper, get_sentence=False, argmax=True):
-    if argmax:
-        pred = np.argmax(pred.cpu().detach(), axis=-1)
-    label = label.cpu()
-    pred = [mapper.translate(p, return_string=True) for p in pred]
-    label = [mapper.translate(l, return_string=True) for l in label]
+    """Mean word-level error rate of the greedy transcripts against the references (postprocess.py:135-146): both
+    sides go through `mapper.translate(..., return_string=True)`, are split on blanks, and the Levenshtein distance is
+    divided by the reference's length.  get_sentence=True returns the two lists of strings instead."""
+    ids = pred.detach().argmax(dim=-1).cpu() if argmax else pred
+    hyp_txt = [mapper.translate(row, return_string=True) for row in ids]
+    ref_txt = [mapper.translate(row, return_string=True) for row in label.cpu()]
     if get_sentence:
-        return pred, label
-    eds = [float(edit_distance(p.split(' '), l.split(' '))) / len(l.split(' ')) for p, l in zip(pred, label)]
-    return sum(eds) / len(eds)
+        return hyp_txt, ref_txt
+    rates = []
+    for h, r in zip(hyp_txt, ref_txt):
+        ref_words = r.split(' ')
+        rates.append(float(edit_distance(h.split(' '), ref_words)) / len(ref_words))
+    return sum(rates) / len(rates)
 
 
 def draw_att(att_list, hyp_txt):
-    '''Only the first attention head is drawn (postprocess.py:149-155).'''
-    attmaps = []
-    for att, hyp in zip(att_list[0], np.argmax(hyp_txt.cpu().detach(), axis=-1)):
-        att_len = len(trim_eos(hyp))
-        att = att.detach().cpu()
-        attmaps.append(torch.stack([att, att, att], dim=0)[:, :att_len, :])
-    return attmaps
+    """[3, steps, T'] image tensors of the first head's alignments, cut at each utterance's <eos> step
+    (postprocess.py:149-155); `hyp_txt` are the decoder logits the lengths are read from."""
+    lengths = [len(trim_eos(row)) for row in hyp_txt.detach().argmax(dim=-1).cpu()]
+    images = []
+    for att, n in zip(att_list[0], lengths):
+        grey = att.detach().cpu()[:n]
+        images.append(grey.unsqueeze(0).expand(3, -1, -1).contiguous())
+    return images
 
 
 _PHN_REDUCE = {
@@ -182,9 +189,10 @@ def collapse_phn(seq):
 
 
 def trim_eos(seqence):
-    new_pred = []
-    for char in seqence:
-        new_pred.append(int(char))
-        if char == 1:
+    """ints of `seqence` up to and including the first <eos> (= 1) (postprocess.py:171-177)."""
+    out = []
+    for tok in seqence:
+        out.append(int(tok))
+        if out[-1] == 1:
             break
-    return new_pred
+    return out
