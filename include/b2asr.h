@@ -11,9 +11,17 @@
  *   - plain C types only: device pointers, sizes, strides (in ELEMENTS) and a
  *     CUDA stream handle passed as void* (cudaStream_t).  No torch types.
  *   - the caller owns every buffer (inputs, outputs, workspace); the library
- *     never allocates or frees device memory and keeps no global device state.
- *   - every launch is stream-ordered on `stream`, performs no host
- *     synchronisation and is CUDA-graph capturable.
+ *     never calls cudaMalloc / cudaFree.  What it does keep, per device and
+ *     created on first use: one cuBLAS handle (csrc/decloop.cu; cuBLAS owns a
+ *     workspace; used only when the fused decoder-step kernels do not take a
+ *     shape or B2ASR_DEC_STEP=0), one extra CUDA stream + two events for the
+ *     CTC call's overlapped schedule (csrc/ctc.cu) and one for the decode
+ *     loop's LM chain (csrc/decode.cu), the 32 MiB static workspace of
+ *     b2asr_ctc_loss_fwd_bwd_static, and two small debug-trace arrays.
+ *   - every launch is stream-ordered on `stream` (work forked to the
+ *     library's own stream is joined back before the call returns control of
+ *     `stream`) and performs no host synchronisation.  Calls that use neither
+ *     cuBLAS nor the first-use creation above are CUDA-graph capturable.
  *   - return value: 0 on success, negative B2ASR_E* on failure;
  *     b2asr_last_error() returns a thread-local message.  Nothing throws.
  *   - all floating point buffers are IEEE fp32 unless noted.
