@@ -604,6 +604,38 @@ def run_native(args):
                     "frac": k["achieved_gbs"] / peak, "traffic": traffic, "peak_source": how,
                     "share_of_step": k["ms_per_step"] / ms_step, "note": note}
 
+    # ---- data-parallel breakdown (N > 1): where the step time goes on every rank -----------------------------
+    # CUDA events on each rank: step start -> all-reduce start = that rank's own compute; the all-reduce interval =
+    # transfer + waiting for the slowest rank (the NCCL kernel spins until every peer has arrived).
+    dp = None
+    if world > 1:
+        ts.grads.timeline = []
+        marks = []
+        barrier()
+        for i in range(min(args.steps, 5)):
+            e0, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            step_resident(i)
+            e2.record()
+            marks.append((e0, e2))
+        torch.cuda.synchronize()
+        rows = []
+        for (e0, e2), (a0, a1) in zip(marks, ts.grads.timeline):
+            rows.append([e0.elapsed_time(a0), a0.elapsed_time(a1), a1.elapsed_time(e2)])
+        ts.grads.timeline = None
+        mine = torch.tensor(rows, device=dev).mean(0)                    # [compute, allreduce, tail] ms on this rank
+        allr = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+        if rank == 0:
+            comp = [float(v[0]) for v in allr]
+            ar = [float(v[1]) for v in allr]
+            dp = {"compute_ms_per_rank": [round(v, 2) for v in comp], "allreduce_ms_per_rank": [round(v, 2) for v in ar],
+                  "tail_ms_per_rank": [round(float(v[2]), 2) for v in allr],
+                  "compute_ms_spread": round(max(comp) - min(comp), 2), "allreduce_ms_min": round(min(ar), 2),
+                  "gradient_mb": ts.grads.flat.numel() * 4 / 1e6,
+                  "note": "per rank: step start -> all-reduce start (own forward+backward on its own batch), the NCCL "
+                          "all-reduce interval (transfer + wait for the slowest rank; its minimum over ranks is the "
+                          "transfer itself), all-reduce end -> step end (norm + clipped optimizer launch)"}
     del ts, opt, model, resident
     torch.cuda.empty_cache()
     workloads, ctc_m5, stock = None, None, None
@@ -637,7 +669,7 @@ def run_native(args):
             "e2e": {"value": e2e_value, "unit": "utterances/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h[0], "ms_per_step": ms_e2e / args.steps},
             "roofline": roofline, "kernels": kernels, "cpu_baseline": cpu_baseline, "stock_torch_gpu": stock,
-            "workloads": workloads, "ctc_m5": ctc_m5, "decode": decode,
+            "workloads": workloads, "ctc_m5": ctc_m5, "decode": decode, "dp_breakdown": dp,
         }
         print(json.dumps(out), flush=True)
     if world > 1:

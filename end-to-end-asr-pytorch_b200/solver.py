@@ -66,6 +66,7 @@ class FlatGradients:
             n += (p.numel() + 3) // 4 * 4
         dev = self.params[0].device
         self.flat = torch.zeros(n, dtype=torch.float32, device=dev)
+        self.timeline = None                    # list -> allreduce_sum appends (start, end) CUDA events
         self.rebind()
 
     def rebind(self):
@@ -80,7 +81,14 @@ class FlatGradients:
         """-> world size; the flat buffer then holds the SUM over ranks (the 1/world goes into the clip coefficient)."""
         import torch.distributed as dist
         if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+            rec = self.timeline
+            if rec is not None:                 # bench.py's data-parallel breakdown: events around the collective
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
             dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group)
+            if rec is not None:
+                e1.record()
+                rec.append((e0, e1))
             return dist.get_world_size(group)
         return 1
 
