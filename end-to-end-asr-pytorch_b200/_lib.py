@@ -12,7 +12,8 @@ import re
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libb2asr.so")
+# B2ASR_LIB: another build of the same library (A/B experiments with tools/keys_variants.sh); default the in-tree one
+LIB_PATH = os.environ.get("B2ASR_LIB") or os.path.join(_HERE, "csrc", "libb2asr.so")
 HEADER_PATH = os.path.join(_HERE, "..", "include", "b2asr.h")
 
 _lib = None

@@ -14,6 +14,8 @@
 // canonical K-major no-swizzle UMMA layout, then fence.proxy.async); three 37 KB stages and register double
 // buffering of the global loads, two CTAs per SM; tcgen05.commit on an mbarrier releases a stage.  Epilogue:
 // tcgen05.ld (32 lanes x 16 columns per warp), + bias, accurate tanh, 64-byte stores per thread.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace b2asr {
@@ -224,6 +226,10 @@ __global__ void __launch_bounds__(kKeysNT, 2) attn_keys_kernel(KeysArgs p) {
 
 }  // namespace b2asr
 
+namespace b2asr {
+int attn_keys_v2(const float* h, const float* W, const float* bias, float* out, int M, int D, int A, cudaStream_t st);   // keys2.cu
+}
+
 using namespace b2asr;
 
 extern "C" int b2asr_attn_keys(const float* h, const float* W, const float* bias, float* out,
@@ -232,6 +238,13 @@ extern "C" int b2asr_attn_keys(const float* h, const float* W, const float* bias
   B2_REQUIRE(M > 0 && D > 0 && A > 0, B2ASR_EINVAL, "attn_keys: bad sizes M=%d D=%d A=%d", M, D, A);
   B2_REQUIRE(D % 4 == 0 && (((uintptr_t)h | (uintptr_t)W) & 15) == 0, B2ASR_EUNSUPPORTED,
              "attn_keys: D=%d must be a multiple of 4 and h/W 16-byte aligned", D);
+  // second generation (keys2.cu: TMA tensor copies, warp-specialised persistent pipeline); B2ASR_KEYS=v1 keeps the
+  // first one, which also takes over when the driver cannot encode tensor maps
+  static const bool v1 = [] { const char* e = getenv("B2ASR_KEYS"); return e && e[0] == 'v' && e[1] == '1'; }();
+  if (!v1) {
+    const int rc = attn_keys_v2(h, W, bias, out, M, D, A, (cudaStream_t)stream);
+    if (rc != B2ASR_EUNSUPPORTED) return rc;
+  }
   KeysArgs a;
   a.h = h; a.W = W; a.bias = bias; a.out = out; a.M = M; a.D = D; a.A = A;
   const int ntiles = (A + kBNmax - 1) / kBNmax;
