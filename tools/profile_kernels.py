@@ -1,0 +1,68 @@
+"""One launch of each hot-path kernel at its SURVEY.md section 8d shape between cudaProfilerStart/Stop, for ONE
+`ncu --profile-from-start off --set full` capture (key projection M2, CTC M5 (1000,150) rows / lattice / occupancy,
+attention step forward / backward M2).  Run with B2ASR_CTC_OVERLAP=0: under ncu kernels are serialised, and the
+overlapped CTC schedules wait for each other across streams.
+usage: B2ASR_CTC_OVERLAP=0 python tools/profile_kernels.py"""
+import importlib
+import os
+import sys
+
+import torch
+
+os.environ.setdefault("B2ASR_CTC_OVERLAP", "0")
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+PKG = "end-to-end-asr-pytorch_b200"
+ctc, keys, attn = (importlib.import_module(PKG + "." + m) for m in ("ctc", "_keys", "_attn"))
+dev = torch.device("cuda:0")
+g = torch.Generator().manual_seed(0)
+
+# key projection, M2
+h = torch.randn(32, 400, 640, device=dev)
+w = torch.randn(300, 640, device=dev) * 640 ** -0.5
+b = torch.randn(300, device=dev)
+
+# CTC, M5 (T'=1000, L=150)
+B, T, L, V = 64, 1000, 150, 5000
+x = torch.randn(B, T, V, device=dev).requires_grad_(True)
+il = torch.randint(int(0.6 * T), T + 1, (B,), generator=g); il[0] = T
+tl = torch.randint(L // 2, L + 1, (B,), generator=g); tl[0] = L
+y = torch.randint(1, V, (B, L), generator=g)
+for i in range(B):
+    y[i, tl[i]:] = 0
+yd, tld, ild = y.to(dev), tl.to(dev), il.to(dev)
+
+# attention step, M2
+Ba, Ta, D, A, dec = 32, 400, 640, 300, 320
+ha = torch.randn(Ba, Ta, D, device=dev)
+ka = torch.tanh(torch.randn(Ba, Ta, A, device=dev))
+lens = attn.lens_i32([Ta] * Ba, dev)
+s = torch.randn(Ba, dec, device=dev)
+W = dict(phi=torch.randn(A, dec, generator=g) * dec ** -0.5, conv=torch.randn(10, 1, 201, generator=g) * 201 ** -0.5,
+         lproj=torch.randn(A, 10, generator=g) * 10 ** -0.5, gw=torch.randn(1, A, generator=g) * A ** -0.5, gb=torch.zeros(1))
+W = {k: v.to(dev) for k, v in W.items()}
+prev = torch.softmax(torch.randn(Ba, Ta, device=dev), -1)
+dk = torch.zeros(Ba, Ta, A, device=dev)
+pg = torch.zeros(attn.num_slots(Ba, Ta, D, A, dec, "loc", 10, 100), attn.pgrad_layout(A, 10, 100)[-1], device=dev)
+dctx, datt = torch.randn(Ba, D, device=dev), torch.randn(Ba, Ta, device=dev) * 0.01
+
+
+def once():
+    keys.project(h, w, b)
+    x.grad = None
+    ctc.ctc_loss(x, yd, ild, tld, from_logits=True, batch_first=True).backward()
+    att, ctx, q = attn.step_forward("loc", s, W["phi"], ka, ha, lens, prev, W["conv"], W["lproj"], W["gw"], W["gb"], 2.0, want_q=True)
+    attn.step_backward("loc", W["phi"], ka, ha, lens, prev, W["conv"], W["lproj"], W["gw"], 2.0, q, att, dctx, datt, dk, pg, dec)
+
+
+for _ in range(2):
+    once()
+torch.cuda.synchronize()
+flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+flush.zero_()                                  # inputs out of L2 before the profiled pass
+torch.cuda.synchronize()
+torch.cuda.cudart().cudaProfilerStart()
+once()
+torch.cuda.synchronize()
+torch.cuda.cudart().cudaProfilerStop()
+print("ok")
