@@ -15,7 +15,7 @@ import os
 
 import torch
 
-from . import _lib
+from . import _gemm, _lib
 
 _status = {}
 
@@ -149,7 +149,7 @@ class LstmSeq(torch.autograd.Function):
         H = w_hh[0].shape[1]
         dev = x.device
         w_cat = torch.cat(w_ih, 0) if nd > 1 else w_ih[0].contiguous()               # [ND*4H, in]
-        gates = torch.mm(x.view(B * T, n_in), w_cat.t()).view(B, T, nd, 4 * H)       # activations in place below
+        gates = _gemm.mm_tn(x.view(B * T, n_in), w_cat).view(B, T, nd, 4 * H)        # activations in place below
         out = torch.empty(B, T, nd * H, dtype=torch.float32, device=dev)
         cells = torch.empty(B, T, nd, H, dtype=torch.float32, device=dev)
         io = _descr(B, T, H, nd, gates, w_hh, b_ih, b_hh, lens, cells, dev)
@@ -222,10 +222,10 @@ class LstmSeq(torch.autograd.Function):
             if not _join_queued[0]:
                 torch.autograd.Variable._execution_engine.queue_callback(_join)
                 _join_queued[0] = True
-            g_x = dG2.mm(w_cat).view(B, T, n_in) if need[0] else None
+            g_x = _gemm.mm_tn(dG2, w_cat.t().contiguous()).view(B, T, n_in) if need[0] else None
             ctx.keep = None
             return (g_x, None, None) + (None,) * len(params)
-        g_x = dG2.mm(w_cat).view(B, T, n_in) if need[0] else None
+        g_x = _gemm.mm_tn(dG2, w_cat.t().contiguous()).view(B, T, n_in) if need[0] else None
         grads = weight_grads()
         ctx.keep = None
         return (g_x, None, None, *grads)

@@ -1,0 +1,33 @@
+"""Dense products next to the Listener recurrence (reference src/asr.py:466-501: nn.LSTM's input projection and its
+input gradient) on the tcgen05 pipeline of csrc/keys2.cu instead of cuBLAS's fp32 SIMT kernels.
+
+    mm_tn(a, b, bias)   a [M,K] . b[N,K]^T (+ bias[N])  ->  [M,N]      (torch.nn.functional.linear's operand form)
+
+Error-compensated TF32 (three tensor-core products per algorithmic one, fp32 accumulation in tensor memory): the max
+abs error against float64 is ~2x cuBLAS fp32's (tests/test_gemm_gpu.py), far inside the 1e-4 parity bar, at about three
+times the SIMT kernels' rate.  Shapes the tensor copies cannot address (K % 4 != 0, unaligned views) take the library
+GEMM; B2ASR_GEMM=cublas selects the library everywhere (A/B runs).
+"""
+import os
+
+import torch
+
+from . import _lib
+
+ENABLED = os.environ.get("B2ASR_GEMM", "tcgen05") != "cublas"
+MIN_WORK = 1 << 22            # M*N*K below which a library GEMM launch is as good (tiny test shapes, decoder steps)
+
+
+def mm_tn(a, b, bias=None):
+    M, K = a.shape
+    N = b.shape[0]
+    if (ENABLED and a.is_cuda and a.dtype == torch.float32 and b.dtype == torch.float32 and K % 4 == 0
+            and M * N * K >= MIN_WORK and a.is_contiguous() and b.is_contiguous()
+            and a.data_ptr() % 16 == 0 and b.data_ptr() % 16 == 0):
+        out = torch.empty(M, N, dtype=torch.float32, device=a.device)
+        if bias is not None:
+            bias = bias.contiguous()
+        _lib.call("b2asr_gemm_tn_3xtf32", 1, _lib.lib().b2asr_gemm_tn_3xtf32, a.data_ptr(), b.data_ptr(), _lib.ptr(bias),
+                  out.data_ptr(), M, N, K, _lib.stream_ptr())
+        return out
+    return torch.nn.functional.linear(a, b, bias)

@@ -99,6 +99,7 @@ class ParamChunk(ctypes.Structure):
 # name -> (restype, argtypes); must list every symbol include/b2asr.h declares.
 _SIGNATURES = {
     "b2asr_attn_keys": (c_i, [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_p]),
+    "b2asr_gemm_tn_3xtf32": (c_i, [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_p]),
     "b2asr_ctc_prefix_init": (c_i, [c_p, c_i, c_i, c_i, c_p, c_p]),
     "b2asr_ctc_prefix_score": (c_i, [c_p, c_i, c_i, c_i, c_i, c_p, c_p, c_i, c_p, c_p, c_p]),
     "b2asr_beam_io_size": (c_sz, []),

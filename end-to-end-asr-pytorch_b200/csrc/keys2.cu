@@ -148,6 +148,8 @@ __device__ __forceinline__ float lo_half(float x) {
   return x - __uint_as_float(__float_as_uint(x) & 0xffffe000u);
 }
 
+// TANH: epilogue tanh (the key projection); otherwise the plain product + optional bias (Listener projections)
+template <bool TANH>
 __global__ void __launch_bounds__(kNT, 1) attn_keys2_kernel(const __grid_constant__ CUtensorMap map_h,
                                                             const __grid_constant__ CUtensorMap map_w, Keys2Args p) {
   extern __shared__ unsigned char smraw[];
@@ -321,7 +323,7 @@ __global__ void __launch_bounds__(kNT, 1) attn_keys2_kernel(const __grid_constan
       const int m0 = (t / p.n_ntiles) * kBM, n0 = (t % p.n_ntiles) * kBN + ch * kEC;
       float* bias_w = bias_sm[warp - 2 - kConvWarps];
       __syncwarp();
-      for (int i = lane; i < kEC; i += 32) bias_w[i] = n0 + i < p.A ? __ldg(p.bias + n0 + i) : 0.f;
+      for (int i = lane; i < kEC; i += 32) bias_w[i] = (p.bias && n0 + i < p.A) ? __ldg(p.bias + n0 + i) : 0.f;
       __syncwarp();
       mbar_wait_sleep(&acc_full, j & 1u);
       tc_fence_after();
@@ -363,8 +365,8 @@ __global__ void __launch_bounds__(kNT, 1) attn_keys2_kernel(const __grid_constan
         for (int c0 = 0; c0 < kEC; c0 += 4) {
           float v[4];
           const float4 bq = *reinterpret_cast<const float4*>(bias_w + c0);
-          v[0] = tanh_fast(r[c0 + 0] + bq.x); v[1] = tanh_fast(r[c0 + 1] + bq.y);
-          v[2] = tanh_fast(r[c0 + 2] + bq.z); v[3] = tanh_fast(r[c0 + 3] + bq.w);
+          v[0] = r[c0 + 0] + bq.x; v[1] = r[c0 + 1] + bq.y; v[2] = r[c0 + 2] + bq.z; v[3] = r[c0 + 3] + bq.w;
+          if (TANH) { v[0] = tanh_fast(v[0]); v[1] = tanh_fast(v[1]); v[2] = tanh_fast(v[2]); v[3] = tanh_fast(v[3]); }
           if (vec && n0 + c0 + 4 <= p.A) *reinterpret_cast<float4*>(o + c0) = make_float4(v[0], v[1], v[2], v[3]);
           else {
 #pragma unroll
@@ -413,9 +415,11 @@ int make_map(CUtensorMap* map, const float* base, int rows, int cols, int box_ro
 
 }  // namespace
 
-// -> B2ASR_OK, or an error; B2ASR_EUNSUPPORTED lets the caller take the first-generation kernel
-int attn_keys_v2(const float* h, const float* W, const float* bias, float* out, int M, int D, int A, cudaStream_t st) {
-  // tensor copies want 16-byte aligned bases and row pitches; anything else goes to the first-generation kernel
+// out[M,A] = act(h[M,D] . W[A,D]^T + bias); -> B2ASR_OK, or an error; B2ASR_EUNSUPPORTED = operands the tensor copies
+// cannot address (the caller takes another route)
+int gemm3x_tn(const float* h, const float* W, const float* bias, float* out, int M, int D, int A, bool tanh_act,
+              cudaStream_t st) {
+  // tensor copies want 16-byte aligned bases and row pitches
   if ((D & 3) || ((reinterpret_cast<uintptr_t>(h) | reinterpret_cast<uintptr_t>(W)) & 15)) return B2ASR_EUNSUPPORTED;
   CUtensorMap map_h, map_w;
   if (int rc = make_map(&map_h, h, M, D, kBM)) return rc;
@@ -433,14 +437,21 @@ int attn_keys_v2(const float* h, const float* W, const float* bias, float* out, 
   int dev = 0, sms = 0;
   B2_CUDA_TRY(cudaGetDevice(&dev));
   if (!configured[dev & 63]) {
-    B2_CUDA_TRY(cudaFuncSetAttribute(attn_keys2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    B2_CUDA_TRY(cudaFuncSetAttribute(attn_keys2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    B2_CUDA_TRY(cudaFuncSetAttribute(attn_keys2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured[dev & 63] = true;
   }
   B2_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  const int tiles = a.n_mtiles * a.n_ntiles;
-  attn_keys2_kernel<<<tiles < sms ? tiles : sms, kNT, smem, st>>>(map_h, map_w, a);
+  const long long tiles = (long long)a.n_mtiles * a.n_ntiles;
+  const int grid = (int)(tiles < sms ? tiles : sms);
+  if (tanh_act) attn_keys2_kernel<true><<<grid, kNT, smem, st>>>(map_h, map_w, a);
+  else attn_keys2_kernel<false><<<grid, kNT, smem, st>>>(map_h, map_w, a);
   B2_CUDA_TRY(cudaGetLastError());
   return B2ASR_OK;
+}
+
+int attn_keys_v2(const float* h, const float* W, const float* bias, float* out, int M, int D, int A, cudaStream_t st) {
+  return gemm3x_tn(h, W, bias, out, M, D, A, true, st);
 }
 
 }  // namespace b2asr
@@ -450,3 +461,12 @@ extern "C" int b2asr_keys_trace(long long* host64) {
   return cudaMemcpyFromSymbol(host64, b2asr::g_keys_trace, 64 * sizeof(long long)) == cudaSuccess ? 0 : -1;
 }
 #endif
+
+// Plain product on the same pipeline: c[M,N] = a[M,K] . b[N,K]^T (+ bias[N]); see include/b2asr.h
+extern "C" int b2asr_gemm_tn_3xtf32(const float* a, const float* b, const float* bias, float* c, int M, int N, int K,
+                                    void* stream) {
+  using namespace b2asr;
+  B2_REQUIRE(a && b && c, B2ASR_EINVAL, "b2asr_gemm_tn_3xtf32: null pointer");
+  B2_REQUIRE(M > 0 && N > 0 && K > 0, B2ASR_EINVAL, "b2asr_gemm_tn_3xtf32: M=%d N=%d K=%d", M, N, K);
+  return gemm3x_tn(a, b, bias, c, M, K, N, false, (cudaStream_t)stream);
+}

@@ -117,6 +117,13 @@ int b2asr_rescale_if_needed(float* buf, int64_t n, const float* upstream, float 
 int b2asr_attn_keys(const float* h, const float* W, const float* bias, float* out,
                     int M, int D, int A, void* stream);
 
+/* The same tensor-core pipeline without the tanh: c[M,N] = a[M,K] . b[N,K]^T (+ bias[N], may be NULL), all row-major
+ * and contiguous, fp32 in and out, error-compensated TF32 (max abs error ~2x cuBLAS fp32's on O(1) results).
+ * Replaces the dense products around the Listener recurrence, reference src/asr.py:466-501 (nn.LSTM's input
+ * projection x W_ih^T and, in backward, dG W_ih).  Returns B2ASR_EUNSUPPORTED (nothing launched) when K % 4 != 0 or
+ * a / b are not 16-byte aligned: the caller then uses a library GEMM. */
+int b2asr_gemm_tn_3xtf32(const float* a, const float* b, const float* bias, float* c, int M, int N, int K, void* stream);
+
 /* ------------------------------------------------------------------------
  * Kernel group (2b): one decoder step of Attention.forward, reference
  * src/asr.py:410-462 (query projection :422, location conv + projection :452,

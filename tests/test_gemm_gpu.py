@@ -1,0 +1,59 @@
+"""b2asr_gemm_tn_3xtf32 (csrc/keys2.cu: the key projection's tcgen05 pipeline without the tanh) against float64.
+
+Tolerance: the Listener products feed kernels held to 1e-4 relative; here |got - ref| <= 2e-5 * (1 + |ref|) with
+operands scaled so that results are O(1) -- cuBLAS fp32 itself is at ~2.5e-6 there, one TF32 pass at ~1.5e-3."""
+import importlib
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def cuda():
+    if not torch.cuda.is_available():
+        pytest.skip("needs a GPU")
+    return torch.device("cuda:0")
+
+
+def _gemm():
+    return importlib.import_module("end-to-end-asr-pytorch_b200._gemm")
+
+
+@pytest.mark.parametrize("M,N,K,bias", [(12800, 2560, 640, False), (51200, 2560, 120, False), (12800, 640, 2560, False),
+                                        (1000, 336, 100, True), (129, 81, 36, True), (128, 80, 32, False),
+                                        (4096, 2560, 640, True)])
+def test_gemm_matches_float64(cuda, M, N, K, bias):
+    g = torch.Generator().manual_seed(M + N + K)
+    a = torch.randn(M, K, generator=g).to(cuda)
+    b = (torch.randn(N, K, generator=g) * K ** -0.5).to(cuda)
+    c = (torch.randn(N, generator=g) * 0.1).to(cuda) if bias else None
+    mod = _gemm()
+    assert mod.ENABLED
+    old, mod.MIN_WORK = mod.MIN_WORK, 0
+    try:
+        got = mod.mm_tn(a, b, c)
+    finally:
+        mod.MIN_WORK = old
+    ref = a.double() @ b.double().t()
+    if bias:
+        ref = ref + c.double()
+    flag = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    lib32 = torch.nn.functional.linear(a, b, c)
+    torch.backends.cuda.matmul.allow_tf32 = flag
+    err = float((got.double() - ref).abs().max())
+    print("M=%d N=%d K=%d: max abs err %.2e (cuBLAS fp32 %.2e)" % (M, N, K, err, float((lib32.double() - ref).abs().max())))
+    assert float(((got.double() - ref).abs() / (1 + ref.abs())).max()) <= 2e-5
+
+
+def test_gemm_unsupported_shapes_take_the_library(cuda):
+    mod = _gemm()
+    a = torch.randn(300, 30, device=cuda)          # K % 4 != 0
+    b = torch.randn(50, 30, device=cuda)
+    got = mod.mm_tn(a, b)
+    assert torch.allclose(got, a @ b.t(), atol=1e-5)
+    a2 = torch.randn(300, 33, device=cuda)[:, 1:]  # unaligned, non-contiguous view
+    got = mod.mm_tn(a2, torch.randn(50, 32, device=cuda))
+    assert got.shape == (300, 50)
