@@ -75,7 +75,7 @@ def _flush(device, after=None):
         side.wait_event(after)
     with torch.cuda.stream(side):
         for fn in work:
-            fn(side)
+            fn(side, after is not None)         # after: the work runs next to the recurrence launched behind that event
 
 
 def _join():
@@ -183,17 +183,29 @@ class LstmSeq(torch.autograd.Function):
         params = ctx.params
         has_bias = ctx.has_bias
 
-        def weight_grads():
-            g_wcat = dG2.t().mm(x.view(B * T, n_in))                                  # [ND*4H, in]
+        def weight_grads(max_ctas=0):
+            """max_ctas > 0: the products share the device with a recurrence kernel and take at most that many SMs."""
+            x2, out2 = x.view(B * T, n_in), out.view(B * T, nd * H)
+            g_wcat = _gemm.mm_nt(dG2, x2, max_ctas=max_ctas)                          # [ND*4H, in]
+            if g_wcat is None:
+                g_wcat = dG2.t().mm(x2)
             g_b = dG2.sum(0)
             grads = []
             for d in range(nd):
                 g_wih = g_wcat[d * 4 * H:(d + 1) * 4 * H]
                 if T > 1:
-                    # h_{t-1} of the forward walk is out[:, t-1, :H]; of the reverse walk out[:, t+1, H:]
-                    dg = d_gates[:, 1:, d] if d == 0 else d_gates[:, :T - 1, d]       # [B,T-1,4H] strided
-                    hp = out[:, :T - 1, d * H:(d + 1) * H] if d == 0 else out[:, 1:, d * H:(d + 1) * H]
-                    g_whh = torch.bmm(dg.transpose(1, 2), hp).sum(0)
+                    # h_{t-1} of the forward walk is out[:, t-1, :H]; of the reverse walk out[:, t+1, H:].  Over the
+                    # flattened [B*T] rows that pairs row r with row r+1 (a view offset); the rows that would pair two
+                    # utterances (r % T == T-1) are excluded inside the kernel.
+                    if d == 0:
+                        a2, b2 = dG2[1:, :4 * H], out2[:-1, :H]
+                    else:
+                        a2, b2 = dG2[:-1, d * 4 * H:(d + 1) * 4 * H], out2[1:, d * H:(d + 1) * H]
+                    g_whh = _gemm.mm_nt(a2, b2, period=T, max_ctas=max_ctas)
+                    if g_whh is None:
+                        dg = d_gates[:, 1:, d] if d == 0 else d_gates[:, :T - 1, d]   # [B,T-1,4H] strided
+                        hp = out[:, :T - 1, d * H:(d + 1) * H] if d == 0 else out[:, 1:, d * H:(d + 1) * H]
+                        g_whh = torch.bmm(dg.transpose(1, 2), hp).sum(0)
                 else:
                     g_whh = torch.zeros_like(w_hh[d])
                 g_bias = g_b[d * 4 * H:(d + 1) * 4 * H]
@@ -206,11 +218,11 @@ class LstmSeq(torch.autograd.Function):
             ready.record()                                  # d_gates complete (this stream)
             _flush(dev, before)                             # upper layers' weight gradients run next to THIS recurrence
 
-            def work(side):
+            def work(side, shared):
                 side.wait_event(ready)
                 for t in (d_gates, x, out):
                     t.record_stream(side)
-                for p, g in zip(params, weight_grads()):
+                for p, g in zip(params, weight_grads(_gemm.SIDE_CTAS if shared else 0)):
                     if p is None or g is None:
                         continue
                     if p.grad is None:

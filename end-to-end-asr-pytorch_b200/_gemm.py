@@ -15,6 +15,9 @@ import torch
 from . import _lib
 
 ENABLED = os.environ.get("B2ASR_GEMM", "tcgen05") != "cublas"
+# SMs a weight-gradient product may take while a Listener recurrence kernel (96 of the 148 SMs at the shipped shapes)
+# runs next to it; a persistent grid wider than the free SMs would make the recurrence's clusters wait for it
+SIDE_CTAS = int(os.environ.get("B2ASR_SIDE_CTAS", "52"))
 MIN_WORK = 1 << 22            # M*N*K below which a library GEMM launch is as good (tiny test shapes, decoder steps)
 
 
@@ -31,3 +34,22 @@ def mm_tn(a, b, bias=None):
                   out.data_ptr(), M, N, K, _lib.stream_ptr())
         return out
     return torch.nn.functional.linear(a, b, bias)
+
+
+def mm_nt(a, b, period=0, max_ctas=0):
+    """a [Kr,Ma], b [Kr,Nb] (row-major views, unit column stride) -> a^T b [Ma,Nb], the reduction over the rows; rows
+    with index % period == period - 1 do not count (see include/b2asr.h).  Returns None when the tensor-core kernel
+    does not take the operands (the caller then uses its library route)."""
+    Kr, Ma = a.shape
+    Nb = b.shape[1]
+    if not (ENABLED and a.is_cuda and a.dtype == torch.float32 and b.dtype == torch.float32 and b.shape[0] == Kr
+            and a.stride(1) == 1 and b.stride(1) == 1 and a.stride(0) % 4 == 0 and b.stride(0) % 4 == 0
+            and a.data_ptr() % 16 == 0 and b.data_ptr() % 16 == 0 and (period == 0 or period >= 32)
+            and Kr * Ma * Nb >= MIN_WORK):
+        return None
+    L = _lib.lib()
+    S = L.b2asr_gemm_nt_3xtf32_slices(Ma, Nb, Kr, max_ctas)
+    out = torch.empty(S, Ma, Nb, dtype=torch.float32, device=a.device)
+    _lib.call("b2asr_gemm_nt_3xtf32", 1, L.b2asr_gemm_nt_3xtf32, a.data_ptr(), a.stride(0), b.data_ptr(), b.stride(0),
+              out.data_ptr(), Ma, Nb, Kr, period, S, max_ctas, _lib.stream_ptr())
+    return out[0] if S == 1 else out.sum(0)

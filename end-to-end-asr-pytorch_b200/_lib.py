@@ -100,6 +100,8 @@ class ParamChunk(ctypes.Structure):
 _SIGNATURES = {
     "b2asr_attn_keys": (c_i, [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_p]),
     "b2asr_gemm_tn_3xtf32": (c_i, [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_p]),
+    "b2asr_gemm_nt_3xtf32": (c_i, [c_p, c_i64, c_p, c_i64, c_p, c_i, c_i, c_i64, c_i, c_i, c_i, c_p]),
+    "b2asr_gemm_nt_3xtf32_slices": (c_i, [c_i, c_i, c_i64, c_i]),
     "b2asr_ctc_prefix_init": (c_i, [c_p, c_i, c_i, c_i, c_p, c_p]),
     "b2asr_ctc_prefix_score": (c_i, [c_p, c_i, c_i, c_i, c_i, c_p, c_p, c_i, c_p, c_p, c_p]),
     "b2asr_beam_io_size": (c_sz, []),

@@ -22,16 +22,19 @@
 //                       gradient row as sparse fire-and-forget reductions; entries too small to change the fp32
 //                       gradient are skipped, so only the band of the lattice around the alignments is touched.
 //
-// Overlapped schedule (V > 1024, gradient wanted): the three kernels run CONCURRENTLY, ordered by device flags.
-//   * the rows pass visits the frames in the order the walks consume them -- 16-frame blocks alternately from the
-//     front and from the back of every utterance -- and counts finished rows per block (`rdy`);
-//   * the walks run on a second stream, launched first so their CTAs are resident: a producer warp per CTA waits
-//     for the blocks of the next chunk, then issues its bulk copy; the walks therefore track the HBM stream and
-//     reach the middle of the utterance when the rows pass ends; every PUB frames they publish how far their stored
-//     rows reach (`prog`);
-//   * the occupancy pass follows in the rows pass's stream, frames ordered from the middle outwards, each CTA
-//     waiting until both walks have passed its frames.
-// What is left serial is the second half of the walks (the rows pass cannot feed them faster than HBM delivers).
+// Schedules (B2ASR_CTC_OVERLAP; V > 1024 and gradient wanted, otherwise 0):
+//   0  the three kernels one after the other in the caller's stream;
+//   2  (default) rows pass, then the walks on a second, high-priority stream and the occupancy pass in the caller's
+//      stream CONCURRENTLY: the occupancy pass visits the frames from the middle outwards -- the order in which both
+//      walks have passed them -- and each of its CTAs waits on the walks' published progress (`prog`, device flags);
+//   3  all three concurrently: additionally the rows pass visits the frames in the order the walks consume them
+//      (16-frame blocks alternately from the front and the back) and counts finished rows per block (`rdy`), and a
+//      producer warp per walk CTA waits for the blocks of the next chunk before issuing its bulk copy.  Measured
+//      slower than 2 at every M5 point: next to the HBM-streaming rows pass the walks' one latency-critical warp per
+//      scheduler loses its issue slots, and the rows pass loses bandwidth to the walks' table reads.
+// For 2 and 3 the walk CTAs must be resident before the wide kernels flood the SMs (gate kernel + `started` counter),
+// every kernel is loaded before the first overlapped call (lazy module loading would otherwise synchronise the
+// context under a spinning kernel) and all kernels ask for the maximum shared-memory carve-out so that they co-reside.
 #include "common.cuh"
 #include <atomic>
 #include <mutex>

@@ -124,6 +124,19 @@ int b2asr_attn_keys(const float* h, const float* W, const float* bias, float* ou
  * a / b are not 16-byte aligned: the caller then uses a library GEMM. */
 int b2asr_gemm_tn_3xtf32(const float* a, const float* b, const float* bias, float* c, int M, int N, int K, void* stream);
 
+/* Weight-gradient form on the same pipeline: c[Ma,Nb] = sum_{k < Kr} a[k,0:Ma]^T b[k,0:Nb]; a / b are row-major with
+ * pitch_a / pitch_b floats between rows (views into wider matrices are fine), the reduction runs over the rows.
+ * Replaces what autograd computes for nn.LSTM's weight_ih / weight_hh, reference src/asr.py:466-501 (dW_ih = dG^T x,
+ * dW_hh = sum_t dG_{t+1}^T h_t).  period != 0: rows with k % period == period - 1 do not count (the dW_hh pairing of
+ * row r with row r + 1 is a pointer offset; pairs straddling two utterances of `period` frames are excluded); period
+ * must be 0 or >= 32.  slices >= 1 = split-K: c holds `slices` partial products [slices][Ma][Nb] which the caller adds
+ * (b2asr_gemm_nt_3xtf32_slices proposes a count).  max_ctas > 0 caps the persistent grid (a launch that shares the
+ * device with another persistent kernel).  Returns B2ASR_EUNSUPPORTED (nothing launched) for pitches that are not
+ * multiples of 4 floats, bases that are not 16-byte aligned, or 0 < period < 32. */
+int b2asr_gemm_nt_3xtf32(const float* a, long long pitch_a, const float* b, long long pitch_b, float* c, int Ma, int Nb,
+                         long long Kr, int period, int slices, int max_ctas, void* stream);
+int b2asr_gemm_nt_3xtf32_slices(int Ma, int Nb, long long Kr, int max_ctas);
+
 /* ------------------------------------------------------------------------
  * Kernel group (2b): one decoder step of Attention.forward, reference
  * src/asr.py:410-462 (query projection :422, location conv + projection :452,

@@ -57,3 +57,63 @@ def test_gemm_unsupported_shapes_take_the_library(cuda):
     a2 = torch.randn(300, 33, device=cuda)[:, 1:]  # unaligned, non-contiguous view
     got = mod.mm_tn(a2, torch.randn(50, 32, device=cuda))
     assert got.shape == (300, 50)
+
+
+@pytest.mark.parametrize("Kr,Ma,Nb", [(12800, 2560, 640), (51200, 2560, 120), (4000, 1280, 320), (1000, 132, 72), (96, 128, 64)])
+def test_gemm_nt_matches_float64(cuda, Kr, Ma, Nb):
+    """weight-gradient form: a^T b with the reduction over the rows of both operands"""
+    g = torch.Generator().manual_seed(Kr + Ma + Nb)
+    a = (torch.randn(Kr, Ma, generator=g) * Kr ** -0.5).to(cuda)
+    b = torch.randn(Kr, Nb, generator=g).to(cuda)
+    mod = _gemm()
+    old, mod.MIN_WORK = mod.MIN_WORK, 0
+    try:
+        got = mod.mm_nt(a, b)
+    finally:
+        mod.MIN_WORK = old
+    assert got is not None and got.shape == (Ma, Nb)
+    ref = a.double().t() @ b.double()
+    flag = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    lib32 = a.t().mm(b)
+    torch.backends.cuda.matmul.allow_tf32 = flag
+    err = float((got.double() - ref).abs().max())
+    print("Kr=%d Ma=%d Nb=%d: max abs err %.2e (cuBLAS fp32 %.2e)" % (Kr, Ma, Nb, err, float((lib32.double() - ref).abs().max())))
+    assert float(((got.double() - ref).abs() / (1 + ref.abs())).max()) <= 2e-5
+
+
+@pytest.mark.parametrize("B,T,H,nd", [(32, 400, 320, 2), (5, 37, 64, 2), (3, 100, 32, 1)])
+def test_gemm_nt_shifted_views_with_utterance_mask(cuda, B, T, H, nd):
+    """dW_hh = sum_b sum_t dG[b,t+1]^T h[b,t] (forward direction) and dG[b,t]^T h[b,t+1] (reverse) from strided views
+    of the [B,T,nd,4H] gate gradients and the [B,T,nd*H] outputs, rows that pair two utterances excluded."""
+    g = torch.Generator().manual_seed(B * T + H)
+    dG = (torch.randn(B, T, nd, 4 * H, generator=g) * (B * T) ** -0.5).to(cuda)
+    out = torch.randn(B, T, nd * H, generator=g).to(cuda)
+    dG2, out2 = dG.view(B * T, nd * 4 * H), out.view(B * T, nd * H)
+    mod = _gemm()
+    old, mod.MIN_WORK = mod.MIN_WORK, 0
+    try:
+        for d in range(nd):
+            if d == 0:
+                a, b = dG2[1:, :4 * H], out2[:-1, :H]
+                ref = torch.bmm(dG[:, 1:, 0].double().transpose(1, 2), out[:, :T - 1, :H].double()).sum(0)
+            else:
+                a, b = dG2[:-1, 4 * H:], out2[1:, H:]
+                ref = torch.bmm(dG[:, :T - 1, 1].double().transpose(1, 2), out[:, 1:, H:].double()).sum(0)
+            got = mod.mm_nt(a, b, period=T)
+            assert got is not None
+            assert float(((got.double() - ref).abs() / (1 + ref.abs())).max()) <= 2e-5, (d, float((got.double() - ref).abs().max()))
+    finally:
+        mod.MIN_WORK = old
+
+
+def test_gemm_nt_capped_grid_and_slices_agree(cuda):
+    g = torch.Generator().manual_seed(3)
+    a = (torch.randn(20000, 1280, generator=g) * 0.01).to(cuda)
+    b = torch.randn(20000, 320, generator=g).to(cuda)
+    mod = _gemm()
+    full = mod.mm_nt(a, b)
+    capped = mod.mm_nt(a, b, max_ctas=48)
+    ref = a.double().t() @ b.double()
+    for got in (full, capped):
+        assert float(((got.double() - ref).abs() / (1 + ref.abs())).max()) <= 2e-5
