@@ -18,7 +18,7 @@ import os
 
 import torch
 
-from . import _attn, _lib
+from . import _attn, _gemm, _lib
 
 
 # one SGEMM per step over [ctx_t | h_{t-1}] x [W_ctx | W_hh] instead of two (B2ASR_DEC_CAT=0: the two-GEMM form)
@@ -27,6 +27,13 @@ FUSED_OPERANDS = os.environ.get("B2ASR_DEC_CAT", "1") != "0"
 
 def _p(t):
     return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def _mm_nt(a, b):
+    """a^T b over the rows (weight-gradient form) on the tensor-core pipeline; library GEMM for what it does not take"""
+    a, b = a.contiguous(), b.contiguous()
+    out = _gemm.mm_nt(a, b)
+    return out if out is not None else a.t().mm(b)
 
 
 def _fill(io, **ptrs):
@@ -127,7 +134,7 @@ class DecoderLoop(torch.autograd.Function):
         g_phi = g_conv = g_lproj = g_gw = g_gb = g_wih = g_whh = g_bih = g_bhh = None
         h_prev = torch.cat([h0.unsqueeze(1), hs[:, :L - 1]], dim=1)                               # [B,L,H]: s_t = h_{t-1}
         if wts["w_phi"] is not None and need[6]:
-            g_phi = d_zq.transpose(0, 1).reshape(B * L, A).t().mm(h_prev.reshape(B * L, H))
+            g_phi = _mm_nt(d_zq.transpose(0, 1).reshape(B * L, A), h_prev.reshape(B * L, H))
         if loc:
             o_wl, o_wc, o_wg, o_bg, _ = _attn.pgrad_layout(A, io.C, io.Kw)
             tot = pgrad.sum(0)
@@ -137,16 +144,16 @@ class DecoderLoop(torch.autograd.Function):
             g_gb = tot[o_bg:o_bg + 1]
         dG2 = d_gates.view(B * L, 4 * H)
         if xcat is not None and need[11] and need[12]:
-            g_cat = dG2.t().mm(xcat.transpose(0, 1).reshape(B * L, D + H))          # [4H, D+H] = [dW_ctx | dW_hh]
+            g_cat = _mm_nt(dG2, xcat.transpose(0, 1).reshape(B * L, D + H))         # [4H, D+H] = [dW_ctx | dW_hh]
             g_wih = torch.zeros(4 * H, emb + D, **f32)                 # the embedding half flows through E's own autograd
             g_wih[:, emb:] = g_cat[:, :D]
             g_whh = g_cat[:, D:]
         else:
             if need[11]:
                 g_wih = torch.zeros(4 * H, emb + D, **f32)
-                g_wih[:, emb:] = dG2.t().mm(cvec.transpose(0, 1).reshape(B * L, D))
+                g_wih[:, emb:] = _mm_nt(dG2, cvec.transpose(0, 1).reshape(B * L, D))
             if need[12]:
-                g_whh = dG2.t().mm(h_prev.reshape(B * L, H))
+                g_whh = _mm_nt(dG2, h_prev.reshape(B * L, H))
         if wts["b_ih"] is not None and (need[13] or need[14]):
             g_bih = dG2.sum(0)
             g_bhh = g_bih

@@ -1,12 +1,13 @@
 """Kernel group (2a): key projection K = tanh(h psi^T + b), once per batch (reference asr.py:412-419).
 
-Forward runs on the tcgen05 kernel b2asr_attn_keys (3xTF32 split for fp32-class accuracy); backward is
-two plain library GEMMs around the tanh derivative (cuBLAS, as SURVEY.md section 2 scopes dense GEMMs).
+Forward runs on the tcgen05 kernel b2asr_attn_keys (3xTF32 split for fp32-class accuracy); backward is the tanh
+derivative and two products on the same pipeline (_gemm.mm_tn / mm_nt; library GEMMs for shapes those do not take).
+The Listener's tanh(Linear) after every layer (reference asr.py:313-316) is the same function and uses it too.
 """
 import torch
 import torch.nn.functional as F
 
-from . import _lib
+from . import _gemm, _lib
 
 
 class _KeysFunction(torch.autograd.Function):
@@ -21,8 +22,14 @@ class _KeysFunction(torch.autograd.Function):
         h, w, keys = ctx.saved_tensors
         dz = g * (1.0 - keys * keys)                       # [B,T,A]
         dz2 = dz.reshape(-1, dz.shape[-1])
-        g_h = dz2.mm(w).view_as(h) if ctx.needs_input_grad[0] else None
-        g_w = dz2.t().mm(h.reshape(-1, h.shape[-1])) if ctx.needs_input_grad[1] else None
+        h2 = h.reshape(-1, h.shape[-1])
+        g_h = g_w = None
+        if ctx.needs_input_grad[0]:
+            g_h = _gemm.mm_tn(dz2, w.t().contiguous()).view_as(h)          # dz W
+        if ctx.needs_input_grad[1]:
+            g_w = _gemm.mm_nt(dz2, h2)                                     # dz^T h
+            if g_w is None:
+                g_w = dz2.t().mm(h2)
         g_b = dz2.sum(0) if ctx.needs_input_grad[2] else None
         return g_h, g_w, g_b
 

@@ -28,7 +28,7 @@ import torch.nn.functional as F
 from torch.distributions.categorical import Categorical
 from torch.nn.utils.rnn import pack_padded_sequence, pad_packed_sequence
 
-from . import _attn, _dec, _decloop, _enc, fp32_library_math
+from . import _attn, _dec, _decloop, _enc, _keys, fp32_library_math
 
 CTC_BEAM_RATIO = 1.5   # asr.py:15
 # B2ASR_ENC=cudnn keeps the Listener's LSTMs on the library's per-frame path (A/B measurements only)
@@ -147,7 +147,11 @@ class Listener(nn.Module):
             input_x, enc_len = self.vgg_extractor(input_x, enc_len)
         for l in range(self.num_layers):
             input_x, _, enc_len = getattr(self, 'layer' + str(l))(input_x, state_len=enc_len, pack_input=True)
-            input_x = torch.tanh(getattr(self, 'proj' + str(l))(input_x))
+            proj = getattr(self, 'proj' + str(l))
+            if input_x.is_cuda and input_x.dtype == torch.float32 and ENCODER_NATIVE:
+                input_x = _keys.project(input_x, proj.weight, proj.bias)      # tanh(Linear) on the tcgen05 pipeline
+            else:
+                input_x = torch.tanh(proj(input_x))
         return input_x, enc_len
 
 
