@@ -27,8 +27,8 @@ PKG = "end-to-end-asr-pytorch_b200"
 METRIC = "utterances/sec hybrid CTC-attn train step"
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the kernel that dominates each call (profiles/, M2 shape)
 NCU_DRAM_BYTES = {
-    "b2asr_decoder_loop_bwd": (54.601472e6 + 0.147968e6, "profiles/r01_ncu_attn_bwd_v2.txt attn_step_bwd_kernel"),
-    "b2asr_decoder_loop_fwd": (48.697344e6 + 0.006144e6, "profiles/r01_ncu_attn_fwd_v1.txt attn_step_fwd_kernel"),
+    "b2asr_decoder_loop_bwd": (69.701e6 + 0.915e6, "profiles/r02_ncu_kernels.txt attn_step_bwd_kernel"),
+    "b2asr_decoder_loop_fwd": (48.698e6 + 0.013e6, "profiles/r02_ncu_kernels.txt attn_step_fwd_kernel"),
 }
 WORKLOAD = "libri_m2"
 N_BATCHES = 4                      # distinct synthetic batches rotated through the timed steps
@@ -548,11 +548,14 @@ def run_native(args):
     h2d = host[0][0].numel() * 4 + host[0][1].numel() * 8
 
     # ---- per-kernel timing pass (same steps, CUDA events around every launch of libb2asr.so) -------
+    gemm = pkg("_gemm")
+    flops0 = dict(gemm.FLOPS)
     lib.profile_start()
     prof_steps = min(args.steps, 3)
     for i in range(prof_steps):
         step_resident(i)
     prof = lib.profile_stop()
+    gemm_flops = {k: (gemm.FLOPS[k] - flops0[k]) / prof_steps for k in gemm.FLOPS}
     roofline = None
     kernels = {}
     if prof:
@@ -581,6 +584,11 @@ def run_native(args):
             kernels[name] = {"calls_per_step": calls / prof_steps, "avg_us": per * 1e3,
                              "ms_per_step": tot_ms / prof_steps, "alg_bytes_per_launch": ab,
                              "achieved_gbs": (ab / (per * 1e-3) / 1e9) if per > 0 else None}
+            if name in gemm_flops and tot_ms > 0:
+                # tensor-core products: algorithmic 2MNK per step over the summed launch time (three times that is
+                # issued: error-compensated TF32); the weight-gradient launches share the device with the recurrence
+                kernels[name]["alg_gflop_per_step"] = gemm_flops[name] / 1e9
+                kernels[name]["achieved_tflops"] = gemm_flops[name] / (tot_ms / prof_steps * 1e-3) / 1e12
         top = max(kernels, key=lambda k: kernels[k]["ms_per_step"])
         k = kernels[top]
         note = "M2 keys+features (48 MB) are L2-resident across decoder steps; see DESIGN.md"

@@ -18,6 +18,7 @@ ENABLED = os.environ.get("B2ASR_GEMM", "tcgen05") != "cublas"
 # SMs a weight-gradient product may take while a Listener recurrence kernel (96 of the 148 SMs at the shipped shapes)
 # runs next to it; a persistent grid wider than the free SMs would make the recurrence's clusters wait for it
 SIDE_CTAS = int(os.environ.get("B2ASR_SIDE_CTAS", "52"))
+FLOPS = {"b2asr_gemm_tn_3xtf32": 0.0, "b2asr_gemm_nt_3xtf32": 0.0}    # algorithmic 2*M*N*K issued so far (bench.py reads it)
 MIN_WORK = 1 << 22            # M*N*K below which a library GEMM launch is as good (tiny test shapes, decoder steps)
 
 
@@ -28,6 +29,7 @@ def mm_tn(a, b, bias=None):
             and M * N * K >= MIN_WORK and a.is_contiguous() and b.is_contiguous()
             and a.data_ptr() % 16 == 0 and b.data_ptr() % 16 == 0):
         out = torch.empty(M, N, dtype=torch.float32, device=a.device)
+        FLOPS["b2asr_gemm_tn_3xtf32"] += 2.0 * M * N * K
         if bias is not None:
             bias = bias.contiguous()
         _lib.call("b2asr_gemm_tn_3xtf32", 1, _lib.lib().b2asr_gemm_tn_3xtf32, a.data_ptr(), b.data_ptr(), _lib.ptr(bias),
@@ -50,6 +52,7 @@ def mm_nt(a, b, period=0, max_ctas=0):
     L = _lib.lib()
     S = L.b2asr_gemm_nt_3xtf32_slices(Ma, Nb, Kr, max_ctas)
     out = torch.empty(S, Ma, Nb, dtype=torch.float32, device=a.device)
+    FLOPS["b2asr_gemm_nt_3xtf32"] += 2.0 * Kr * Ma * Nb
     _lib.call("b2asr_gemm_nt_3xtf32", 1, L.b2asr_gemm_nt_3xtf32, a.data_ptr(), a.stride(0), b.data_ptr(), b.stride(0),
               out.data_ptr(), Ma, Nb, Kr, period, S, max_ctas, _lib.stream_ptr())
     return out[0] if S == 1 else out.sum(0)
