@@ -206,6 +206,8 @@ def bench_config(workload, world, n_params=None):
            "feature_dim": w["d_in"], "vocab": w["vocab"], "parallelism": "dp%d" % world,
            "l2": "inputs larger than L2: %d distinct batches rotate and one step touches >1 GB of "
                  "activations (126 MB L2)" % N_BATCHES}
+    if world > 1:
+        cfg["rank_batches"] = "same utterance/label lengths on every rank (fixed work per GPU), different content"
     if n_params is not None:
         cfg["params"] = n_params
     return cfg
@@ -229,7 +231,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": "utterances/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(out), flush=True)
+    emit(json.dumps(out))
 
 
 # ------------------------------------------------------------------------------------------------
@@ -473,8 +475,6 @@ def run_native(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"          # keep NCCL's version banner off stdout: one JSON line only
         dist.init_process_group("nccl", device_id=dev)
     lib = pkg("_lib")
     lib.lib()                                          # fail loudly if libb2asr.so is missing
@@ -492,7 +492,9 @@ def run_native(args):
 
     host = []
     for i in range(N_BATCHES):
-        x, y, lens = syn.make_batch(WORKLOAD, 1234 + rank + 1000 * i)
+        # every rank: the same utterance and label LENGTHS (fixed work per GPU = weak scaling; otherwise the step waits
+        # for whichever rank drew the longest batch), its own content
+        x, y, lens = syn.make_batch(WORKLOAD, 1234 + rank + 1000 * i, shape_seed=1234 + 1000 * i)
         host.append((x.pin_memory(), y.pin_memory(), lens))
     resident = [(x.to(dev), y.to(dev)) for x, y, _ in host]
     B = w["batch"]
@@ -679,12 +681,32 @@ def run_native(args):
             "roofline": roofline, "kernels": kernels, "cpu_baseline": cpu_baseline, "stock_torch_gpu": stock,
             "workloads": workloads, "ctc_m5": ctc_m5, "decode": decode, "dp_breakdown": dp,
         }
-        print(json.dumps(out), flush=True)
+        emit(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
 
 
+_REAL_STDOUT = None
+
+
+def claim_stdout():
+    """ONE JSON line on stdout: libraries print there too (NCCL's version banner comes from C code at communicator
+    set-up), so file descriptor 1 is pointed at stderr for the whole run and the line goes to a saved copy."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit(line):
+    out = _REAL_STDOUT if _REAL_STDOUT is not None else sys.stdout
+    out.write(line + "\n")
+    out.flush()
+
+
 def main():
+    claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)

@@ -36,11 +36,25 @@ WORKLOADS = {
 }
 
 
-def make_batch(workload, seed, batch=None):
+def make_batch(workload, seed, batch=None, shape_seed=None):
     """-> x [B,T,D] fp32 (padded frames exactly 0, no valid frame sums to 0), y [B,Lmax+2] int64
-    (y[:,0]=<sos>=0, tokens in 2..V-1, <eos>=1, right padded 0), frame lengths (sorted descending)."""
+    (y[:,0]=<sos>=0, tokens in 2..V-1, <eos>=1, right padded 0), frame lengths (sorted descending).
+    shape_seed: draw the frame and label LENGTHS from that seed and only the content from `seed` -- data-parallel ranks
+    then hold batches of identical shape (fixed work per GPU: weak scaling) with different content."""
     w = WORKLOADS[workload]
     B = batch or w['batch']
+    if shape_seed is not None and shape_seed != seed:
+        _, y0, lens = make_batch(workload, shape_seed, batch)
+        labs = [int(v) for v in (y0 > 1).sum(-1)]
+        g = torch.Generator().manual_seed(seed)
+        x = torch.randn(B, w['t_hi'], w['d_in'], generator=g)
+        for b, n in enumerate(lens):
+            x[b, n:] = 0
+        y = torch.zeros_like(y0)
+        for b, n in enumerate(labs):
+            y[b, 1:n + 1] = torch.randint(2, w['vocab'], (n,), generator=g)
+            y[b, n + 1] = 1
+        return x, y, lens
     g = torch.Generator().manual_seed(seed)
     T = w['t_hi']
     lens = sorted([int(v) for v in torch.randint(w['t_lo'], T + 1, (B,), generator=g)], reverse=True)
