@@ -257,12 +257,17 @@ extern "C" int b2asr_gemm_nt_3xtf32_slices(int Ma, int Nb, long long Kr, int max
   int dev = 0, sms = 148;
   if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   const int ctas = max_ctas > 0 && max_ctas < sms ? max_ctas : sms;
-  // enough items for ~3 rounds of the grid, slices of at least 64 k-blocks (the prologue / epilogue of an item costs ~10)
-  long long S = (3LL * ctas + tiles - 1) / tiles;
-  const long long smax = nkb / 64 > 0 ? nkb / 64 : 1;
-  if (S > smax) S = smax;
-  if (S > 32) S = 32;
-  if (S < 1) S = 1;
+  // the persistent grid works through tiles * S items in rounds; an item costs its k-blocks plus ~12 k-blocks' worth of
+  // pipeline fill, accumulator hand-over and epilogue: take the S with the cheapest last round (<= 32 slices, >= 16
+  // k-blocks each)
+  long long S = 1, best = -1;
+  for (long long s = 1; s <= 32 && (s == 1 || nkb / s >= 16); ++s) {
+    const long long per = (nkb + s - 1) / s;
+    if ((s - 1) * per >= nkb) continue;                            // would leave an empty slice
+    const long long rounds = (tiles * s + ctas - 1) / ctas;
+    const long long cost = rounds * (per + 12);
+    if (best < 0 || cost < best) { best = cost; S = s; }
+  }
   return (int)S;
 }
 

@@ -1,6 +1,6 @@
 """One launch of each hot-path kernel at its SURVEY.md section 8d shape between cudaProfilerStart/Stop, for ONE
-`ncu --profile-from-start off --set full` capture (key projection M2, CTC M5 (1000,150) rows / lattice / occupancy,
-attention step forward / backward M2).  Run with B2ASR_CTC_OVERLAP=0: under ncu kernels are serialised, and the
+`ncu --profile-from-start off --set full` capture (key projection M2, the two Listener product forms, CTC M5 (1000,150)
+rows / lattice / occupancy, attention step forward / backward M2).  Run with B2ASR_CTC_OVERLAP=0: under ncu kernels are serialised, and the
 overlapped CTC schedules wait for each other across streams.
 usage: B2ASR_CTC_OVERLAP=0 python tools/profile_kernels.py"""
 import importlib
@@ -13,7 +13,7 @@ os.environ.setdefault("B2ASR_CTC_OVERLAP", "0")
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 PKG = "end-to-end-asr-pytorch_b200"
-ctc, keys, attn = (importlib.import_module(PKG + "." + m) for m in ("ctc", "_keys", "_attn"))
+ctc, keys, attn, gemm = (importlib.import_module(PKG + "." + m) for m in ("ctc", "_keys", "_attn", "_gemm"))
 dev = torch.device("cuda:0")
 g = torch.Generator().manual_seed(0)
 
@@ -47,8 +47,16 @@ pg = torch.zeros(attn.num_slots(Ba, Ta, D, A, dec, "loc", 10, 100), attn.pgrad_l
 dctx, datt = torch.randn(Ba, D, device=dev), torch.randn(Ba, Ta, device=dev) * 0.01
 
 
+# Listener products, M2 layer 2-4 shapes: input projection [12800,640]x[2560,640]^T, weight gradient [12800,2560]^T[12800,640]
+xg = torch.randn(12800, 640, device=dev)
+wg_ = torch.randn(2560, 640, device=dev) * 640 ** -0.5
+dg = torch.randn(12800, 2560, device=dev) * 0.01
+
+
 def once():
     keys.project(h, w, b)
+    gemm.mm_tn(xg, wg_)
+    gemm.mm_nt(dg, xg)
     x.grad = None
     ctc.ctc_loss(x, yd, ild, tld, from_logits=True, batch_first=True).backward()
     att, ctx, q = attn.step_forward("loc", s, W["phi"], ka, ha, lens, prev, W["conv"], W["lproj"], W["gw"], W["gb"], 2.0, want_q=True)
