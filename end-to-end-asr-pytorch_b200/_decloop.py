@@ -17,6 +17,8 @@ import ctypes
 import os
 
 import torch
+import torch.nn.functional as F
+from torch.distributions.categorical import Categorical
 
 from . import _attn, _gemm, _lib
 
@@ -45,7 +47,12 @@ class DecoderLoop(torch.autograd.Function):
     """(keys, h, E, h0, c0, attention weights, cell weights) -> hs [B,L,H], att [L,B,T], h_L, c_L."""
 
     @staticmethod
-    def forward(ctx, meta, keys, h, E, h0, c0, phi, conv, lproj, gen_w, gen_b, w_ih, w_hh, b_ih, b_hh):
+    def forward(ctx, meta, keys, h, E, h0, c0, phi, conv, lproj, gen_w, gen_b, w_ih, w_hh, b_ih, b_hh, embed_w=None):
+        """meta["coins"] (optional, one bool per step): steps whose coin is False feed a SAMPLED character to the next
+        step (scheduled sampling, reference asr.py:96-101).  The loop then runs range by range: after such a step
+        meta["char_trans"] gives its logits, one Categorical sample is drawn -- the same draws in the same order as
+        the per-step loop -- and the sample's embedding projection replaces row t+1 of the gate buffer.  embed_w is the
+        embedding table; its gradient and the embedding half of w_ih's for the sampled rows are formed in backward."""
         _lib.require_cuda(keys, h, E, h0, c0, w_ih, w_hh)
         mode, lens, scale, emb = meta["mode"], meta["lens"], float(meta["scale"]), int(meta["emb_dim"])
         B, T, A = keys.shape
@@ -82,7 +89,27 @@ class DecoderLoop(torch.autograd.Function):
         _fill(io, keys=keys, h=h, lens=lens, w_ctx=w_ctx, w_hh=w_hh, h0=h0, c0=c0, att=att,
               ctx=None if FUSED_OPERANDS else cvec, q=q, gates=gates, hs=hs, cs=cs, xcat=xcat, w_cat=w_cat, **wts)
         io.w_ctx_ld = w_ih.stride(0)
-        _lib.call("b2asr_decoder_loop_fwd", 2 * L, _lib.lib().b2asr_decoder_loop_fwd, ctypes.byref(io), _lib.stream_ptr())
+        coins = meta.get("coins")
+        samples = {}
+        if coins is None or all(coins):
+            _lib.call("b2asr_decoder_loop_fwd", 2 * L, _lib.lib().b2asr_decoder_loop_fwd, ctypes.byref(io), _lib.stream_ptr())
+        else:
+            fwd_range = _lib.lib().b2asr_decoder_loop_fwd_range
+            w_emb = w_ih[:, :emb]
+            t0 = 0
+            for t in range(L):
+                if coins[t]:
+                    continue
+                _lib.call("b2asr_decoder_loop_fwd_range", 2 * (t + 1 - t0), fwd_range, ctypes.byref(io), t0, t + 1, _lib.stream_ptr())
+                t0 = t + 1
+                tok = Categorical(F.softmax(meta["char_trans"](hs[:, t]), dim=-1)).sample()
+                samples[t] = tok
+                if t + 1 < L:
+                    gates[:, t + 1] = F.linear(embed_w.detach()[tok], w_emb)
+            if t0 < L:
+                _lib.call("b2asr_decoder_loop_fwd_range", 2 * (L - t0), fwd_range, ctypes.byref(io), t0, L, _lib.stream_ptr())
+        ctx.samples = {t: tok for t, tok in samples.items() if t + 1 < L}
+        ctx.embed_w = embed_w
         ctx.io, ctx.meta = io, meta
         ctx.keep = (keys, h, lens, w_ih, w_hh, wts, h0, c0, att, cvec, q, gates, hs, cs, xcat, w_cat)   # what io points at
         ctx.mark_non_differentiable(att)
@@ -157,5 +184,23 @@ class DecoderLoop(torch.autograd.Function):
         if wts["b_ih"] is not None and (need[13] or need[14]):
             g_bih = dG2.sum(0)
             g_bhh = g_bih
+        g_embed = None
+        if ctx.samples:
+            # rows of the gate buffer that held a sampled character's projection embed_w[tok] w_emb^T: their gradient
+            # belongs to the embedding table and to the embedding half of w_ih, not to the teacher's row of E
+            steps = sorted(ctx.samples)
+            idx = torch.tensor([t + 1 for t in steps], device=dev)
+            toks = torch.stack([ctx.samples[t] for t in steps], dim=1).reshape(-1)              # [B*n]
+            rows = d_gates[:, idx].reshape(-1, 4 * H)                                          # [B*n, 4H]
+            embed_w = ctx.embed_w.detach()
+            if need[11]:
+                if g_wih is None:
+                    g_wih = torch.zeros(4 * H, emb + D, **f32)
+                g_wih[:, :emb] += rows.t().mm(embed_w[toks])
+            if need[15]:
+                g_embed = torch.zeros_like(embed_w).index_add_(0, toks, rows.mm(w_ih[:, :emb]))
+            if g_E is not None:
+                g_E = g_E.clone()
+                g_E[:, idx] = 0
         ctx.keep = None
-        return (None, g_keys, g_h, g_E, g_h0, g_c0, g_phi, g_conv, g_lproj, g_gw, g_gb, g_wih, g_whh, g_bih, g_bhh)
+        return (None, g_keys, g_h, g_E, g_h0, g_c0, g_phi, g_conv, g_lproj, g_gw, g_gb, g_wih, g_whh, g_bih, g_bhh, g_embed)

@@ -122,6 +122,7 @@ _SIGNATURES = {
     "b2asr_lstm_cell_bwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_i64, c_p, c_i, c_i, c_p]),
     "b2asr_decloop_size": (c_sz, []),
     "b2asr_decoder_loop_fwd": (c_i, [ctypes.POINTER(DecLoop), c_p]),
+    "b2asr_decoder_loop_fwd_range": (c_i, [ctypes.POINTER(DecLoop), c_i, c_i, c_p]),
     "b2asr_decoder_loop_bwd": (c_i, [ctypes.POINTER(DecLoop), c_p]),
     "b2asr_lstm_seq_size": (c_sz, []),
     "b2asr_lstm_seq_path": (c_i, [c_i]),

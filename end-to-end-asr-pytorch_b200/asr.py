@@ -511,9 +511,10 @@ class Seq2Seq(nn.Module):
         # the reference draws one coin per step inside the loop (asr.py:96); nothing else touches Python's
         # generator in between, so drawing the L coins up front yields the same sequence
         coins = [random.random() <= tf_rate for _ in range(decode_step)] if teacher is not None else None
-        if (coins is not None and all(coins) and decode_step > 0 and self.attention.comp_listener_feature is None
-                and os.environ.get("B2ASR_DECLOOP", "1") != "0"):
-            return self._decode_loop_native(encode_feature, encode_len, E, h, c)
+        if (coins is not None and decode_step > 0 and self.attention.comp_listener_feature is None
+                and os.environ.get("B2ASR_DECLOOP", "1") != "0"
+                and (all(coins) or os.environ.get("B2ASR_DECLOOP_SAMPLING", "1") != "0")):
+            return self._decode_loop_native(encode_feature, encode_len, E, h, c, None if all(coins) else coins)
         if need_grad:
             ses = _dec.DecSession(cell, E, emb_dim, decode_step)
             token = _dec.DecOpen.apply(ses, E, cell.weight_ih, cell.weight_hh, cell.bias_ih, cell.bias_hh)
@@ -547,16 +548,19 @@ class Seq2Seq(nn.Module):
             att_output = torch.stack(chars, dim=1)
         return att_output, [torch.stack(maps, dim=1)]
 
-    def _decode_loop_native(self, encode_feature, encode_len, E, h0, c0):
-        """Every step teacher-forced: the whole loop and its backward are one native call each (_decloop.py,
-        csrc/decloop.cu); leaves the module state (decoder state, prev_att) as the per-step loop would."""
+    def _decode_loop_native(self, encode_feature, encode_len, E, h0, c0, coins=None):
+        """The whole loop and its backward are one native call each (_decloop.py, csrc/decloop.cu) when every step is
+        teacher-forced; with scheduled sampling (coins: False = the next step gets a sampled character) the forward
+        runs range by range between the sampled steps.  Leaves the module state (decoder state, prev_att) as the
+        per-step loop would."""
         att_mod, cell = self.attention, self.decoder.layer0
         keys = att_mod.prepare(encode_feature, encode_len)
         p = att_mod._params()
-        meta = dict(mode=att_mod.mode, lens=att_mod._lens_dev, scale=2.0, emb_dim=self.embed.embedding_dim)
+        meta = dict(mode=att_mod.mode, lens=att_mod._lens_dev, scale=2.0, emb_dim=self.embed.embedding_dim,
+                    coins=coins, char_trans=self.char_trans)
         hs, att, h_last, c_last = _decloop.DecoderLoop.apply(
             meta, keys, encode_feature, E, h0, c0, p['phi'], p['conv'], p['lproj'], p['gen_w'], p['gen_b'],
-            cell.weight_ih, cell.weight_hh, cell.bias_ih, cell.bias_hh)
+            cell.weight_ih, cell.weight_hh, cell.bias_ih, cell.bias_hh, self.embed.weight if coins is not None else None)
         self.decoder.state_list[0], self.decoder.cell_list[0] = h_last, c_last
         if att_mod.mode == 'loc':
             att_mod.prev_att = att[-1].unsqueeze(1)                              # asr.py:456

@@ -106,7 +106,12 @@ using namespace b2asr;
 extern "C" size_t b2asr_decloop_size(void) { return sizeof(b2asr_decloop); }
 
 extern "C" int b2asr_decoder_loop_fwd(const b2asr_decloop* a, void* stream) {
+  return b2asr_decoder_loop_fwd_range(a, 0, a ? a->L : 0, stream);
+}
+
+extern "C" int b2asr_decoder_loop_fwd_range(const b2asr_decloop* a, int t0, int t1, void* stream) {
   if (int rc = check_common(a)) return rc;
+  B2_REQUIRE(0 <= t0 && t0 <= t1 && t1 <= a->L, B2ASR_EINVAL, "decoder loop forward: steps [%d,%d) of %d", t0, t1, a->L);
   cudaStream_t st = (cudaStream_t)stream;
   cublasHandle_t hd;
   if (int rc = blas_handle(&hd, st)) return rc;
@@ -116,10 +121,10 @@ extern "C" int b2asr_decoder_loop_fwd(const b2asr_decloop* a, void* stream) {
   const bool cat = a->xcat && a->w_cat;
   const int X = D + H;
   const bool fused = cat && fused_step_enabled() && dec_step_supported(H, X, X, gl);
-  if (cat)
+  if (cat && t0 == 0 && t1 > 0)
     B2_CUDA_TRY(cudaMemcpy2DAsync(a->xcat + D, sizeof(float) * X, a->h0, sizeof(float) * H, sizeof(float) * H, B,
                                   cudaMemcpyDeviceToDevice, st));
-  for (int t = 0; t < L; ++t) {
+  for (int t = t0; t < t1; ++t) {
     const float* s = t ? a->hs + (int64_t)(t - 1) * H : a->h0;
     const int64_t ss = t ? hl : H;
     const float* prev = (a->mode == 1 && t) ? a->att + (int64_t)(t - 1) * B * T : nullptr;

@@ -400,6 +400,11 @@ typedef struct b2asr_decloop {
 } b2asr_decloop;
 size_t b2asr_decloop_size(void);
 int b2asr_decoder_loop_fwd(const b2asr_decloop* io, void* stream);
+/* Steps [t0, t1) only; the state of step t0 - 1 is read from the stacks (hs, cs, att, xcat), so consecutive ranges add
+ * up to b2asr_decoder_loop_fwd.  Scheduled sampling (reference asr.py:96-101: some steps feed back a sampled character
+ * instead of the teacher's) runs the loop range by range and writes the sampled step's embedding projection into
+ * gates[:, t1] before continuing. */
+int b2asr_decoder_loop_fwd_range(const b2asr_decloop* io, int t0, int t1, void* stream);
 int b2asr_decoder_loop_bwd(const b2asr_decloop* io, void* stream);
 
 /* ------------------------------------------------------------------------

@@ -121,3 +121,40 @@ def test_native_loop_matches_per_step_path(cuda, monkeypatch, att_mode, B, T, L)
     assert model.decoder.state_list[0].shape == (B, 40)
     if att_mode == "loc":
         assert model.attention.prev_att.shape == (B, 1, T // 4)
+
+
+@pytest.mark.parametrize("att_mode", ["loc", "dot"])
+def test_native_loop_with_scheduled_sampling_matches_per_step_path(cuda, monkeypatch, att_mode):
+    """Scheduled sampling (reference asr.py:96-101) through the native loop run range by range (csrc/decloop.cu
+    b2asr_decoder_loop_fwd_range) against the per-step path.  The output layer is made so peaked that the Categorical
+    draw is the argmax in both paths (the draws themselves consume the same RNG stream), so tokens agree and outputs
+    and EVERY gradient -- including the embedding table's and the embedding half of weight_ih through the sampled
+    rows -- must agree."""
+    asr = importlib.import_module(PKG + ".asr")
+    lib = importlib.import_module(PKG + "._lib")
+    torch.manual_seed(5)
+    B, T, D_in, V, L = 6, 64, 12, 13, 12
+    model = asr.Seq2Seq(torch.zeros(1, 8, D_in), V, _cfg(att_mode)).to(cuda).train()
+    with torch.no_grad():
+        model.char_trans.weight.mul_(60.0)
+    x = torch.randn(B, T, D_in, device=cuda)
+    lens = [64, 61, 55, 50, 41, 33]
+    for b, n in enumerate(lens):
+        x[b, n:] = 0
+    y = torch.randint(2, V, (B, L + 1), device=cuda); y[:, 0] = 0
+    monkeypatch.setenv("B2ASR_DECLOOP_SAMPLING", "0")
+    a0, m0, g0, r0 = _run(model, x, y, lens, 0.5, True, 11)
+    monkeypatch.setenv("B2ASR_DECLOOP_SAMPLING", "1")
+    lib.profile_start()
+    a1, m1, g1, r1 = _run(model, x, y, lens, 0.5, True, 11)
+    prof = lib.profile_stop()
+    assert "b2asr_decoder_loop_fwd_range" in prof and prof["b2asr_decoder_loop_fwd_range"][0] >= 2   # really segmented
+    assert r0 == r1
+    assert torch.allclose(a0, a1, rtol=1e-4, atol=1e-4 * float(a0.abs().max()))
+    assert torch.allclose(m0, m1, rtol=1e-4, atol=1e-6)
+    assert set(g0) == set(g1)
+    for n in g0:
+        # (gen_energy.bias shifts every energy alike, its true gradient is 0: both paths return rounding noise there)
+        tol = 1e-4 * float(g0[n].abs().max()) + 1e-6
+        assert float((g0[n] - g1[n]).abs().max()) <= tol, n
+    assert float(g1["embed.weight"].abs().max()) > 0
