@@ -56,3 +56,40 @@ def mm_nt(a, b, period=0, max_ctas=0):
     _lib.call("b2asr_gemm_nt_3xtf32", 1, L.b2asr_gemm_nt_3xtf32, a.data_ptr(), a.stride(0), b.data_ptr(), b.stride(0),
               out.data_ptr(), Ma, Nb, Kr, period, S, max_ctas, _lib.stream_ptr())
     return out[0] if S == 1 else out.sum(0)
+
+
+class _Linear(torch.autograd.Function):
+    """y = x W^T + b for a wide output layer (the V=5000 `ctc_layer` / `char_trans` of the shipped libri config,
+    reference asr.py:38-44): the forward product, dx = dy W and dW = dy^T x on the tensor-core pipeline."""
+
+    @staticmethod
+    def forward(ctx, x, w, b):
+        x2 = x.reshape(-1, x.shape[-1])
+        ctx.save_for_backward(x2, w)
+        ctx.shape, ctx.has_bias = x.shape, b is not None
+        return mm_tn(x2.contiguous(), w.contiguous(), b).view(*x.shape[:-1], w.shape[0])
+
+    @staticmethod
+    def backward(ctx, g):
+        x2, w = ctx.saved_tensors
+        g2 = g.reshape(-1, g.shape[-1]).contiguous()
+        g_x = g_w = g_b = None
+        if ctx.needs_input_grad[0]:
+            g_x = mm_tn(g2, w.t().contiguous()).view(ctx.shape)
+        if ctx.needs_input_grad[1]:
+            g_w = mm_nt(g2, x2.contiguous())
+            if g_w is None:
+                g_w = g2.t().mm(x2)
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            g_b = g2.sum(0)
+        return g_x, g_w, g_b
+
+
+def linear(layer, x):
+    """layer(x) for an nn.Linear; wide layers on CUDA fp32 go through the tensor-core products, everything else (and
+    B2ASR_GEMM=cublas) through the library."""
+    w = layer.weight
+    if (ENABLED and x.is_cuda and x.dtype == torch.float32 and w.shape[0] >= 256 and w.shape[0] % 4 == 0
+            and w.shape[1] % 4 == 0 and x.numel() // x.shape[-1] * w.shape[0] * w.shape[1] >= MIN_WORK):
+        return _Linear.apply(x, w, layer.bias)
+    return layer(x)

@@ -28,7 +28,7 @@ import torch.nn.functional as F
 from torch.distributions.categorical import Categorical
 from torch.nn.utils.rnn import pack_padded_sequence, pad_packed_sequence
 
-from . import _attn, _dec, _decloop, _enc, _keys, fp32_library_math
+from . import _attn, _dec, _decloop, _enc, _gemm, _keys, fp32_library_math
 
 CTC_BEAM_RATIO = 1.5   # asr.py:15
 # B2ASR_ENC=cudnn keeps the Listener's LSTMs on the library's per-frame path (A/B measurements only)
@@ -462,7 +462,7 @@ class Seq2Seq(nn.Module):
         encode_feature, encode_len = self.encoder(audio_feature, state_len)
         ctc_output = att_output = att_maps = None
         if self.joint_ctc:
-            ctc_output = self.ctc_layer(encode_feature)
+            ctc_output = _gemm.linear(self.ctc_layer, encode_feature)
         if self.joint_att:
             if teacher is not None:
                 teacher = self.embed(teacher)
@@ -539,7 +539,7 @@ class Seq2Seq(nn.Module):
             maps.append(score[0].detach())
         todo = [t for t in range(decode_step) if chars[t] is None]
         if len(todo) == decode_step:
-            att_output = self.char_trans(torch.stack(outs, dim=1))      # one GEMM for every step
+            att_output = _gemm.linear(self.char_trans, torch.stack(outs, dim=1))      # one GEMM for every step
         else:
             if todo:
                 late = self.char_trans(torch.stack([outs[t] for t in todo], dim=1)).unbind(1)
@@ -564,7 +564,7 @@ class Seq2Seq(nn.Module):
         self.decoder.state_list[0], self.decoder.cell_list[0] = h_last, c_last
         if att_mod.mode == 'loc':
             att_mod.prev_att = att[-1].unsqueeze(1)                              # asr.py:456
-        return self.char_trans(hs), [att.transpose(0, 1)]
+        return _gemm.linear(self.char_trans, hs), [att.transpose(0, 1)]
 
     def beam_decode(self, audio_feature, decode_step, state_len, decode_beam_size):
         """Joint CTC/attention/RNN-LM beam search, device-resident (asr.py:155-258); returns the top

@@ -117,3 +117,38 @@ def test_gemm_nt_capped_grid_and_slices_agree(cuda):
     ref = a.double().t() @ b.double()
     for got in (full, capped):
         assert float(((got.double() - ref).abs() / (1 + ref.abs())).max()) <= 2e-5
+
+
+def test_wide_linear_autograd_matches_torch(cuda):
+    """_gemm.linear (the V=5000 output layers of the shipped libri config): forward, dx, dW, db against nn.Linear in
+    float64."""
+    mod = _gemm()
+    torch.manual_seed(0)
+    lin = torch.nn.Linear(320, 1000).to(cuda)
+    x = torch.randn(6, 50, 320, device=cuda, requires_grad=True)
+    old, mod.MIN_WORK = mod.MIN_WORK, 0
+    try:
+        y = mod.linear(lin, x)
+        assert y.grad_fn is not None and "Linear" in type(y.grad_fn).__name__
+        gy = torch.randn_like(y)
+        gx, gw, gb = torch.autograd.grad(y, (x, lin.weight, lin.bias), gy)
+    finally:
+        mod.MIN_WORK = old
+    lin64 = torch.nn.Linear(320, 1000).double().to(cuda)
+    lin64.load_state_dict({k: v.double() for k, v in lin.state_dict().items()})
+    x64 = x.detach().double().requires_grad_(True)
+    y64 = lin64(x64)
+    rx, rw, rb = torch.autograd.grad(y64, (x64, lin64.weight, lin64.bias), gy.double())
+    # the yardstick is the library's own fp32 rounding on the same products (sums of K terms of size O(1)-O(10))
+    flag = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    x32 = x.detach().clone().requires_grad_(True)
+    y32 = lin(x32)
+    lx, lw, lb = torch.autograd.grad(y32, (x32, lin.weight, lin.bias), gy)
+    torch.backends.cuda.matmul.allow_tf32 = flag
+    for got, lib32, ref in ((y, y32, y64), (gx, lx, rx), (gw, lw, rw), (gb, lb, rb)):
+        err = float((got.detach().double() - ref).abs().max())
+        err_lib = float((lib32.detach().double() - ref).abs().max())
+        assert err <= max(6 * err_lib, 2e-5), (err, err_lib)
+    small = torch.nn.Linear(320, 31).to(cuda)                  # narrow layers stay on the library
+    assert "_Linear" not in type(mod.linear(small, x).grad_fn).__name__
