@@ -7,7 +7,7 @@ The Listener's tanh(Linear) after every layer (reference asr.py:313-316) is the 
 import torch
 import torch.nn.functional as F
 
-from . import _gemm, _lib
+from . import _enc, _gemm, _lib
 
 
 class _KeysFunction(torch.autograd.Function):
@@ -15,6 +15,7 @@ class _KeysFunction(torch.autograd.Function):
     def forward(ctx, h, w, b):
         keys = _forward(h, w, b)
         ctx.save_for_backward(h, w, keys)
+        ctx.params = (w, b)
         return keys
 
     @staticmethod
@@ -26,6 +27,35 @@ class _KeysFunction(torch.autograd.Function):
         g_h = g_w = None
         if ctx.needs_input_grad[0]:
             g_h = _gemm.mm_tn(dz2, w.t().contiguous()).view_as(h)          # dz W
+        pw, pb = ctx.params
+        if (_enc._armed[0] and not torch.is_grad_enabled() and ctx.needs_input_grad[1] and pw.is_leaf
+                and (pb is None or pb.is_leaf)):
+            # inside solver.TrainStep's backward pass (see _enc.deferred_weight_grads): nothing downstream reads the
+            # weight gradients, so they join the Listener's on the side stream, next to the next recurrence kernel
+            ready = torch.cuda.Event()
+            ready.record()
+            want_b = ctx.needs_input_grad[2] and pb is not None
+
+            def work(side, shared):
+                side.wait_event(ready)
+                for t in (dz2, h2):
+                    t.record_stream(side)
+                gw = _gemm.mm_nt(dz2, h2, max_ctas=_gemm.SIDE_CTAS if shared else 0)
+                if gw is None:
+                    gw = dz2.t().mm(h2)
+                for p, g in ((pw, gw), (pb, dz2.sum(0) if want_b else None)):
+                    if g is None:
+                        continue
+                    if p.grad is None:
+                        p.grad = g.clone()
+                    else:
+                        p.grad.add_(g)
+
+            _enc._deferred.append(work)
+            if not _enc._join_queued[0]:
+                torch.autograd.Variable._execution_engine.queue_callback(_enc._join)
+                _enc._join_queued[0] = True
+            return g_h, None, None
         if ctx.needs_input_grad[1]:
             g_w = _gemm.mm_nt(dz2, h2)                                     # dz^T h
             if g_w is None:
