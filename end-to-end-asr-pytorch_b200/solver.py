@@ -105,6 +105,46 @@ class FlatGradients:
         return norm
 
 
+class DevicePrefetcher:
+    """Iterates host batches (tuples of tensors) as device tensors; the host->device copies of batch i+1 are issued on a
+    side stream before batch i is handed out, so they run under step i (asynchronous when the host tensors are pinned).
+    dtypes: optional per-tensor target dtypes (converted on the device, like `.to(device, dtype)`)."""
+
+    def __init__(self, batches, device, dtypes=None):
+        self.batches, self.device, self.dtypes = batches, torch.device(device), dtypes
+
+    def _load(self, batch, stream):
+        dtypes = self.dtypes or [None] * len(batch)
+        if stream is None:
+            return tuple(t.to(self.device, dtype=d) if d is not None else t.to(self.device) for t, d in zip(batch, dtypes)), None
+        with torch.cuda.stream(stream):
+            out = tuple(t.to(self.device, dtype=d, non_blocking=True) if d is not None else t.to(self.device, non_blocking=True)
+                        for t, d in zip(batch, dtypes))
+            ev = torch.cuda.Event()
+            ev.record(stream)
+        return out, ev
+
+    def __iter__(self):
+        stream = torch.cuda.Stream(self.device) if self.device.type == 'cuda' else None
+        it = iter(self.batches)
+        try:
+            nxt = self._load(next(it), stream)
+        except StopIteration:
+            return
+        while nxt is not None:
+            cur, ev = nxt
+            try:
+                nxt = self._load(next(it), stream)          # batch i+1 starts moving before batch i is used
+            except StopIteration:
+                nxt = None
+            if ev is not None:
+                main = torch.cuda.current_stream(self.device)
+                main.wait_event(ev)
+                for t in cur:
+                    t.record_stream(main)
+            yield cur
+
+
 class _Stepped:
     """Truth value of "the optimizer stepped" (reference solver.py:179: `math.isnan(grad_norm)` -> no step), read from
     the device only when somebody asks."""
@@ -312,17 +352,21 @@ class Trainer(Solver):
         rank, world = _dist()
         usable = (len(self.train_set) // world) * world
         while self.step < self.max_step:
-            for i, (x, y) in enumerate(self.train_set):
-                if i >= usable:
-                    break
-                if i % world != rank:
-                    continue
+            def mine():
+                for i, (x, y) in enumerate(self.train_set):
+                    if i >= usable:
+                        break
+                    if i % world != rank:
+                        continue
+                    assert len(x.shape) == 4, 'Bucketing should cause acoustic feature to have shape 1xBxTxD'
+                    assert len(y.shape) == 3, 'Bucketing should cause label have to shape 1xBxT'
+                    yield x.squeeze(0), y.squeeze(0)
+
+            # the next batch's host->device copies run under the current step (reference solver.py:139-140 moves each
+            # batch synchronously at the top of its step)
+            for x, y in DevicePrefetcher(mine(), self.device, dtypes=(torch.float32, torch.long)):
                 self.progress('Training step - ' + str(self.step))
                 tf_rate = self.tf_start - self.step * (self.tf_start - self.tf_end) / self.max_step
-                assert len(x.shape) == 4, 'Bucketing should cause acoustic feature to have shape 1xBxTxD'
-                assert len(y.shape) == 3, 'Bucketing should cause label have to shape 1xBxT'
-                x = x.squeeze(0).to(device=self.device, dtype=torch.float32, non_blocking=True)
-                y = y.squeeze(0).to(device=self.device, dtype=torch.long, non_blocking=True)
                 out = self.train_step.step(x, y, tf_rate)
                 if not out['stepped']:
                     self.verbose('Error : grad norm is NaN @ step ' + str(self.step))
