@@ -402,7 +402,10 @@ def _native_decode(model, lm, bs, h, keys, enc_len0, decode_step):
         dst = 1 - src
         pg = progs[src]
         a = pg.attn
-        a.mode, a.C, a.Kw, a.B, a.T, a.D, a.A, a.dec, a.cluster = _attn.MODES[att.mode], C, Kw, n, Tp, D, A, pk.H, 0
+        # cluster hint: with the RNN-LM chain running next to it on the second stream the attention launch is better
+        # off with half the CTAs (B2ASR_ATT_FWD_CS A/B at M4: 4 CTAs per row 218 us per step, the automatic 8: 228 us)
+        hint = 4 if (pk.lm is not None and Tp >= 128 and 8 * n > 148) else 0
+        a.mode, a.C, a.Kw, a.B, a.T, a.D, a.A, a.dec, a.cluster = _attn.MODES[att.mode], C, Kw, n, Tp, D, A, pk.H, hint
         a.scale = 2.0
         a.s, a.s_stride = p(dec_h[0][src]), pk.H4
         a.Wphi, a.keys, a.k_bstride, a.h, a.h_bstride = p(pr['phi']), p(keys), 0, p(h), 0
