@@ -7,7 +7,7 @@ Tolerances (north_star: 1e-4 relative in fp32):
     reference call, where row_scale = upstream/(B*target_len_b) is the largest magnitude a
     gradient entry of that utterance can take (softmax and occupancy both lie in [0,1]).
     The fp32 ATen kernel the reference runs is itself 1e-3..2e-2*row_scale away from float64
-    at T>=300 (fp32 log-space cancellation; measured in tools/diag_ctc.py), so float64 is the
+    at T>=300 (fp32 log-space cancellation; measured with a one-off script in round 1), so float64 is the
     judge; against torch fp32 we only require that we are no further from it than it is from
     float64 (x4).
 """
