@@ -23,15 +23,25 @@ constexpr float kNegCtc  = -1000000.0f;       // asr.py:225
 constexpr float kNegSos  = -10000000.0f;      // asr.py:229
 constexpr int   kEos     = 1;
 constexpr int   kBeamNT  = 256;
-constexpr int   kCandPerWarp = 10;            // 3 lanes per candidate
 constexpr int   kMaxK    = 32;
 
 // numpy's float32 logaddexp (npy_logaddexpf): x==y -> x+ln2, else max + log1pf(expf(-|x-y|)).
+// The frame-sequential evaluation order is the reference's; the two transcendentals are evaluated on the special
+// function unit instead of through libm: e = 2^(-|x-y| log2 e) (MUFU.EX2) and log1p(e) = ln2 * log2(u) + (e - (u-1))/u
+// with u = 1 + e (MUFU.LG2; the second term restores what rounding 1 + e lost).  Absolute error per call <= ~2e-7
+// (libm: ~6e-8) on values of magnitude 10-1000, i.e. 1e-8 relative against the 1e-5 bar of the prefix scores; the
+// dependent chain per frame shrinks from ~370 to ~130 clk, which is what the step time of kernel (3) consists of.
+// -DB2ASR_BEAM_LIBM restores log1pf(expf()).
 __device__ __forceinline__ float np_logaddexp(float x, float y) {
-  // branch-free form of the same arithmetic: both of numpy's branches compute max + log1pf(expf(-|x-y|))
   const float tmp = __fsub_rn(x, y);
   const float m = tmp > 0.f ? x : y;
+#ifdef B2ASR_BEAM_LIBM
   const float r = __fadd_rn(m, log1pf(expf(-fabsf(tmp))));
+#else
+  const float e = ex2(-fabsf(tmp) * kLog2e);
+  const float u = 1.f + e;
+  const float r = m + fmaf(lg2(u), 0.693147180559945309417232121458176568f, __fdividef(e - (u - 1.f), u));
+#endif
   return x == y ? __fadd_rn(x, 0.693147180559945309417232121458176568f) : r;
 }
 
@@ -145,38 +155,35 @@ __device__ void prefix_fill_tables(const PrefixTables& tb, const float* x, int T
   }
 }
 
-// The sequential recursion (ctc.py:85-98).  Executed by warps 0..ceil(K/10)-1; lane = 3*c + role with
-// role 0: r[t,0] (ends in non-blank), 1: r[t,1] (ends in blank), 2: psi.  r rows are written with the
-// caller's strides: element (t,k,j) at r_out[t*st_t + k*st_k + j].
+// The sequential recursion (ctc.py:85-98).  Executed by warp 0, lane = candidate: a lane carries its candidate's three
+// running values -- r[t,0] (prefix ends in the candidate), r[t,1] (ends in blank) and psi -- whose three logaddexp per
+// frame are independent of each other, so their latencies overlap inside the thread and nothing crosses lanes
+// (one lane per value with a shuffle per frame was 307 clk per frame: a pure dependency chain).  r rows are written
+// with the caller's strides: element (t,k,j) at r_out[t*st_t + k*st_k + j].
 __device__ void prefix_recursion(const PrefixTables& tb, int T, int K, int prefix_len, int last,
                                  const int* cand_sm, float* psi_out, float* r_out, long long st_t, long long st_k) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int c = lane / 3, role = lane - 3 * c;
-  const int k = warp * kCandPerWarp + c;
-  const bool on = (c < kCandPerWarp) && (k < K);
+  const int k = threadIdx.x & 31;
+  if (k >= K) return;
   const int start = max(1, prefix_len);
-  const bool same = on && (cand_sm[k] == last);
+  const bool same = cand_sm[k] == last;
+  float* ro = r_out + k * st_k;
   // rows before start-1 (and the blank column of row start-1) are "log zero" (ctc.py:73)
-  if (on && role < 2) {
-    for (int t = 0; t < min(start, T); ++t) r_out[t * st_t + k * st_k + role] = kLogZero;
-  }
-  float cur = kLogZero;
-  if (on && role != 1 && prefix_len == 0) cur = tb.xk[k];       // r[0,0,:] = x[0,cands]; psi = r[start-1,0,:]
-  if (on && role == 0 && start - 1 < T) r_out[(start - 1) * st_t + k * st_k] = cur;
+  for (int t = 0; t < min(start, T); ++t) { ro[t * st_t] = kLogZero; ro[t * st_t + 1] = kLogZero; }
+  float rn = kLogZero, rb = kLogZero;
+  if (prefix_len == 0) rn = tb.xk[k];                           // r[0,0,:] = x[0,cands]
+  float psi = rn;                                               // psi = r[start-1,0,:]
+  if (start - 1 < T) ro[(start - 1) * st_t] = rn;
+  const float* phis = same ? tb.phiS : tb.phiD;
+#pragma unroll 2
   for (int t = start; t < T; ++t) {
-    const float left = __shfl_up_sync(kFull, cur, 1);            // role 1 reads its candidate's r[t-1,0]
-    if (on) {
-      const float phi = same ? tb.phiS[t] : tb.phiD[t];
-      const float xe = tb.xk[t * 32 + k];
-      const float b = role == 0 ? phi : (role == 1 ? left : __fadd_rn(phi, xe));
-      const float add = role == 0 ? xe : (role == 1 ? tb.xb[t] : 0.f);
-      float v = np_logaddexp(cur, b);
-      if (role != 2) v = __fadd_rn(v, add);
-      cur = v;
-      if (role < 2) r_out[t * st_t + k * st_k + role] = v;
-    }
+    const float phi = phis[t], xe = tb.xk[t * 32 + k], xbt = tb.xb[t];
+    const float n0 = __fadd_rn(np_logaddexp(rn, phi), xe);      // ctc.py:94
+    const float n1 = __fadd_rn(np_logaddexp(rb, rn), xbt);      // ctc.py:95 (reads r[t-1,0])
+    psi = np_logaddexp(psi, __fadd_rn(phi, xe));                // ctc.py:96
+    rn = n0; rb = n1;
+    ro[t * st_t] = n0; ro[t * st_t + 1] = n1;
   }
-  if (on && role == 2) psi_out[k] = cur;
+  psi_out[k] = psi;
 }
 
 __host__ __device__ inline size_t prefix_smem_floats(int T) { return (size_t)T * 32 + 3 * (size_t)((T + 3) / 4 * 4); }
@@ -207,7 +214,7 @@ __global__ void __launch_bounds__(kBeamNT) prefix_score_kernel(const float* x, i
   __syncthreads();
   prefix_fill_tables(tb, x, T, V, r_prev, cand_sm, K, max(1, prefix_len));
   __syncthreads();
-  if ((threadIdx.x >> 5) * kCandPerWarp < K) prefix_recursion(tb, T, K, prefix_len, last, cand_sm, psi, r_out, 2, (long long)T * 2);
+  if (threadIdx.x < 32) prefix_recursion(tb, T, K, prefix_len, last, cand_sm, psi, r_out, 2, (long long)T * 2);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -278,7 +285,7 @@ __global__ void __launch_bounds__(kBeamNT) beam_step_kernel(b2asr_beam_io io) {
       __syncthreads();
       BT(3);
       // ---- prefix scores of prefix+[c] (ctc.py:65-101) ------------------------------------------------
-      if ((tid >> 5) * kCandPerWarp < K)
+      if (tid < 32)
         prefix_recursion(tb, T, K, plen, (int)io.last_in[row], cand_sm, psi_sm,
                          io.r_all + (long long)row * T * K * 2, (long long)K * 2, 2);
       __syncthreads();
