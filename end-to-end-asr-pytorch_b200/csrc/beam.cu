@@ -26,16 +26,16 @@ constexpr int   kBeamNT  = 256;
 constexpr int   kMaxK    = 32;
 
 // numpy's float32 logaddexp (npy_logaddexpf): x==y -> x+ln2, else max + log1pf(expf(-|x-y|)).
-// The frame-sequential evaluation order is the reference's; the two transcendentals are evaluated on the special
-// function unit instead of through libm: e = 2^(-|x-y| log2 e) (MUFU.EX2) and log1p(e) = ln2 * log2(u) + (e - (u-1))/u
-// with u = 1 + e (MUFU.LG2; the second term restores what rounding 1 + e lost).  Absolute error per call <= ~2e-7
-// (libm: ~6e-8) on values of magnitude 10-1000, i.e. 1e-8 relative against the 1e-5 bar of the prefix scores; the
-// dependent chain per frame shrinks from ~370 to ~130 clk, which is what the step time of kernel (3) consists of.
-// -DB2ASR_BEAM_LIBM restores log1pf(expf()).
+// Default: the same two libm calls as numpy makes (CUDA's expf / log1pf differ from glibc's by an ulp in ~1.5 % of
+// calls).  -DB2ASR_BEAM_SFU evaluates them on the special function unit instead -- e = 2^(-|x-y| log2 e) (MUFU.EX2),
+// log1p(e) = ln2 * log2(u) + (e - (u-1))/u with u = 1 + e (MUFU.LG2; the second term restores what rounding 1 + e lost)
+// -- absolute error per call <= ~2e-7 instead of ~6e-8, the recursion 26.7 instead of 39.3 us per step at M4 and all
+// decode tests still token-identical; not the default because every rounding difference is a chance to flip a
+// near-tie against the reference.
 __device__ __forceinline__ float np_logaddexp(float x, float y) {
   const float tmp = __fsub_rn(x, y);
   const float m = tmp > 0.f ? x : y;
-#ifdef B2ASR_BEAM_LIBM
+#ifndef B2ASR_BEAM_SFU
   const float r = __fadd_rn(m, log1pf(expf(-fabsf(tmp))));
 #else
   const float e = ex2(-fabsf(tmp) * kLog2e);
