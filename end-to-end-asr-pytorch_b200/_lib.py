@@ -39,6 +39,7 @@ class BeamIO(ctypes.Structure):
         ("hist_parent", c_p), ("hist_tok", c_p), ("hist_score", c_p),
         ("fin_count", c_p), ("fin_step", c_p), ("fin_row", c_p), ("fin_score", c_p), ("fin_sum", c_p),
         ("att_lse", c_p), ("lm_lse", c_p),
+        ("x_ctc_t", c_p), ("x_ctc_t_ld", c_i64),
     ]
 
 

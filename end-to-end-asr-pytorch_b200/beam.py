@@ -83,6 +83,12 @@ class BeamSearch:
             raise ValueError('joint CTC decoding supports int(1.5*beam) <= 32 candidates (beam <= 21), got beam %d' % beam)
         self.x_ctc = None if x_ctc is None else x_ctc.detach().to(device, torch.float32).contiguous()
         self.T = 0 if self.x_ctc is None else int(self.x_ctc.shape[0])
+        # [V, T'] copy, made once per utterance: the per-step gather of the candidates' columns becomes K row reads
+        self.x_ctc_t = None
+        if self.x_ctc is not None:
+            Tp4 = (self.T + 3) // 4 * 4
+            self.x_ctc_t = torch.zeros(self.x_ctc.shape[1], Tp4, dtype=torch.float32, device=device)
+            self.x_ctc_t[:, :self.T] = self.x_ctc.t()
         self.ctc_weight, self.lm_weight = float(ctc_weight), float(lm_weight)
         n, T, K, V = self.n, max(self.T, 1), max(self.K, 1), self.V
         f32 = dict(dtype=torch.float32, device=device)
@@ -127,6 +133,7 @@ class BeamSearch:
         io = _lib.BeamIO()
         p = _lib.ptr
         io.x_ctc = p(self.x_ctc)
+        io.x_ctc_t, io.x_ctc_t_ld = p(self.x_ctc_t), (0 if self.x_ctc_t is None else self.x_ctc_t.stride(0))
         io.T, io.V, io.n, io.K, io.max_steps = self.T, self.V, self.n, self.K, self.max_steps
         io.w_att = float(np.float32(1 - self.ctc_weight))       # python double (1-w) cast to fp32, as torch does
         io.w_ctc = float(np.float32(self.ctc_weight))

@@ -134,19 +134,33 @@ __device__ void cta_topk(const float* vals, int V, int k, float* outv, int* outi
 }
 
 // Shared-memory frame tables of one hypothesis, filled by the whole CTA.
-struct PrefixTables { float* xk; float* xb; float* phiD; float* phiS; };   // xk [T][32]
+// xk [32][xk_pitch(T)]: candidate-major; the pitch is odd, so the recursion's lanes (one candidate each, same frame) hit
+// 32 different banks and the fill writes runs of consecutive frames
+struct PrefixTables { float* xk; float* xb; float* phiD; float* phiS; };
+__host__ __device__ inline int xk_pitch(int T) { return T | 1; }
 
 __device__ void prefix_fill_tables(const PrefixTables& tb, const float* x, int T, int V, const float* r_prev,
-                                   const int* cand_sm, int K, int start) {
+                                   const int* cand_sm, int K, int start, const float* xt = nullptr, long long xt_ld = 0) {
   const int tid = threadIdx.x, NT = blockDim.x;
   const int first = start == 1 ? 0 : start;        // row 0 is read only for the empty prefix (start == 1)
+  const int TP = xk_pitch(T);
+  if (xt) {
+    // transposed posteriors: candidate k's column is the contiguous row xt[cand[k]][0:T] -- a warp reads 32
+    // consecutive frames of one candidate (one 128-byte line) and scatters them down column k of xk
+    const int lane = tid & 31, warp = tid >> 5, nw = NT >> 5;
+    for (int k = warp; k < 32; k += nw) {
+      const float* row = xt + (long long)cand_sm[k < K ? k : 0] * xt_ld;
+      for (int t = lane; t < T; t += 32) tb.xk[k * TP + t] = (k < K && t >= first) ? __ldg(row + t) : 0.f;
+    }
+  } else {
 #pragma unroll 8
-  for (int i = first * 32 + tid; i < T * 32; i += NT) {
-    const int t = i >> 5, k = i & 31;
-    tb.xk[i] = k < K ? __ldg(x + (long long)t * V + cand_sm[k]) : 0.f;
+    for (int i = first * 32 + tid; i < T * 32; i += NT) {
+      const int t = i >> 5, k = i & 31;
+      tb.xk[k * TP + t] = k < K ? __ldg(x + (long long)t * V + cand_sm[k]) : 0.f;
+    }
   }
   for (int t = tid; t < T; t += NT) {
-    tb.xb[t] = __ldg(x + (long long)t * V);                     // blank = 0 (ctc.py:12)
+    tb.xb[t] = xt ? __ldg(xt + t) : __ldg(x + (long long)t * V);  // blank = 0 (ctc.py:12): row 0 of the transposed table
     if (t >= start) {
       const float pnb = r_prev[2 * (t - 1)], pb = r_prev[2 * (t - 1) + 1];
       tb.phiD[t] = np_logaddexp(pnb, pb);                        // ctc.py:87-93
@@ -170,13 +184,14 @@ __device__ void prefix_recursion(const PrefixTables& tb, int T, int K, int prefi
   // rows before start-1 (and the blank column of row start-1) are "log zero" (ctc.py:73)
   for (int t = 0; t < min(start, T); ++t) { ro[t * st_t] = kLogZero; ro[t * st_t + 1] = kLogZero; }
   float rn = kLogZero, rb = kLogZero;
-  if (prefix_len == 0) rn = tb.xk[k];                           // r[0,0,:] = x[0,cands]
+  const float* xkk = tb.xk + k * xk_pitch(T);                   // this candidate's column of the posteriors
+  if (prefix_len == 0) rn = xkk[0];                             // r[0,0,:] = x[0,cands]
   float psi = rn;                                               // psi = r[start-1,0,:]
   if (start - 1 < T) ro[(start - 1) * st_t] = rn;
   const float* phis = same ? tb.phiS : tb.phiD;
 #pragma unroll 2
   for (int t = start; t < T; ++t) {
-    const float phi = phis[t], xe = tb.xk[t * 32 + k], xbt = tb.xb[t];
+    const float phi = phis[t], xe = xkk[t], xbt = tb.xb[t];
     const float n0 = __fadd_rn(np_logaddexp(rn, phi), xe);      // ctc.py:94
     const float n1 = __fadd_rn(np_logaddexp(rb, rn), xbt);      // ctc.py:95 (reads r[t-1,0])
     psi = np_logaddexp(psi, __fadd_rn(phi, xe));                // ctc.py:96
@@ -186,7 +201,7 @@ __device__ void prefix_recursion(const PrefixTables& tb, int T, int K, int prefi
   psi_out[k] = psi;
 }
 
-__host__ __device__ inline size_t prefix_smem_floats(int T) { return (size_t)T * 32 + 3 * (size_t)((T + 3) / 4 * 4); }
+__host__ __device__ inline size_t prefix_smem_floats(int T) { return (size_t)xk_pitch(T) * 32 + 3 * (size_t)((T + 3) / 4 * 4); }
 
 // ------------------------------------------------------------------------------------------------
 // Stand-alone scorer kernels (API parity with CTCPrefixScore)
@@ -209,7 +224,8 @@ __global__ void __launch_bounds__(kBeamNT) prefix_score_kernel(const float* x, i
   extern __shared__ __align__(16) float smf[];
   __shared__ int cand_sm[kMaxK];
   const int Tp = (T + 3) / 4 * 4;
-  PrefixTables tb{smf, smf + (size_t)T * 32, smf + (size_t)T * 32 + Tp, smf + (size_t)T * 32 + 2 * Tp};
+  const size_t xkf = (size_t)xk_pitch(T) * 32;
+  PrefixTables tb{smf, smf + xkf, smf + xkf + Tp, smf + xkf + 2 * Tp};
   if (threadIdx.x < kMaxK) cand_sm[threadIdx.x] = threadIdx.x < K ? min(V - 1, max(0, cands[threadIdx.x])) : 0;
   __syncthreads();
   prefix_fill_tables(tb, x, T, V, r_prev, cand_sm, K, max(1, prefix_len));
@@ -279,9 +295,10 @@ __global__ void __launch_bounds__(kBeamNT) beam_step_kernel(b2asr_beam_io io) {
       BT(2);
       const int Tp = (T + 3) / 4 * 4;
       float* base = smf + Vp;
-      PrefixTables tb{base, base + (size_t)T * 32, base + (size_t)T * 32 + Tp, base + (size_t)T * 32 + 2 * Tp};
+      const size_t xkf = (size_t)xk_pitch(T) * 32;
+      PrefixTables tb{base, base + xkf, base + xkf + Tp, base + xkf + 2 * Tp};
       const float* r_prev = io.r_in + (long long)row * T * 2;
-      prefix_fill_tables(tb, io.x_ctc, T, V, r_prev, cand_sm, K, max(1, plen));
+      prefix_fill_tables(tb, io.x_ctc, T, V, r_prev, cand_sm, K, max(1, plen), io.x_ctc_t, io.x_ctc_t_ld);
       __syncthreads();
       BT(3);
       // ---- prefix scores of prefix+[c] (ctc.py:65-101) ------------------------------------------------

@@ -268,6 +268,9 @@ typedef struct b2asr_beam_io {
    * asr.py:210,235 is `logit - lse` (torch's own epilogue form) inside the kernel; NULL = the inputs are log-probs */
   const float* att_lse;    /* [n] or NULL */
   const float* lm_lse;     /* [n] or NULL */
+  /* optional: x_ctc transposed, [V,T] with row pitch x_ctc_t_ld >= T (multiple of 4 floats), or NULL.  With it the
+   * per-step gather of the K candidates' frame columns reads K contiguous rows instead of T*K scattered sectors. */
+  const float* x_ctc_t; int64_t x_ctc_t_ld;
 } b2asr_beam_io;
 
 size_t b2asr_beam_io_size(void);   /* sizeof(b2asr_beam_io), for binding sanity checks */
