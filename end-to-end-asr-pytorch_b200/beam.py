@@ -463,7 +463,49 @@ def _native_decode(model, lm, bs, h, keys, enc_len0, decode_step):
     bs._keep = (keep, progs, ios, pk)                                          # alive until the results are read
 
 
-def beam_decode(model, audio_feature, decode_step, state_len, decode_beam_size, use_graph=None):
+def beam_decode_many(model, utterances, decode_beam_size, streams=4):
+    """Several utterances in flight on one GPU.  utterances: iterable of (audio_feature [1,T,D], decode_step, state_len);
+    returns their Hypothesis lists in order.  One decode is a latency-bound chain that keeps a fraction of the SMs busy
+    (the beam step runs `beam` CTAs), so up to `streams` utterances are enqueued on CUDA streams of their own -- the
+    reference's answer to the same observation is `--njobs` worker processes (README.md:123).  Each utterance's search
+    is the one beam_decode runs; utterances whose model configuration the native loop does not take are decoded one
+    after the other."""
+    utterances = list(utterances)
+    if not utterances:
+        return []
+    dev = utterances[0][0].device
+    pool = [torch.cuda.Stream(dev) for _ in range(max(1, min(int(streams), 8)))]
+    main = torch.cuda.current_stream(dev)
+    results = [None] * len(utterances)
+    pending = {}                                                     # stream slot -> (index, BeamSearch)
+
+    def finish(slot):
+        i, bs = pending.pop(slot)
+        with torch.cuda.stream(pool[slot]):
+            results[i] = bs.results(emb=model.embed)
+
+    for i, (x, decode_step, state_len) in enumerate(utterances):
+        slot = i % len(pool)
+        if slot in pending:
+            finish(slot)                                             # at most len(pool) utterances hold buffers
+        pool[slot].wait_stream(main)
+        with torch.cuda.stream(pool[slot]):
+            x.record_stream(pool[slot])
+            out = beam_decode(model, x, decode_step, state_len, decode_beam_size, _defer=True)
+        if isinstance(out, BeamSearch):
+            pending[slot] = (i, out)
+        else:
+            results[i] = out                                         # decoded synchronously (per-step path) or empty
+    for slot in sorted(pending):
+        finish(slot)
+    for st in pool:
+        main.wait_stream(st)
+    from . import _enc
+    _enc.check_status(dev)
+    return results
+
+
+def beam_decode(model, audio_feature, decode_step, state_len, decode_beam_size, use_graph=None, _defer=False):
     """Seq2Seq.beam_decode (asr.py:155-258) for one utterance; returns the top `decode_beam_size`
     Hypothesis objects sorted by mean score."""
     assert audio_feature.shape[0] == 1
@@ -502,6 +544,8 @@ def beam_decode(model, audio_feature, decode_step, state_len, decode_beam_size, 
             # every step's kernels enqueued by ONE C call (csrc/decode.cu); the per-step path below stays for cells
             # the tile kernels do not take (GRU) and for A/B runs
             _native_decode(model, lm, bs, h, keys, int(enc_len[0]), int(decode_step))
+            if _defer:
+                return bs                                        # beam_decode_many reads the results later
             out = bs.results(emb=model.embed)
             _enc.check_status(dev)
             return out

@@ -232,25 +232,28 @@ size_t tile_smem(int K) { return (size_t)16 * ((K + 127) & ~127) * sizeof(float)
 
 // The LM's chain of a step (its layers and output layer) depends only on the hypotheses' last tokens and on its own
 // state, not on the attention / Speller chain: it runs on a second stream next to it.  One stream + fork / join events
-// per device, created on first use (host-side driver objects).
-struct LmStream { cudaStream_t stream; cudaEvent_t fork, join; std::atomic<int> ready; };
-LmStream g_lm[64];
+// per (device, caller stream), created on first use (host-side driver objects).
+struct LmStream { cudaStream_t stream; cudaEvent_t fork, join; int dev; cudaStream_t owner; };
+// one side stream per (device, caller stream): utterances decoded concurrently on different streams of one GPU
+// (beam.beam_decode_many) must not queue their LM chains behind each other
+constexpr int kMaxLmStreams = 64;
+LmStream g_lm[kMaxLmStreams];
+int g_lm_n = 0;
 std::mutex g_lm_mu;
 
-int lm_stream(LmStream** out) {
+int lm_stream(LmStream** out, cudaStream_t owner) {
   int dev = -1;
   B2_CUDA_TRY(cudaGetDevice(&dev));
-  B2_REQUIRE(dev >= 0 && dev < 64, B2ASR_EUNSUPPORTED, "decode: device ordinal %d outside [0,64)", dev);
-  LmStream& s = g_lm[dev];
-  if (!s.ready.load(std::memory_order_acquire)) {
-    std::lock_guard<std::mutex> lk(g_lm_mu);
-    if (!s.ready.load(std::memory_order_relaxed)) {
-      B2_CUDA_TRY(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
-      B2_CUDA_TRY(cudaEventCreateWithFlags(&s.fork, cudaEventDisableTiming));
-      B2_CUDA_TRY(cudaEventCreateWithFlags(&s.join, cudaEventDisableTiming));
-      s.ready.store(1, std::memory_order_release);
-    }
-  }
+  std::lock_guard<std::mutex> lk(g_lm_mu);
+  for (int i = 0; i < g_lm_n; ++i)
+    if (g_lm[i].dev == dev && g_lm[i].owner == owner) { *out = &g_lm[i]; return B2ASR_OK; }
+  B2_REQUIRE(g_lm_n < kMaxLmStreams, B2ASR_EUNSUPPORTED, "decode: more than %d (device, stream) pairs in use", kMaxLmStreams);
+  LmStream& s = g_lm[g_lm_n];
+  B2_CUDA_TRY(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+  B2_CUDA_TRY(cudaEventCreateWithFlags(&s.fork, cudaEventDisableTiming));
+  B2_CUDA_TRY(cudaEventCreateWithFlags(&s.join, cudaEventDisableTiming));
+  s.dev = dev; s.owner = owner;
+  ++g_lm_n;
   *out = &s;
   return B2ASR_OK;
 }
@@ -310,7 +313,7 @@ extern "C" int b2asr_decode_run(const b2asr_decode_prog* prog, int first_step, i
   LmStream* lm = nullptr;
   const bool has_lm = prog[0].n_linear > 1;
   if (has_lm && split) {
-    if (int rc = lm_stream(&lm)) return rc;
+    if (int rc = lm_stream(&lm, st)) return rc;
   }
   for (int t = first_step; t < first_step + steps; ++t) {
     const b2asr_decode_prog& p = prog[t & 1];

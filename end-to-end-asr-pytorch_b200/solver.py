@@ -464,7 +464,7 @@ class Tester(Solver):
 
     def __init__(self, config, paras):
         super(Tester, self).__init__(config, paras)
-        self.verbose('During beam decoding, batch size is set to 1; utterances are sharded across GPUs, --njobs is ignored.')
+        self.verbose('During beam decoding, batch size is set to 1; utterances are sharded across GPUs, --njobs utterances in flight per GPU.')
         self.njobs = self.paras.njobs
         self.decode_step_ratio = config['solver']['max_decode_step_ratio']
         self.decode_file = "_".join(['decode', 'beam', str(self.config['solver']['decode_beam_size']),
@@ -515,21 +515,58 @@ class Tester(Solver):
         if world > 1:                       # rank-local journal, appended per utterance: an abort loses nothing decoded
             import json
             journal = open(os.path.join(self.ckpdir, self.decode_file + '.rank%d.jsonl' % rank), 'w')
-        for i, (x, y) in enumerate(self.test_set):
-            if i % world != rank:
-                continue
-            ref = y[0].tolist()[0]
+        def one(i, x, ref):
             try:
-                item = self.beam_decode(x[0], ref, write=False)
+                return self.beam_decode(x, ref, write=False)
             except ValueError as e:         # a shape the kernels refuse (e.g. an over-long utterance): report, go on
                 self.verbose('Utterance {} skipped: {}'.format(i, e))
-                item = (self.mapper.translate(ref, return_string=True), [''])
+                return (self.mapper.translate(ref, return_string=True), [''])
+
+        def emit(i, item):
             if world == 1:
                 self._write(*item)          # appended utterance by utterance, like the reference (solver.py:360-367)
             else:
                 mine.append((i, item))
                 journal.write(json.dumps([i, item[0], item[1]]) + '\n')
                 journal.flush()
+
+        # --njobs N (the reference's worker processes, README.md:123) = up to N utterances in flight on this GPU,
+        # each on a CUDA stream of its own (beam.beam_decode_many); results are written in corpus order either way
+        group_size = max(1, min(int(getattr(self, 'njobs', 1) or 1), 8))
+        group = []
+
+        def flush():
+            if not group:
+                return
+            items = None
+            if len(group) > 1:
+                try:
+                    from . import beam as _beam
+                    utts = []
+                    for _, x, _ in group:
+                        xd = x.to(device=self.device, dtype=torch.float32)
+                        lens = infer_lengths(xd)
+                        utts.append((xd, int(np.ceil(lens[0] * self.decode_step_ratio)), lens))
+                    with torch.no_grad():
+                        outs = _beam.beam_decode_many(self.asr_model, utts, self.decode_beam_size, streams=len(group))
+                    items = [(self.mapper.translate(ref, return_string=True),
+                              [self.mapper.translate(h.outIndex, return_string=True) for h in hyps])
+                             for (_, _, ref), hyps in zip(group, outs)]
+                except ValueError:
+                    items = None            # one of them is refused: decode the group one by one to find and skip it
+            if items is None:
+                items = [one(i, x, ref) for i, x, ref in group]
+            for (i, _, _), item in zip(group, items):
+                emit(i, item)
+            del group[:]
+
+        for i, (x, y) in enumerate(self.test_set):
+            if i % world != rank:
+                continue
+            group.append((i, x[0], y[0].tolist()[0]))
+            if len(group) >= group_size:
+                flush()
+        flush()
         if world > 1:
             import torch.distributed as dist
             journal.close()

@@ -24,7 +24,7 @@ parser.add_argument('--logdir', default='log/', type=str, help='Logging path.')
 parser.add_argument('--ckpdir', default='result/', type=str, help='Checkpoint/Result path.')
 parser.add_argument('--load', default=None, type=str, help='Load pre-trained model')
 parser.add_argument('--seed', default=0, type=int, help='Random seed for reproducable results.')
-parser.add_argument('--njobs', default=1, type=int, help='Number of threads for decoding (ignored: decoding is device-resident).')
+parser.add_argument('--njobs', default=1, type=int, help='Utterances decoded concurrently per GPU (the reference: worker processes).')
 parser.add_argument('--cpu', action='store_true', help='Disable GPU training (unsupported in this build).')
 parser.add_argument('--test', action='store_true', help='Test the model.')
 parser.add_argument('--no-msg', action='store_true', help='Hide all messages.')

@@ -114,3 +114,27 @@ def test_native_decode_equals_per_step_path_at_m4_shape(cuda, monkeypatch):
         outs[native] = [(h.outIndex, float(h.avgScore())) for h in hyps]
     assert [a for a, _ in outs["1"]] == [a for a, _ in outs["0"]]
     assert all(abs(a - b) <= 1e-4 * abs(b) + 1e-5 for (_, a), (_, b) in zip(outs["1"], outs["0"]))
+
+
+def test_concurrent_decode_equals_sequential(cuda):
+    """beam.beam_decode_many (several utterances in flight on streams of their own) returns exactly what beam_decode
+    returns for each utterance on its own: same tokens, same scores."""
+    asr = importlib.import_module(PKG + ".asr")
+    rnnlm = importlib.import_module(PKG + ".rnnlm")
+    beam = importlib.import_module(PKG + ".beam")
+    torch.manual_seed(3)
+    cfg = {'encoder': {'enc_type': 'BiRNN', 'sample_rate': '2_2', 'sample_style': 'drop', 'dim': '32_32', 'dropout': '0_0', 'rnn_cell': 'LSTM'},
+           'attention': {'att_mode': 'loc', 'dim': 32, 'proj': True, 'num_head': 1},
+           'decoder': {'dim': 40, 'layer': 1, 'dropout': 0, 'rnn_cell': 'LSTMCell'}, 'optimizer': {'joint_ctc': 0.5}}
+    V = 50
+    model = asr.Seq2Seq(torch.zeros(1, 8, 20), V, cfg).to(cuda).eval()
+    model.joint_ctc, model.ctc_weight, model.decode_lm_weight = True, 0.5, 0.3
+    model.rnn_lm = rnnlm.RNN_LM(24, 24, V, layers=2).to(cuda).eval()
+    utts = [(torch.randn(1, T, 20, device=cuda), 12, [T]) for T in (96, 120, 64, 200, 88, 144, 100)]
+    with torch.no_grad():
+        seq = [model.beam_decode(x, steps, lens, 5) for x, steps, lens in utts]
+        par = beam.beam_decode_many(model, utts, 5, streams=3)
+    assert len(par) == len(seq)
+    for a, b in zip(seq, par):
+        assert [h.outIndex for h in a] == [h.outIndex for h in b]
+        assert [float(h.avgScore()) for h in a] == [float(h.avgScore()) for h in b]

@@ -63,3 +63,9 @@ def test_train_then_beam_decode_then_eval(cuda, tmp_path, dataset):
     assert len(nbest.read_text().splitlines()) >= 4
     out = _run([os.path.join(ROOT, "eval.py"), "--file", str(best)], str(tmp_path))
     assert "CER :" in out and "WER :" in out
+    # --njobs 3: three utterances in flight per GPU (beam.beam_decode_many) write byte-identical result files
+    one_by_one = (best.read_text(), nbest.read_text())
+    best.unlink(); nbest.unlink()
+    out = _run([os.path.join(ROOT, "main.py")] + common + ["--test", "--njobs", "3"], str(tmp_path))
+    assert "Decode done" in out
+    assert (best.read_text(), nbest.read_text()) == one_by_one
