@@ -104,7 +104,7 @@ class BeamSearch:
         # scratch + history
         self.cand = torch.zeros(n, K, **i32)
         self.psi = torch.zeros(n, K, **f32)
-        self.r_all = torch.zeros(n, T, K, 2, **f32)
+        self.r_all = torch.zeros(n, K, T, 2, **f32)
         self.topv = torch.zeros(n, n, **f32)
         self.topi = torch.zeros(n, n, **i32)
         self.step_ctr = torch.zeros(1, **i32)

@@ -50,10 +50,14 @@ __device__ __forceinline__ unsigned f2key(float f) {   // order-preserving float
   return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
 
+constexpr int kTopkCollect = 256;             // candidates the fast path collects before ranking them exactly
 struct TopkScratch {
   int cnt_iter[3];
   int cnt, minidx;
   float tv[kMaxK]; int ti[kMaxK];
+  unsigned lmax[kBeamNT];                     // fast path: every thread's largest key
+  unsigned thr;                               //   the k-th largest of those = a lower bound of the k-th largest key
+  float cv[kTopkCollect]; int ci[kTopkCollect];
 };
 
 constexpr int kKeysPerThread = 24;            // register-resident keys: V <= 24*256 = 6144, else the shared-memory loop
@@ -62,6 +66,12 @@ constexpr int kKeysPerThread = 24;            // register-resident keys: V <= 24
 // The k-th largest key is found by bisection over its 32 bits (one CTA-wide count per bit; the keys
 // stay in registers), everything above it is collected, ties at the threshold are taken lowest index
 // first, and the k survivors are ordered by a warp-level rank sort.
+//
+// Fast path (keys in registers, one CTA of kBeamNT threads): the k-th largest of the threads' LOCAL maxima is a lower
+// bound of the k-th largest key (k different threads hold a key at least that large), found by one warp without any
+// CTA-wide barrier; everything at or above it is collected (typically a few dozen entries) and ranked exactly by
+// (value desc, index asc) -- the same total order, hence the same result, as the bisection below, which remains for
+// large vocabularies and for inputs with more than kTopkCollect entries at or above the bound (long runs of ties).
 __device__ void cta_topk(const float* vals, int V, int k, float* outv, int* outi, TopkScratch* S) {
   const int tid = threadIdx.x, NT = blockDim.x;
   if (k > V) k = V;
@@ -71,6 +81,57 @@ __device__ void cta_topk(const float* vals, int V, int k, float* outv, int* outi
   for (int j = 0; j < kKeysPerThread; ++j) {
     const int i = tid + j * NT;
     keys[j] = (in_regs && i < V) ? f2key(vals[i]) : 0u;       // key 0 never reaches a threshold (>= 1)
+  }
+  if (in_regs && NT == kBeamNT && k >= 1) {
+    unsigned lm = 0u;
+#pragma unroll
+    for (int j = 0; j < kKeysPerThread; ++j) lm = max(lm, keys[j]);
+    S->lmax[tid] = lm;
+    if (tid == 0) S->cnt = 0;
+    __syncthreads();
+    if (tid < 32) {                                            // k-th largest of the kBeamNT local maxima, one warp
+      unsigned mine[kBeamNT / 32];
+#pragma unroll
+      for (int i = 0; i < kBeamNT / 32; ++i) mine[i] = S->lmax[tid + 32 * i];
+      unsigned prefix = 0u;
+      for (int it = 0; it < 32; ++it) {
+        const unsigned trial = prefix | (0x80000000u >> it);
+        int c = 0;
+#pragma unroll
+        for (int i = 0; i < kBeamNT / 32; ++i) c += mine[i] >= trial;
+        if (__reduce_add_sync(kFull, c) >= k) prefix = trial;
+      }
+      if (tid == 0) S->thr = prefix;
+    }
+    __syncthreads();
+    const unsigned thr = S->thr;
+    if (thr != 0u) {                                           // (0: fewer than k threads hold a key -- tiny V)
+#pragma unroll
+      for (int j = 0; j < kKeysPerThread; ++j) {
+        if (keys[j] >= thr) {
+          const int pos = atomicAdd(&S->cnt, 1);
+          if (pos < kTopkCollect) { S->cv[pos] = vals[tid + j * NT]; S->ci[pos] = tid + j * NT; }
+        }
+      }
+      __syncthreads();
+      const int C = S->cnt;
+      if (C <= kTopkCollect) {                                 // (C >= k by construction)
+        if (tid < C) {
+          const float v = S->cv[tid];
+          const int ix = S->ci[tid];
+          const unsigned kv = f2key(v);
+          int rank = 0;
+          for (int m = 0; m < C; ++m) {
+            const unsigned km = f2key(S->cv[m]);
+            rank += (km > kv) || (km == kv && S->ci[m] < ix);
+          }
+          if (rank < k) { outv[rank] = v; outi[rank] = ix; }
+        }
+        __syncthreads();
+        return;
+      }
+    }
+    __syncthreads();                                           // fall through to the bisection
   }
   unsigned prefix = 0u;
   if (tid == 0) { S->cnt_iter[0] = 0; S->cnt_iter[1] = 0; S->cnt_iter[2] = 0; }
@@ -236,23 +297,41 @@ __global__ void __launch_bounds__(kBeamNT) prefix_score_kernel(const float* x, i
 // ------------------------------------------------------------------------------------------------
 // Fused beam step
 // ------------------------------------------------------------------------------------------------
-// Stable descending rank of every child (asr.py:251): one warp per child; the lane's competitors (32*Q >= nc of
-// them) stay in registers while the warp walks its children.  A slot without a child holds -inf: it never
-// outranks anything and is never ranked itself.
-template <int Q>
-__device__ __forceinline__ void rank_children(const float* avg, const int* slotk, int* slot_child, int nc, int n) {
-  const int lane = threadIdx.x & 31;
-  float mine[Q];
-#pragma unroll
-  for (int q = 0; q < Q; ++q) { const int m = lane + 32 * q; mine[q] = m < nc ? avg[m] : -INFINITY; }
-  for (int c = threadIdx.x >> 5; c < nc; c += blockDim.x >> 5) {
-    if (slotk[c] == -2) continue;                              // warp-uniform
-    const float a = avg[c];
-    int rank = 0;
-#pragma unroll
-    for (int q = 0; q < Q; ++q) rank += (mine[q] > a) || (mine[q] == a && lane + 32 * q < c);
-    rank = __reduce_add_sync(kFull, rank);
-    if (lane == 0 && rank < n) slot_child[rank] = c;
+// The best n children in stable descending order of their mean score (asr.py:251), by ONE warp.  Every row's children
+// arrive sorted (cta_topk returns value desc, index asc, and the mean is a monotone function of the value), so this is
+// an n-way merge of n sorted lists: lane r holds the head of row r, the warp takes the largest head n times
+// (`redux.sync.max` on the order-preserving key; among equal heads the lowest row, i.e. the stable order) and only the
+// winner advances.  Slots without a child (<eos>, dead rows) are skipped, as the reference never creates them.
+__device__ __forceinline__ void rank_children(const float* avg, const int* slotk, int* slot_child, unsigned* ckey, int n) {
+  if (threadIdx.x >= 32) return;
+  const int lane = threadIdx.x;
+  const int base = lane * (n + 1);
+  // the row's children compacted to (key, position) pairs with a 0 terminator, so that the winner's advance is one
+  // load at a known address, issued a round before its value is needed
+  unsigned char* cpos = reinterpret_cast<unsigned char*>(ckey + n * (n + 1));
+  if (lane < n) {
+    int q = 0;
+    for (int p = 0; p < n; ++p) {
+      const int sk = slotk[lane * n + p];
+      const unsigned k = f2key(avg[lane * n + p]);
+      if (sk != -2) { ckey[base + q] = k; cpos[lane * n + q] = (unsigned char)p; ++q; }
+    }
+    ckey[base + q] = 0u;
+  }
+  __syncwarp();
+  int q = 0;
+  unsigned key = lane < n ? ckey[base] : 0u;                   // 0: row exhausted (every real key is > 0)
+  unsigned nkey = key != 0u ? ckey[base + 1] : 0u;
+  for (int j = 0; j < n; ++j) {
+    const unsigned mx = __reduce_max_sync(kFull, key);
+    if (mx == 0u) break;
+    const int w = __ffs(__ballot_sync(kFull, key == mx)) - 1;
+    if (lane == w) {
+      slot_child[j] = lane * n + cpos[lane * n + q];
+      ++q;
+      key = nkey;
+      nkey = key != 0u ? ckey[base + q + 1] : 0u;
+    }
   }
 }
 
@@ -304,7 +383,7 @@ __global__ void __launch_bounds__(kBeamNT) beam_step_kernel(b2asr_beam_io io) {
       // ---- prefix scores of prefix+[c] (ctc.py:65-101) ------------------------------------------------
       if (tid < 32)
         prefix_recursion(tb, T, K, plen, (int)io.last_in[row], cand_sm, psi_sm,
-                         io.r_all + (long long)row * T * K * 2, (long long)K * 2, 2);
+                         io.r_all + (long long)row * T * K * 2, 2, (long long)T * 2);   // [K][T][2]: a survivor's rows are contiguous
       __syncthreads();
       BT(4);
       // ---- fusion (asr.py:222-229): separate fp32 multiply and add roundings, as torch does -----------
@@ -354,27 +433,44 @@ __global__ void __launch_bounds__(kBeamNT) beam_step_kernel(b2asr_beam_io io) {
   const int nc = n * n;
   int* slot_child = slotk + nc;                                // [n] child index occupying each survivor slot
   int* cand_all = slot_child + n;                              // [n*K] every row's CTC candidates, staged once
-  if (ctc) for (int i = tid; i < n * K; i += NT) cand_all[i] = __ldcg(io.cand + i);
-  for (int j = tid; j < n; j += NT) slot_child[j] = -1;
-  __syncthreads();
-  for (int c = tid; c < nc; c += NT) {
-    const int r = c / n;
-    float a = -INFINITY; int sk = -2;                           // -2: no child here; -1: child, token not a CTC candidate
-    if (io.valid_in[r]) {
-      const int tok = __ldcg(io.topi + c);
-      if (tok >= 0 && tok != kEos) {
-        a = __fdiv_rn(__fadd_rn(io.sum_in[r], __ldcg(io.topv + c)), cnt);      // postprocess.py:71-74
-        sk = -1;
-        if (ctc) for (int j = 0; j < K; ++j) if (cand_all[r * K + j] == tok) { sk = j; break; }
-      }
+  unsigned* ckey = reinterpret_cast<unsigned*>(cand_all + (ctc ? n * K : 0));   // [n*(n+1)] + [n*n] bytes: rank_children's lists
+  for (int base = 0; base < nc; base += 2 * NT) {             // two children per thread; every load of a round is
+    int tok[2], vin[2]; float tv[2], sum[2];                   // issued before the first one is consumed
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const int c = min(base + u * NT + tid, nc - 1);
+      const int r = c / n;
+      vin[u] = io.valid_in[r];
+      tok[u] = __ldcg(io.topi + c);
+      tv[u] = __ldcg(io.topv + c);
+      sum[u] = io.sum_in[r];
     }
-    avg[c] = a; slotk[c] = sk;
+    if (base == 0) {
+      if (ctc) for (int i = tid; i < n * K; i += NT) cand_all[i] = __ldcg(io.cand + i);
+      for (int j = tid; j < n; j += NT) slot_child[j] = -1;
+      __syncthreads();
+    }
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const int c = base + u * NT + tid;
+      if (c >= nc) break;
+      const int r = c / n;
+      float a = -INFINITY; int sk = -2;                         // -2: no child here; -1: child, token not a CTC candidate
+      if (vin[u] && tok[u] >= 0 && tok[u] != kEos) {
+        a = __fdiv_rn(__fadd_rn(sum[u], tv[u]), cnt);           // postprocess.py:71-74
+        sk = -1;
+        if (ctc) {                                              // a row's candidates are distinct: no early exit needed,
+          const int* cr = cand_all + r * K;                     // so the K compares are independent
+          for (int j = 0; j < K; ++j) sk = cr[j] == tok[u] ? j : sk;
+        }
+      }
+      avg[c] = a; slotk[c] = sk;
+    }
   }
   BT(9);
   __syncthreads();
-  // stable descending rank of every child (asr.py:251): one warp per child, lanes stride the competitors.
-  // A slot without a child holds -inf: it never outranks anything and is never ranked itself.
-  if (nc <= 512) rank_children<16>(avg, slotk, slot_child, nc, n); else rank_children<32>(avg, slotk, slot_child, nc, n);
+  // the best n children in stable descending order (asr.py:251): n-way merge of the rows' sorted children
+  rank_children(avg, slotk, slot_child, ckey, n);
   __syncthreads();
   BT(10);
   const long long hoff = (long long)min(plen, io.max_steps - 1) * n;
@@ -395,33 +491,26 @@ __global__ void __launch_bounds__(kBeamNT) beam_step_kernel(b2asr_beam_io io) {
   }
   BT(11);
   if (ctc) {                                                   // survivors inherit r[cand slot] (postprocess.py:95-97)
-    // one warp-strided pass per survivor: (r[t,0], r[t,1]) is one 8-byte load from the parent's candidate slot
+    // r_all is candidate-major, so a survivor's T rows (r[t,0], r[t,1]) are one contiguous run of the parent's slot
     const float2* rall2 = reinterpret_cast<const float2*>(io.r_all);
     float2* rout2 = reinterpret_cast<float2*>(io.r_out);
-    // survivors' source offsets once, then a flat (survivor, frame) sweep with 8 loads in flight per thread
-    long long* src_of = reinterpret_cast<long long*>(reinterpret_cast<int*>(smf) + ((2 * nc + n + n * K + 1) & ~1));   // [n], 8-byte aligned
-    for (int j = tid; j < n; j += NT) {
+    // one warp per survivor: its T rows are one contiguous run, every lane keeps all of its loads in flight
+    const int warp = tid >> 5, lane = tid & 31, nw = NT >> 5;
+    for (int j = warp; j < n; j += nw) {
       const int c = slot_child[j];
-      src_of[j] = (c >= 0 && slotk[c] >= 0) ? ((long long)(c / n) * T * K + slotk[c]) : -1;
-    }
-    __syncthreads();
-    const int total = n * T;
-    for (int i0 = 0; i0 < total; i0 += 8 * NT) {
-      float2 v[8];
-#pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const int i = i0 + u * NT + tid;
-        v[u] = make_float2(kLogZero, kLogZero);
-        if (i < total) {
-          const int j = i / T, t = i - j * T;
-          const long long so = src_of[j];
-          if (so >= 0) v[u] = __ldcg(rall2 + so + (long long)t * K);
-        }
+      const int sk = c >= 0 ? slotk[c] : -1;
+      float2* dst = rout2 + (long long)j * T;
+      if (sk < 0) {
+        for (int t = lane; t < T; t += 32) dst[t] = make_float2(kLogZero, kLogZero);
+        continue;
       }
+      const float2* src = rall2 + ((long long)(c / n) * K + sk) * T;
+      for (int t0 = 0; t0 < T; t0 += 32 * 16) {
+        float2 v[16];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const int i = i0 + u * NT + tid;
-        if (i < total) rout2[i] = v[u];
+        for (int u = 0; u < 16; ++u) { const int t = t0 + u * 32 + lane; if (t < T) v[u] = __ldcg(src + t); }
+#pragma unroll
+        for (int u = 0; u < 16; ++u) { const int t = t0 + u * 32 + lane; if (t < T) dst[t] = v[u]; }
       }
     }
   }
@@ -489,7 +578,7 @@ extern "C" int b2asr_beam_step(const b2asr_beam_io* io, void* stream) {
     B2_REQUIRE(a.r_in && a.r_out && a.ctc_prob_in && a.cand && a.psi && a.r_all, B2ASR_EINVAL, "beam_step: joint CTC needs r_in/r_out/ctc_prob_in/cand/psi/r_all");
     floats += prefix_smem_floats(a.T);
   }
-  const size_t prune = (size_t)2 * a.n * a.n + a.n + (size_t)a.n * (a.x_ctc ? a.K : 0) + 2 + 2 * (size_t)a.n;
+  const size_t prune = (size_t)4 * a.n * a.n + 2 * a.n + (size_t)a.n * (a.x_ctc ? a.K : 0) + 2 + 2 * (size_t)a.n;
   if (floats < prune) floats = prune;
   const size_t smem = floats * sizeof(float);
   B2_REQUIRE(smem <= 200 * 1024, B2ASR_EUNSUPPORTED, "beam_step: V=%d, T=%d need %zu bytes of shared memory", a.V, a.T, smem);

@@ -250,7 +250,7 @@ typedef struct b2asr_beam_io {
   /* scratch */
   int32_t* cand;           /* [n,K] */
   float*   psi;            /* [n,K] */
-  float*   r_all;          /* [n,T,K,2] */
+  float*   r_all;          /* [n,K,T,2] scratch: every candidate's rows, candidate-major */
   float*   topv;           /* [n,n] */
   int32_t* topi;           /* [n,n] */
   int32_t* step;           /* [1] prefix length of the live rows; the kernel increments it */
