@@ -272,6 +272,237 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_fwd_kernel(const SeqArgs a) {
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// forward, tensor-core variant (default; B2ASR_ENC_MMA=0 selects the FFMA2 kernel above).
+//
+// The frame's product G[16 x 4UC] = h_{t-1}[16 x H] . W_slice^T runs on the warp-level tensor-core path
+// (mma.sync.m16n8k16, fp16 operands, fp32 accumulation; measured on B200 with tools/micro/mma_rate.cu: 2.0 clk per
+// instruction and SM = 1022 MAC/clk/SM, against the 71 MAC/clk/SM the FFMA2 loop reaches) with both operands split in
+// two fp16 terms, x = hi + lo (hi = rn16(x), lo = rn16(x - hi): 22 significant bits, absolute error <= 3e-8 for
+// |x| <= 1 -- h is in (-1,1), weights are O(1)), and three products per k-step: hi.hi + hi.lo + lo.hi (the dropped
+// lo.lo term is 2^-22 of the result; fp16 x fp16 products are exact in the fp32 accumulator).
+//   * the CTA's 4UC gate columns are H/32 m16n8 tiles (tile n = the four gates of units 2n, 2n+1).  Warp (pair, half)
+//     multiplies the TWO tiles of its pair over ONE half of K (ranks 0-7 or 8-15), so an A fragment feeds six
+//     instructions and the CTA reads h from shared memory five times per frame instead of ten (the loads, not the
+//     tensor pipe, bound the one-tile-per-warp version: 1.25 us); the two warps of a pair swap one partial tile through
+//     shared memory (named barrier of 64 threads) and each finishes one tile.  The W fragments, hi and lo, stay in
+//     registers for the whole sequence (4*H/16 = 80 registers at H=320);
+//   * h crosses the cluster ALREADY SPLIT: the cell owner writes (hi, lo) of its unit once, 4 bytes per value as before,
+//     so the exchange moves the same bytes and the receivers' A fragments are plain 128-bit shared-memory loads
+//     without a single conversion instruction.  Inside a rank's chunk the layout is [unit quad][row][hi0 hi1 hi2 hi3 lo0
+//     lo1 lo2 lo3] (16 bytes per row and quad);
+//   * k-step (m, q) takes quad q of the four ranks 4m..4m+3, one rank per thread-in-group: with the chunk stride
+//     == 8 words (mod 32) the 8 lanes of a shared-memory phase (2 rows x 4 ranks) hit 8 different 16-byte bank groups.
+//     The order of k inside a tile is free as long as A and B agree, and B is laid out once, in registers;
+//   * the accumulator fragment holds (i,f) or (g,o) of a unit for rows g and g+8: one shuffle pair with the neighbour
+//     lane gives every lane all four gates of ONE (row, unit) -- 320 lanes = 16 rows x 20 units, every lane a cell.
+// ---------------------------------------------------------------------------------------------------------
+// words between two ranks' chunks: room for rows up to 15 of the last quad (they are read when BS > 8), == 8 (mod 32)
+__host__ __device__ constexpr int mma_chunk_need(int UC, int BS) { return BS > 8 ? ((UC / 4 - 1) * BS + 16) * 4 : BS * UC; }
+__host__ __device__ constexpr int mma_chunk_stride(int UC, int BS) { return ((mma_chunk_need(UC, BS) - 8 + 31) / 32) * 32 + 8; }
+__device__ __forceinline__ void mma_f16(float (&c)[4], const unsigned (&a)[4], unsigned b0, unsigned b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ unsigned short f16_bits(float x) {
+  unsigned short h; asm("cvt.rn.f16.f32 %0, %1;" : "=h"(h) : "f"(x)); return h;
+}
+__device__ __forceinline__ float f16_value(unsigned short h) {
+  float x; asm("cvt.f32.f16 %0, %1;" : "=f"(x) : "h"(h)); return x;
+}
+__device__ __forceinline__ void split_f16(float x, unsigned short& hi, unsigned short& lo) {
+  hi = f16_bits(x);
+  lo = f16_bits(x - f16_value(hi));
+}
+
+template <int H, int BS>
+__global__ void __launch_bounds__(H, 1) lstm_cl_fwd_mma_kernel(const SeqArgs a) {
+  constexpr int UC = H / NCL;                 // units per CTA
+  constexpr int QC = UC / 4;                  // unit quads per rank
+  constexpr int KS = 4 * QC;                  // k16-steps: (m, q) = quad q of ranks 4m..4m+3
+  constexpr int CH = BS * UC;                 // 32-bit words one CTA contributes per frame
+  constexpr int S = mma_chunk_stride(UC, BS);
+  static_assert(H / 32 == (4 * UC) / 8 && UC % 4 == 0 && BS % 4 == 0 && BS <= 16, "one m16n8 tile per warp");
+  extern __shared__ __align__(128) float smem[];
+  __shared__ __align__(8) unsigned long long full[2];
+  unsigned* h_s = reinterpret_cast<unsigned*>(smem);          // [2][NCL][S]
+  unsigned* stage = h_s + 2 * NCL * S;                        // [2][CH]
+  constexpr int NP = H / 64;                  // warp pairs
+  __shared__ float4 xch[H / 32][32];          // the partial tile a warp hands to its partner
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5, g = lane >> 2, tig = lane & 3;
+  const int np = w % NP, kh = w / NP;         // tiles 2np, 2np+1; ranks [8kh, 8kh+8) of K
+  const int tn = 2 * np + kh;                 // the tile this warp finishes
+  const unsigned rank = cluster_ctarank();
+  const int dir = blockIdx.z, b0 = blockIdx.y, bstep = gridDim.y, u0 = (int)rank * UC;
+  const int T = a.T, ND = a.ND;
+  const long long ldo = (long long)ND * H;
+
+  // B fragments: column n = g of tile x is gate (g & 3) of unit 2x + (g >> 2)
+  unsigned bh[2][KS / 2][2], bl[2][KS / 2][2];
+#pragma unroll
+  for (int x = 0; x < 2; ++x) {
+    const float* Wr = a.w_hh[dir] + ((long long)(g & 3) * H + u0 + 2 * (2 * np + x) + (g >> 2)) * H;
+#pragma unroll
+    for (int m = 0; m < 2; ++m)
+#pragma unroll
+      for (int q = 0; q < QC; ++q) {
+        const float4 v = __ldg(reinterpret_cast<const float4*>(Wr + (4 * (2 * kh + m) + tig) * UC + 4 * q));
+        unsigned short h0, h1, h2, h3, l0, l1, l2, l3;
+        split_f16(v.x, h0, l0); split_f16(v.y, h1, l1); split_f16(v.z, h2, l2); split_f16(v.w, h3, l3);
+        const int kk = m * QC + q;
+        bh[x][kk][0] = (unsigned)h0 | ((unsigned)h1 << 16); bh[x][kk][1] = (unsigned)h2 | ((unsigned)h3 << 16);
+        bl[x][kk][0] = (unsigned)l0 | ((unsigned)l1 << 16); bl[x][kk][1] = (unsigned)l2 | ((unsigned)l3 << 16);
+      }
+  }
+  for (int idx = tid; idx < 2 * NCL * S; idx += H) h_s[idx] = 0u;
+  if (tid == 0) {
+    mbar_init(&full[0], 1); mbar_init(&full[1], 1);
+    mbar_fence_init();
+    mbar_expect_tx(&full[0], NCL * CH * 4);   // frame 1 reads buffer 1, frame 2 buffer 0
+    mbar_expect_tx(&full[1], NCL * CH * 4);
+  }
+
+  // cell role: even thread-in-group -> row g, odd -> row g + 8; unit 2*tile + tig/2
+  const int row = g + 8 * (tig & 1), ul = 2 * tn + (tig >> 1);
+  const int gb = b0 + row * bstep, unit = u0 + ul;
+  const bool valid = row < BS && gb < a.B;
+  const int len = valid ? a.lens[gb] : 0;
+  float bias[4] = {0.f, 0.f, 0.f, 0.f};
+  if (valid) {
+#pragma unroll
+    for (int gt = 0; gt < 4; ++gt) {
+      if (a.b_ih[dir]) bias[gt] += a.b_ih[dir][gt * H + unit];
+      if (a.b_hh[dir]) bias[gt] += a.b_hh[dir][gt * H + unit];
+    }
+  }
+  // where this lane's (hi, lo) halves go inside the CTA's slice: [quad][row][hi x4 | lo x4]
+  const int st_half = ((ul >> 2) * BS + row) * 8 + (ul & 3);
+  float c = 0.f;
+  unsigned phase = 0;
+  long long cyc_wait = 0, cyc_mac = 0, cyc_rest = 0;
+  __syncthreads();
+  cluster_arrive();
+  cluster_wait();                             // every CTA's barriers are armed before the first remote copy
+
+  float pre[4] = {0.f, 0.f, 0.f, 0.f};
+  {
+    const int t0 = dir ? T - 1 : 0;
+    if (valid && t0 < len) {
+      const float* g0 = a.gates + (((long long)gb * T + t0) * ND + dir) * 4 * H + unit;
+#pragma unroll
+      for (int gt = 0; gt < 4; ++gt) pre[gt] = g0[(long long)gt * H];
+    }
+  }
+  for (int s = 0; s < T; ++s) {
+    const int t = dir ? T - 1 - s : s;
+    const int p = s & 1;
+    const bool active = valid && t < len;
+    float* grow = a.gates + (((long long)gb * T + t) * ND + dir) * 4 * H + unit;
+    float nxt[4] = {0.f, 0.f, 0.f, 0.f};
+    {
+      const int t1 = dir ? t - 1 : t + 1;
+      if (s + 1 < T && valid && t1 < len) {
+        const float* g1 = a.gates + (((long long)gb * T + t1) * ND + dir) * 4 * H + unit;
+#pragma unroll
+        for (int gt = 0; gt < 4; ++gt) nxt[gt] = g1[(long long)gt * H];
+      }
+    }
+    const long long c0 = clock64();
+    if (s > 0) {                              // h_{t-1}: all 16 slices have landed in h_s[p]
+      if (!mbar_wait_bounded(&full[p], (phase >> p) & 1u)) { atomicExch(a.status, 1); return; }
+      phase ^= 1u << p;
+      if (tid == 0) mbar_expect_tx(&full[p], NCL * CH * 4);    // re-arm for frame s+2
+    }
+    const long long c1 = clock64();
+    float acc[2][3][4];
+#pragma unroll
+    for (int x = 0; x < 2; ++x)
+#pragma unroll
+      for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[x][i][j] = 0.f;
+    {
+      const uint4* hb = reinterpret_cast<const uint4*>(h_s + p * (NCL * S) + (8 * kh + tig) * S) + g;
+#pragma unroll
+      for (int m = 0; m < 2; ++m)
+#pragma unroll
+        for (int q = 0; q < QC; ++q) {
+          const int kk = m * QC + q;
+          const uint4 r0 = hb[(m * 4 * S) / 4 + q * BS];
+          uint4 r1 = make_uint4(0u, 0u, 0u, 0u);
+          if (BS > 8) r1 = hb[(m * 4 * S) / 4 + q * BS + 8];
+          const unsigned ah[4] = {r0.x, r1.x, r0.y, r1.y};
+          const unsigned al[4] = {r0.z, r1.z, r0.w, r1.w};
+#pragma unroll
+          for (int x = 0; x < 2; ++x) {
+            mma_f16(acc[x][0], ah, bh[x][kk][0], bh[x][kk][1]);
+            mma_f16(acc[x][1], ah, bl[x][kk][0], bl[x][kk][1]);
+            mma_f16(acc[x][2], al, bh[x][kk][0], bh[x][kk][1]);
+          }
+        }
+    }
+    float gsum[4];
+    {
+      float v[4], o[4];                       // v: the tile this warp finishes, o: its partner's
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float s0 = acc[0][0][j] + (acc[0][1][j] + acc[0][2][j]), s1 = acc[1][0][j] + (acc[1][1][j] + acc[1][2][j]);
+        v[j] = kh ? s1 : s0; o[j] = kh ? s0 : s1;
+      }
+      xch[w][lane] = make_float4(o[0], o[1], o[2], o[3]);
+      named_sync(1 + np, 64);
+      const float4 pr = xch[(1 - kh) * NP + np][lane];
+      v[0] += pr.x; v[1] += pr.y; v[2] += pr.z; v[3] += pr.w;
+      const bool odd = tig & 1;
+      const float r0 = __shfl_xor_sync(kFull, odd ? v[0] : v[2], 1);
+      const float r1 = __shfl_xor_sync(kFull, odd ? v[1] : v[3], 1);
+      gsum[0] = odd ? r0 : v[0]; gsum[1] = odd ? r1 : v[1];
+      gsum[2] = odd ? v[2] : r0; gsum[3] = odd ? v[3] : r1;
+    }
+    const long long c2 = clock64();
+    float sv[4] = {0.f, 0.f, 0.f, 0.f}, hval = 0.f;
+    if (active) {
+      const float gi = sigmoid_f(gsum[0] + pre[0] + bias[0]);
+      const float gf = sigmoid_f(gsum[1] + pre[1] + bias[1]);
+      const float gg = tanh_acc(gsum[2] + pre[2] + bias[2]);
+      const float go = sigmoid_f(gsum[3] + pre[3] + bias[3]);
+      c = fmaf(gf, c, gi * gg);
+      hval = go * tanh_acc(c);
+      sv[0] = gi; sv[1] = gf; sv[2] = gg; sv[3] = go;
+    } else {
+      c = 0.f;
+    }
+    if (row < BS) {
+      unsigned short hi, lo;
+      split_f16(hval, hi, lo);
+      unsigned short* sh = reinterpret_cast<unsigned short*>(stage + p * CH) + st_half;
+      sh[0] = hi; sh[4] = lo;
+    }
+    if (active) {
+      grow[0] = sv[0]; grow[(long long)H] = sv[1]; grow[2ll * H] = sv[2]; grow[3ll * H] = sv[3];
+      a.cells[(((long long)gb * T + t) * ND + dir) * H + unit] = c;
+    }
+    if (valid) a.out[((long long)gb * T + t) * ldo + dir * H + unit] = hval;
+    if (s + 1 < T) {
+      fence_proxy_async_smem();               // the cell outputs above are read by the async proxy below
+      __syncthreads();
+      // this CTA's slice of h_t -> chunk `rank` of h_s[1-p] in every CTA of the cluster (two lanes per warp issue)
+      const int d = w + (lane & 1) * (H / 32);
+      if (lane < 2 && d < NCL)
+        bulk_s2cluster(h_s + (p ^ 1) * (NCL * S) + (int)rank * S, stage + p * CH, CH * 4, &full[p ^ 1], (unsigned)d);
+    }
+#pragma unroll
+    for (int gt = 0; gt < 4; ++gt) pre[gt] = nxt[gt];
+    const long long c6 = clock64();
+    cyc_wait += c1 - c0; cyc_mac += c2 - c1; cyc_rest += c6 - c2;
+  }
+  cluster_arrive();
+  cluster_wait();                             // nobody leaves while a copy may still read or write its shared memory
+  if (tid == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) {   // CTA 0's cycle split (clock64)
+    a.status[4] = (int)cyc_wait; a.status[5] = (int)cyc_mac; a.status[6] = (int)cyc_rest;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // backward.  block = H threads: thread j owns column j of this CTA's rows of W_hh (partial dh of unit j, BS rows);
 // the first BS*UC threads double as the cell-backward owners of (row, unit).
 // ---------------------------------------------------------------------------------------------------------
@@ -444,8 +675,11 @@ __global__ void __launch_bounds__(H + kIssueWarp, 1) lstm_cl_bwd_kernel(const Se
 template <int H, int BS>
 int launch(const SeqArgs& a, bool backward, cudaStream_t st, bool probe_only, int* fit_out) {
   constexpr int UC = H / NCL;
-  void (*fn)(const SeqArgs) = backward ? lstm_cl_bwd_kernel<H, BS> : lstm_cl_fwd_kernel<H, BS>;
+  static const bool mma = [] { const char* e = getenv("B2ASR_ENC_MMA"); return !(e && e[0] == '0'); }();
+  void (*fn)(const SeqArgs) = backward ? lstm_cl_bwd_kernel<H, BS>
+                              : mma    ? lstm_cl_fwd_mma_kernel<H, BS> : lstm_cl_fwd_kernel<H, BS>;
   const size_t smem = backward ? (size_t)(4 * UC * BS + 4 * NCL * BS * UC) * sizeof(float)
+                      : mma    ? (size_t)(2 * NCL * mma_chunk_stride(UC, BS) + 2 * BS * UC) * sizeof(float)
                                : (size_t)(2 * NCL * chunk_stride(UC, BS) + 2 * BS * UC) * sizeof(float);
   B2_CUDA_TRY(cudaFuncSetAttribute((const void*)fn, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
   B2_CUDA_TRY(cudaFuncSetAttribute((const void*)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
