@@ -672,13 +672,229 @@ __global__ void __launch_bounds__(H + kIssueWarp, 1) lstm_cl_bwd_kernel(const Se
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// backward, tensor-core variant (default; B2ASR_ENC_MMA=0 selects the FFMA2 kernel above).
+//
+// partial dh[16 x H] = dG_slice[16 x 4UC] . W_slice[4UC x H] on mma.sync.m16n8k16 (fp16 hi/lo split of both operands,
+// three products per k-step, fp32 accumulation -- see the forward kernel).  Warp w owns columns [32w, 32w+32) (four
+// n-tiles) over all of K = 4UC; its W fragments stay in registers (80 at H=320).  Gate gradients span many orders of
+// magnitude, fp16 does not: every batch row is multiplied by an exact power of two that brings ITS largest |dG| of the
+// frame to [2^13, 2^14) before the split (the owners of the row publish that maximum with one shared-memory atomicMax
+// each) and the product row is multiplied back, so the result carries 22 bits relative to the row's own scale and no
+// row can push another one out of range.  A (16 x 80 fp32, this CTA's own d_gates of the last frame) is converted at
+// fragment load -- it is small, ten 128-bit loads per warp and frame.  The exchange is the same reduce-scatter as in
+// the FFMA2 kernel, in one part: all rows of a tile finish together, the extra warp issues the 16 copies.
+// ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void split_f16x2(float x0, float x1, unsigned& hi2, unsigned& lo2) {
+  asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(hi2) : "f"(x1), "f"(x0));           // lower half = x0
+  unsigned short h0, h1;
+  asm("mov.b32 {%0, %1}, %2;" : "=h"(h0), "=h"(h1) : "r"(hi2));
+  const float l0 = x0 - f16_value(h0), l1 = x1 - f16_value(h1);
+  asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(lo2) : "f"(l1), "f"(l0));
+}
+
+template <int H, int BS>
+__global__ void __launch_bounds__(H + kIssueWarp, 1) lstm_cl_bwd_mma_kernel(const SeqArgs a) {
+  constexpr int UC = H / NCL, LR = 4 * UC, CH = BS * UC;
+  constexpr int KSB = LR / 16;                // k16-steps
+  constexpr int RSA = LR % 32 == 16 ? LR : LR + 16;   // A row stride (words): rows 2j, 2j+1 of a phase 16 banks apart
+  static_assert(BS % 4 == 0 && BS * UC <= H && LR % 16 == 0 && UC % 2 == 0, "cell owners fit the block; whole k-steps");
+  extern __shared__ __align__(128) float smem[];
+  __shared__ __align__(8) unsigned long long full[2];
+  __shared__ unsigned rmax[2][16];            // per frame parity: bits of the largest |dG| of every row
+  float* dga = smem;                          // [16][RSA]  d_gates this CTA produced last frame, k = gate*UC + uu
+  float* Ps = smem + 16 * RSA;                // [2][NCL][BS][UC]  partial dh, grouped by owner rank
+  float* recv = Ps + 2 * NCL * CH;            // [2][NCL][BS][UC]  partials of MY units from every rank
+  const int tid = threadIdx.x;
+  const unsigned rank = cluster_ctarank();
+  const int dir = blockIdx.z, b0 = blockIdx.y, bstep = gridDim.y, u0 = (int)rank * UC;
+  const int T = a.T, ND = a.ND;
+  const long long ldo = (long long)ND * H;
+  const int lane = tid & 31, w = (tid >> 5) % (H / 32), g = lane >> 2, tig = lane & 3;
+
+  // B fragments: B[k][n] = W_hh[gate(k)*H + u0 + uu(k)][32w + 8x + n], k-step kk holds k = 16kk + 4tig + {0..3}
+  unsigned bh[4][KSB][2], bl[4][KSB][2];
+  if (tid < H) {
+    const float* W = a.w_hh[dir];
+#pragma unroll
+    for (int x = 0; x < 4; ++x)
+#pragma unroll
+      for (int kk = 0; kk < KSB; ++kk) {
+        float v[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int k = 16 * kk + 4 * tig + i;
+          v[i] = __ldg(W + ((long long)(k / UC) * H + u0 + (k % UC)) * H + 32 * w + 8 * x + g);
+        }
+        split_f16x2(v[0], v[1], bh[x][kk][0], bl[x][kk][0]);
+        split_f16x2(v[2], v[3], bh[x][kk][1], bl[x][kk][1]);
+      }
+  }
+  for (int idx = tid; idx < 16 * RSA; idx += H + kIssueWarp) dga[idx] = 0.f;
+  if (tid < 32) { rmax[0][tid & 15] = 0u; rmax[1][tid & 15] = 0u; }
+  if (tid == 0) {
+    mbar_init(&full[0], 1);
+    mbar_init(&full[1], 1);
+    mbar_fence_init();
+    mbar_expect_tx(&full[1], NCL * CH * 4);   // frame 1 uses buffer 1, frame 2 buffer 0
+    mbar_expect_tx(&full[0], NCL * CH * 4);
+  }
+  const bool pw = tid < CH;
+  const int row = tid / UC, uu = tid - row * UC;
+  const int gb = b0 + row * bstep, unit = u0 + uu;
+  const bool valid = pw && gb < a.B;
+  const int len = valid ? a.lens[gb] : 0;
+  float dc = 0.f;
+  unsigned phase = 0;
+  long long cyc_wait = 0, cyc_mac = 0, cyc_rest = 0, cyc_r0 = 0, cyc_r1 = 0, cyc_r2 = 0, cyc_r3 = 0;
+  __syncthreads();
+  cluster_arrive();
+  cluster_wait();
+
+  bool dead = false;                          // a wait timed out: keep walking (status says so), never hang a peer
+  if (tid >= H) {
+    // the reduce-scatter's copies are issued by this warp: a thread that issues a cp.async.bulk into a peer is held
+    // until the CTA's ~21 B/clk path has taken the copy
+    for (int s = 1; s < T; ++s) {
+      const int p = s & 1;
+      named_sync(1, H + kIssueWarp);
+      if (lane < NCL)
+        bulk_s2cluster(recv + p * (NCL * CH) + (int)rank * CH, Ps + p * (NCL * CH) + lane * CH, CH * 4, &full[p], (unsigned)lane);
+    }
+  } else {
+  for (int s = 0; s < T; ++s) {
+    const int t = dir ? s : T - 1 - s;
+    const int tcp = dir ? t + 1 : t - 1;      // frame whose cell state entered frame t in the forward walk
+    const int p = s & 1;
+    const bool active = valid && t < len;
+    float gi = 0.f, gf = 0.f, gg = 0.f, go = 0.f, ct = 0.f, cp = 0.f, dh = 0.f;
+    const long long grow = (((long long)gb * T + t) * ND + dir) * 4 * H + unit;
+    if (active) {
+      const float* gp = a.gates + grow;
+      gi = __ldg(gp); gf = __ldg(gp + H); gg = __ldg(gp + 2ll * H); go = __ldg(gp + 3ll * H);
+      ct = __ldg(a.cells + (((long long)gb * T + t) * ND + dir) * H + unit);
+      if (tcp >= 0 && tcp < len) cp = __ldg(a.cells + (((long long)gb * T + tcp) * ND + dir) * H + unit);
+      dh = __ldg(a.d_out + ((long long)gb * T + t) * ldo + dir * H + unit);
+    }
+    const long long c0 = clock64();
+    long long c1 = c0, c2 = c0;
+    if (s > 0) {
+      // the rows' scales: 2^(13 - floor(log2 max|dG|)) and its inverse, both exact powers of two
+      float sc[2], inv[2];
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const unsigned m = rmax[p ^ 1][g + 8 * h];
+        int sf = 267 - (int)(m >> 23);
+        sf = m == 0u ? 127 : min(253, max(1, sf));
+        sc[h] = __uint_as_float((unsigned)sf << 23);
+        inv[h] = __uint_as_float((unsigned)(254 - sf) << 23);
+      }
+      float acc[4][2][4];
+#pragma unroll
+      for (int x = 0; x < 4; ++x)
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) acc[x][i][j] = 0.f;
+      const float4* ap = reinterpret_cast<const float4*>(dga + g * RSA) + tig;
+#pragma unroll
+      for (int kk = 0; kk < KSB; ++kk) {
+        const float4 r0 = ap[4 * kk];
+        float4 r1 = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (BS > 8) r1 = ap[4 * kk + 8 * RSA / 4];
+        unsigned ah[4], al[4];
+        split_f16x2(r0.x * sc[0], r0.y * sc[0], ah[0], al[0]);
+        split_f16x2(r1.x * sc[1], r1.y * sc[1], ah[1], al[1]);
+        split_f16x2(r0.z * sc[0], r0.w * sc[0], ah[2], al[2]);
+        split_f16x2(r1.z * sc[1], r1.w * sc[1], ah[3], al[3]);
+#pragma unroll
+        for (int x = 0; x < 4; ++x) {
+          mma_f16(acc[x][0], ah, bh[x][kk][0], bh[x][kk][1]);
+          mma_f16(acc[x][1], ah, bl[x][kk][0], bl[x][kk][1]);
+          mma_f16(acc[x][1], al, bh[x][kk][0], bh[x][kk][1]);
+        }
+      }
+      // partials -> Ps, grouped by owner rank: columns (c, c+1) of rows g and g+8
+      float* pb = Ps + p * (NCL * CH);
+#pragma unroll
+      for (int x = 0; x < 4; ++x) {
+        const int cidx = 32 * w + 8 * x + 2 * tig, d = cidx / UC, cu = cidx - d * UC;
+        if (g < BS)
+          *reinterpret_cast<float2*>(pb + d * CH + g * UC + cu) =
+              make_float2((acc[x][0][0] + acc[x][1][0]) * inv[0], (acc[x][0][1] + acc[x][1][1]) * inv[0]);
+        if (g + 8 < BS)
+          *reinterpret_cast<float2*>(pb + d * CH + (g + 8) * UC + cu) =
+              make_float2((acc[x][0][2] + acc[x][1][2]) * inv[1], (acc[x][0][3] + acc[x][1][3]) * inv[1]);
+      }
+      fence_proxy_async_smem();
+      named_arrive(1, H + kIssueWarp);          // the issue warp sends the 16 slices
+      c1 = clock64();
+      if (!dead && !mbar_wait_bounded(&full[p], (phase >> p) & 1u)) { atomicExch(a.status, 1); dead = true; }
+      phase ^= 1u << p;
+      if (tid == 0) mbar_expect_tx(&full[p], NCL * CH * 4);     // re-arm for frame s+2
+      c2 = clock64();
+      if (pw) {
+        const float* rb = recv + p * (NCL * CH) + row * UC + uu;
+        float sum = 0.f;
+#pragma unroll
+        for (int src = 0; src < NCL; ++src) sum += rb[src * CH];
+        dh += sum;
+      }
+    }
+    const long long c3 = clock64();
+    long long c4 = c3, c5 = c3;
+    if (tid < 16) rmax[p ^ 1][tid] = 0u;        // every warp has read it (own copies issued => all MACs of the frame done)
+    if (pw) {
+      float di = 0.f, df = 0.f, dgg = 0.f, dob = 0.f;
+      if (active) {
+        const float tc = tanh_acc(ct);
+        const float dct = dc + dh * go * (1.f - tc * tc);
+        di = dct * gg * gi * (1.f - gi);
+        df = dct * cp * gf * (1.f - gf);
+        dgg = dct * gi * (1.f - gg * gg);
+        dob = dh * tc * go * (1.f - go);
+        dc = dct * gf;
+      } else {
+        dc = 0.f;
+      }
+      c4 = clock64();
+      {
+        float* dq = dga + row * RSA + uu;
+        dq[0] = di; dq[UC] = df; dq[2 * UC] = dgg; dq[3 * UC] = dob;
+        const float mx = fmaxf(fmaxf(fabsf(di), fabsf(df)), fmaxf(fabsf(dgg), fabsf(dob)));
+        if (mx > 0.f) atomicMax(&rmax[p][row], __float_as_uint(mx));
+      }
+      c5 = clock64();
+      if (valid) {
+        float* o = a.d_gates + grow;
+        o[0] = di; o[(long long)H] = df; o[2ll * H] = dgg; o[3ll * H] = dob;
+      }
+    }
+    const long long c6 = clock64();
+    named_sync(3, H);                         // compute warps only: dga and the row maxima are complete before the next frame
+    const long long c7 = clock64();
+    cyc_mac += c1 - c0; cyc_wait += c2 - c1; cyc_rest += c7 - c2;
+    cyc_r0 += c4 - c2; cyc_r1 += c5 - c4; cyc_r2 += c6 - c5; cyc_r3 += c7 - c6;
+  }
+  }
+  cluster_arrive();
+  cluster_wait();                             // nobody leaves while a copy may still read or write its shared memory
+  if (tid == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) {
+    a.status[8] = (int)cyc_wait; a.status[9] = (int)cyc_mac; a.status[10] = (int)cyc_rest;
+    a.status[11] = (int)cyc_r0; a.status[12] = (int)cyc_r1; a.status[13] = (int)cyc_r2; a.status[14] = (int)cyc_r3;
+  }
+}
+
 template <int H, int BS>
 int launch(const SeqArgs& a, bool backward, cudaStream_t st, bool probe_only, int* fit_out) {
   constexpr int UC = H / NCL;
   static const bool mma = [] { const char* e = getenv("B2ASR_ENC_MMA"); return !(e && e[0] == '0'); }();
-  void (*fn)(const SeqArgs) = backward ? lstm_cl_bwd_kernel<H, BS>
+  static const bool mma_bwd = [] { const char* e = getenv("B2ASR_ENC_MMA_BWD"); return !(e && e[0] == '0'); }();
+  constexpr int LR = 4 * UC, RSA = LR % 32 == 16 ? LR : LR + 16;
+  void (*fn)(const SeqArgs) = backward ? (mma && mma_bwd ? lstm_cl_bwd_mma_kernel<H, BS> : lstm_cl_bwd_kernel<H, BS>)
                               : mma    ? lstm_cl_fwd_mma_kernel<H, BS> : lstm_cl_fwd_kernel<H, BS>;
-  const size_t smem = backward ? (size_t)(4 * UC * BS + 4 * NCL * BS * UC) * sizeof(float)
+  const size_t smem = backward ? (mma && mma_bwd ? (size_t)(16 * RSA + 4 * NCL * BS * UC) * sizeof(float)
+                                                 : (size_t)(4 * UC * BS + 4 * NCL * BS * UC) * sizeof(float))
                       : mma    ? (size_t)(2 * NCL * mma_chunk_stride(UC, BS) + 2 * BS * UC) * sizeof(float)
                                : (size_t)(2 * NCL * chunk_stride(UC, BS) + 2 * BS * UC) * sizeof(float);
   B2_CUDA_TRY(cudaFuncSetAttribute((const void*)fn, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
