@@ -76,7 +76,7 @@ def main():
                  polls[1] / (256.0 * T), polls[2] / (256.0 * 4 * T)), flush=True)
         print("          CTA 0 us per frame {exchange, MACs, rest}: fwd %s  bwd %s" % (
             ["%.2f" % (c / 1965.0 / T) for c in polls[4:7]], ["%.2f" % (c / 1965.0 / T) for c in polls[8:11]]), flush=True)
-        print("          fwd rest = {cell, fence+sync, issue, stores}: %s" % ["%.2f" % (c / 1965.0 / T) for c in polls[11:15]], flush=True)
+        print("          rest of the last kernel that wrote it (bwd: recv sum+cell, dG store+row max, global stores, barrier): %s" % ["%.2f" % (c / 1965.0 / T) for c in polls[11:15]], flush=True)
     print("five layers: native %.1f ms, cudnn %.1f ms" % (tot["native"], tot["cudnn"]))
 
 
