@@ -210,3 +210,52 @@ def test_recurrence_kernels_are_bit_reproducible():
     for other in runs[1:]:
         for a, b in zip(runs[0], other):
             assert torch.equal(a, b)
+
+
+def test_tensor_core_recurrence_long_sequence_and_row_scales():
+    """The cluster kernels multiply on mma.sync with fp16 hi/lo operands (enc_cluster.cu): 400 frames of error
+    accumulation, and upstream gradients whose magnitude differs by up to 1e8 between batch rows and by 1e3 between
+    frames of a row -- every ROW of dx must meet 1e-4 of ITS OWN largest entry (the backward kernel scales each row by
+    its own power of two before the fp16 split; one scale per frame would flush the small rows)."""
+    enc = importlib.import_module(PKG + "._enc")
+    dev = torch.device("cuda:0")
+    B, T, n_in, H = 12, 400, 32, 320
+    layer64 = eo.make_layer(n_in, H, True, seed=11)
+    lens = _lens(B, T, seed=5)
+    g = torch.Generator().manual_seed(9)
+    x64 = torch.randn(B, T, n_in, generator=g, dtype=torch.float64)
+    for b, n in enumerate(lens):
+        x64[b, n:] = 0
+    row_scale = 10.0 ** torch.linspace(-8, 0, B, dtype=torch.float64)
+    frame_scale = 10.0 ** (-3 * torch.rand(B, T, generator=g, dtype=torch.float64))
+    w64 = torch.randn(B, T, 2 * H, generator=g, dtype=torch.float64) * (row_scale[:, None] * frame_scale)[:, :, None]
+    x64.requires_grad_(True)
+    ref = eo.reference_call(layer64, x64, lens)
+    (ref * w64).sum().backward()
+
+    layer = torch.nn.LSTM(n_in, H, bidirectional=True, num_layers=1, batch_first=True).to(dev)
+    layer.load_state_dict({k: v.float() for k, v in layer64.state_dict().items()})
+    x = x64.detach().float().to(dev).requires_grad_(True)
+    out = enc.lstm_layer(layer, x, lens)
+    (out * w64.float().to(dev)).sum().backward()
+    torch.cuda.synchronize()
+    enc.check_status(dev)
+    _close(out, ref, "out")
+    for b in range(B):
+        _close(x.grad[b], x64.grad[b], "dx row %d (upstream scale %.0e)" % (b, float(row_scale[b])))
+    for (name, p), (_, p64) in zip(layer.named_parameters(), layer64.named_parameters()):
+        _close(p.grad, p64.grad, "d" + name)
+
+
+def test_ffma_recurrence_kernels_still_match():
+    """B2ASR_ENC_MMA=0 selects the packed-FFMA cluster kernels (read once per process, hence the child process)."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, B2ASR_ENC_MMA="0")
+    r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-x", "-m", "gpu", os.path.abspath(__file__), "-k",
+                        "match_reference_call and auto and (32-50-640-320 or 16-60-39-256 or 20-3-24-320)"],
+                       cwd=root, env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "3 passed" in r.stdout, r.stdout[-500:]
