@@ -11,7 +11,10 @@ WANT = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
         "sm__throughput.avg.pct_of_peak_sustained_elapsed", "sm__warps_active.avg.pct_of_peak_sustained_active",
         "launch__registers_per_thread", "launch__grid_size", "launch__block_size", "launch__cluster_size",
         "launch__shared_mem_per_block_dynamic", "inst_executed", "sm__inst_issued.avg.pct_of_peak_sustained_active",
-        "smsp__average_warp_latency_per_inst_issued.ratio", "sm__cycles_active.avg"]
+        "smsp__average_warp_latency_per_inst_issued.ratio", "sm__cycles_active.avg",
+        "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_tensor.sum", "sm__inst_executed_pipe_fma.sum", "sm__inst_executed_pipe_lsu.sum",
+        "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum", "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum"]
 for r in rows[2:]:
     print("==", r[hdr.index("Kernel Name")][:100])
     for w in WANT:
