@@ -205,7 +205,9 @@ __device__ void prefix_fill_tables(const PrefixTables& tb, const float* x, int T
   const int tid = threadIdx.x, NT = blockDim.x;
   const int first = start == 1 ? 0 : start;        // row 0 is read only for the empty prefix (start == 1)
   const int TP = xk_pitch(T);
-  if (xt) {
+  if (tb.xk == nullptr) {
+    // long utterance: the recursion reads the candidates' rows of the transposed table directly
+  } else if (xt) {
     // transposed posteriors: candidate k's column is the contiguous row xt[cand[k]][0:T] -- a warp reads 32
     // consecutive frames of one candidate (one 128-byte line) and scatters them down column k of xk
     const int lane = tid & 31, warp = tid >> 5, nw = NT >> 5;
@@ -258,6 +260,50 @@ __device__ void prefix_recursion(const PrefixTables& tb, int T, int K, int prefi
     psi = np_logaddexp(psi, __fadd_rn(phi, xe));                // ctc.py:96
     rn = n0; rb = n1;
     ro[t * st_t] = n0; ro[t * st_t + 1] = n1;
+  }
+  psi_out[k] = psi;
+}
+
+// The same recursion for utterances whose [32][T'] candidate table does not fit in shared memory: the lane reads its
+// candidate's posteriors from a global row (`xcol` = row cand[k] of the transposed table), eight frames ahead of their
+// use.  Same values, same arithmetic; a function of its own so that the common path above keeps its code.
+__device__ __noinline__ void prefix_recursion_global(const PrefixTables& tb, int T, int K, int prefix_len, int last,
+                                                     const int* cand_sm, float* psi_out, float* r_out, long long st_t,
+                                                     long long st_k, const float* xt, long long xt_ld) {
+  const int k = threadIdx.x & 31;
+  if (k >= K) return;
+  const float* xcol = xt + (long long)cand_sm[k] * xt_ld;
+  const int start = max(1, prefix_len);
+  const bool same = cand_sm[k] == last;
+  float* ro = r_out + k * st_k;
+  for (int t = 0; t < min(start, T); ++t) { ro[t * st_t] = kLogZero; ro[t * st_t + 1] = kLogZero; }
+  float rn = kLogZero, rb = kLogZero;
+  if (prefix_len == 0) rn = __ldg(xcol);
+  float psi = rn;
+  if (start - 1 < T) ro[(start - 1) * st_t] = rn;
+  const float* phis = same ? tb.phiS : tb.phiD;
+  constexpr int PF = 8;
+  float q[PF];
+#pragma unroll
+  for (int u = 0; u < PF; ++u) q[u] = start + u < T ? __ldg(xcol + start + u) : 0.f;
+  for (int t0 = start; t0 < T; t0 += PF) {
+    float nq[PF];
+#pragma unroll
+    for (int u = 0; u < PF; ++u) nq[u] = t0 + PF + u < T ? __ldg(xcol + t0 + PF + u) : 0.f;
+#pragma unroll
+    for (int u = 0; u < PF; ++u) {
+      const int t = t0 + u;
+      if (t < T) {
+        const float phi = phis[t], xe = q[u], xbt = tb.xb[t];
+        const float n0 = __fadd_rn(np_logaddexp(rn, phi), xe);
+        const float n1 = __fadd_rn(np_logaddexp(rb, rn), xbt);
+        psi = np_logaddexp(psi, __fadd_rn(phi, xe));
+        rn = n0; rb = n1;
+        ro[t * st_t] = n0; ro[t * st_t + 1] = n1;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < PF; ++u) q[u] = nq[u];
   }
   psi_out[k] = psi;
 }
@@ -374,16 +420,24 @@ __global__ void __launch_bounds__(kBeamNT) beam_step_kernel(b2asr_beam_io io) {
       BT(2);
       const int Tp = (T + 3) / 4 * 4;
       float* base = smf + Vp;
-      const size_t xkf = (size_t)xk_pitch(T) * 32;
-      PrefixTables tb{base, base + xkf, base + xkf + Tp, base + xkf + 2 * Tp};
+      // long utterances (V + 35 T' floats beyond the 200 KB the launch may ask for): the launch carries shared memory
+      // for the three per-frame vectors only and the [32][T'] candidate table stays in the transposed global copy
+      unsigned dyn_smem;
+      asm("mov.u32 %0, %%dynamic_smem_size;" : "=r"(dyn_smem));
+      const bool xk_global = ((size_t)Vp + prefix_smem_floats(T)) * sizeof(float) > dyn_smem;
+      const size_t xkf = xk_global ? 0 : (size_t)xk_pitch(T) * 32;
+      PrefixTables tb{xk_global ? nullptr : base, base + xkf, base + xkf + Tp, base + xkf + 2 * Tp};
       const float* r_prev = io.r_in + (long long)row * T * 2;
       prefix_fill_tables(tb, io.x_ctc, T, V, r_prev, cand_sm, K, max(1, plen), io.x_ctc_t, io.x_ctc_t_ld);
       __syncthreads();
       BT(3);
       // ---- prefix scores of prefix+[c] (ctc.py:65-101) ------------------------------------------------
-      if (tid < 32)
-        prefix_recursion(tb, T, K, plen, (int)io.last_in[row], cand_sm, psi_sm,
-                         io.r_all + (long long)row * T * K * 2, 2, (long long)T * 2);   // [K][T][2]: a survivor's rows are contiguous
+      if (tid < 32) {
+        float* rall = io.r_all + (long long)row * T * K * 2;    // [K][T][2]: a survivor's rows are contiguous
+        if (!xk_global) prefix_recursion(tb, T, K, plen, (int)io.last_in[row], cand_sm, psi_sm, rall, 2, (long long)T * 2);
+        else prefix_recursion_global(tb, T, K, plen, (int)io.last_in[row], cand_sm, psi_sm, rall, 2, (long long)T * 2,
+                                     io.x_ctc_t, io.x_ctc_t_ld);
+      }
       __syncthreads();
       BT(4);
       // ---- fusion (asr.py:222-229): separate fp32 multiply and add roundings, as torch does -----------
@@ -577,6 +631,8 @@ extern "C" int b2asr_beam_step(const b2asr_beam_io* io, void* stream) {
     B2_REQUIRE(a.K >= 1 && a.K <= kMaxK && a.K <= a.V && a.T > 0, B2ASR_EUNSUPPORTED, "beam_step: K=%d CTC candidates (1..%d), T=%d", a.K, kMaxK, a.T);
     B2_REQUIRE(a.r_in && a.r_out && a.ctc_prob_in && a.cand && a.psi && a.r_all, B2ASR_EINVAL, "beam_step: joint CTC needs r_in/r_out/ctc_prob_in/cand/psi/r_all");
     floats += prefix_smem_floats(a.T);
+    if (floats * sizeof(float) > 200 * 1024 && a.x_ctc_t)          // long utterance: candidate table read from x_ctc_t
+      floats = (size_t)((a.V + 3) / 4 * 4) + 3 * (size_t)((a.T + 3) / 4 * 4);
   }
   const size_t prune = (size_t)4 * a.n * a.n + 2 * a.n + (size_t)a.n * (a.x_ctc ? a.K : 0) + 2 + 2 * (size_t)a.n;
   if (floats < prune) floats = prune;

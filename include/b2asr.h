@@ -269,7 +269,9 @@ typedef struct b2asr_beam_io {
   const float* att_lse;    /* [n] or NULL */
   const float* lm_lse;     /* [n] or NULL */
   /* optional: x_ctc transposed, [V,T] with row pitch x_ctc_t_ld >= T (multiple of 4 floats), or NULL.  With it the
-   * per-step gather of the K candidates' frame columns reads K contiguous rows instead of T*K scattered sectors. */
+   * per-step gather of the K candidates' frame columns reads K contiguous rows instead of T*K scattered sectors, and
+   * utterances whose frame tables exceed the kernel's shared memory (V + 35 T floats > 200 KB) are still decoded: the
+   * candidates' rows are then read from this table directly (without it such a call returns B2ASR_EUNSUPPORTED). */
   const float* x_ctc_t; int64_t x_ctc_t_ld;
 } b2asr_beam_io;
 

@@ -111,6 +111,8 @@ CASES = [
     (5000, 400, 20, 12, 0.5, 0.0, 0.0),
     (40, 30, 1, 8, 0.5, 0.0, 2.0),       # beam 1 returns at the first <eos> (asr.py:246-247)
     (40, 30, 1, 6, 0.0, 0.0, -5.0),      # beam 1, never finishes
+    (5000, 1500, 6, 5, 0.5, 0.0, 0.0),   # T' beyond the shared-memory table (V + 35 T' floats > 200 KB): candidate
+    (31, 2000, 4, 5, 0.5, 0.3, 1.0),     # columns are read from the transposed posteriors in global memory
 ]
 
 
