@@ -215,15 +215,47 @@ __global__ void __launch_bounds__(256) linear_lse_kernel(const b2asr_linear_lse 
   __syncthreads();
   if (!is_last) return;
   __threadfence();
-  for (int b = w; b < a.B; b += 8) {
-    const float* pr = a.part + (long long)b * ncta * 2;
-    float m = -INFINITY;
-    for (int j = lane; j < ncta; j += 32) m = fmaxf(m, __ldcg(pr + 2 * j));
-    m = warp_max(m);
-    float s = 0.f;
-    for (int j = lane; j < ncta; j += 32) s += __ldcg(pr + 2 * j + 1) * ex2((__ldcg(pr + 2 * j) - m) * kLog2e);
-    s = warp_sum(s);
-    if (lane == 0) a.lse[b] = m + logf(s);
+  constexpr int kPairs = 12;                  // (max, sum) pairs a lane holds per row: ncta <= 384, i.e. V <= 6144
+  if (ncta <= 32 * kPairs && a.B <= 32) {
+    // every load of the warp's (up to four) rows is issued before the first is used: the combine is ONE round trip
+    // to L2 instead of two per row (it sat at the end of both chains of a decode step).  Same operations in the same
+    // order as the loop below, so the result is bit-identical.
+    float2 pv[4][kPairs];
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const int b = w + 8 * r;
+      const float2* pr = reinterpret_cast<const float2*>(a.part) + (long long)min(b, a.B - 1) * ncta;
+#pragma unroll
+      for (int q = 0; q < kPairs; ++q) {
+        const int j = lane + 32 * q;
+        pv[r][q] = (b < a.B && j < ncta) ? __ldcg(pr + j) : make_float2(-INFINITY, 0.f);
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const int b = w + 8 * r;
+      if (b >= a.B) break;
+      float m = -INFINITY;
+#pragma unroll
+      for (int q = 0; q < kPairs; ++q) if (lane + 32 * q < ncta) m = fmaxf(m, pv[r][q].x);
+      m = warp_max(m);
+      float sum = 0.f;
+#pragma unroll
+      for (int q = 0; q < kPairs; ++q) if (lane + 32 * q < ncta) sum += pv[r][q].y * ex2((pv[r][q].x - m) * kLog2e);
+      sum = warp_sum(sum);
+      if (lane == 0) a.lse[b] = m + logf(sum);
+    }
+  } else {
+    for (int b = w; b < a.B; b += 8) {
+      const float* pr = a.part + (long long)b * ncta * 2;
+      float m = -INFINITY;
+      for (int j = lane; j < ncta; j += 32) m = fmaxf(m, __ldcg(pr + 2 * j));
+      m = warp_max(m);
+      float s = 0.f;
+      for (int j = lane; j < ncta; j += 32) s += __ldcg(pr + 2 * j + 1) * ex2((__ldcg(pr + 2 * j) - m) * kLog2e);
+      s = warp_sum(s);
+      if (lane == 0) a.lse[b] = m + logf(s);
+    }
   }
   if (tid == 0) *a.ticket = 0u;                                   // re-armed for the next step
 }
