@@ -391,11 +391,11 @@ def train_workload_leg(name, dev, steps, warmup, tf_rate):
         return e0.elapsed_time(e1)
 
     run_e2e(2)                                  # untimed: the prefetcher's stream and the allocator's blocks for the per-step copies
-    ms_e = run_e2e(steps)
+    ms_e = min(run_e2e(steps), run_e2e(steps))  # these short legs (5 steps) are at the mercy of one host hiccup: best of two passes
     B = w["batch"]
     out = {"value": B * steps / (ms * 1e-3), "unit": "utterances/s", "ms_per_step": ms / steps,
            "e2e": {"value": B * steps / (ms_e * 1e-3), "unit": "utterances/s", "ms_per_step": ms_e / steps,
-                   "h2d_bytes_per_step": host[0][0].numel() * 4 + host[0][1].numel() * 8},
+                   "h2d_bytes_per_step": host[0][0].numel() * 4 + host[0][1].numel() * 8, "passes": "best of 2"},
            "steps": steps, "warmup": warmup, "tf_rate": tf_rate, "batch": B, "frames": w["t_hi"], "vocab": w["vocab"],
            "feature_dim": w["d_in"], "encoder": w["cfg"]["encoder"]["enc_type"], "gpu_launches": launches,
            "params": sum(p.numel() for p in model.parameters())}
