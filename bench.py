@@ -11,6 +11,7 @@ fbank+delta, V=31 chars, pBLSTM 5x320 -> T'=400, location attention 300, decoder
 tf_rate 1.0, Adadelta).  Prints ONE JSON line (rank 0).
 """
 import argparse
+import gc
 import importlib
 import json
 import math
@@ -381,13 +382,18 @@ def train_workload_leg(name, dev, steps, warmup, tf_rate):
 
     def run_e2e(n):
         torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for x, y in solver.DevicePrefetcher((host[i % N_BATCHES] for i in range(n)), dev):
-            out = ts.step(x, y, tf_rate=tf_rate)
-            float(out["loss"])
-        e1.record()
-        torch.cuda.synchronize()
+        gc.collect()
+        gc.disable()                            # a generation-2 collection inside the loop is tens of ms of host time,
+        try:                                    # which the per-step loss read-back turns into GPU idle time
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for x, y in solver.DevicePrefetcher((host[i % N_BATCHES] for i in range(n)), dev):
+                out = ts.step(x, y, tf_rate=tf_rate)
+                float(out["loss"])
+            e1.record()
+            torch.cuda.synchronize()
+        finally:
+            gc.enable()
         return e0.elapsed_time(e1)
 
     run_e2e(2)                                  # untimed: the prefetcher's stream and the allocator's blocks for the per-step copies
@@ -585,12 +591,17 @@ def run_native(args):
         host->device copies on a side stream under step i; every copy and every loss read-back is inside the timed
         region (the first copy is issued after the start event)."""
         barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for x, y in solver.DevicePrefetcher(((host[i % N_BATCHES][0], host[i % N_BATCHES][1]) for i in range(steps)), dev):
-            out = ts.step(x, y, tf_rate=1.0)
-            float(out["loss"])
-        e1.record()
+        gc.collect()
+        gc.disable()                            # a generation-2 collection inside the loop is tens of ms of host time,
+        try:                                    # which the per-step loss read-back turns into GPU idle time
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for x, y in solver.DevicePrefetcher(((host[i % N_BATCHES][0], host[i % N_BATCHES][1]) for i in range(steps)), dev):
+                out = ts.step(x, y, tf_rate=1.0)
+                float(out["loss"])
+            e1.record()
+        finally:
+            gc.enable()
         barrier()
         ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
         if world > 1:
