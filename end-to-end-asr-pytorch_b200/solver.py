@@ -351,6 +351,12 @@ class Trainer(Solver):
         # enter the same number of gradient all-reduces
         rank, world = _dist()
         usable = (len(self.train_set) // world) * world
+        # everything built so far (model, data set, configuration) lives for the whole run: moved out of the garbage
+        # collector's generations, its periodic full passes stay short -- with the loss read back every step a long
+        # host pause is GPU idle time
+        import gc
+        gc.collect()
+        gc.freeze()
         while self.step < self.max_step:
             def mine():
                 for i, (x, y) in enumerate(self.train_set):
