@@ -197,3 +197,35 @@ def test_upstream_pickled_model_decodes_on_the_gpu(cuda, tmp_path):
     with torch.no_grad():
         hyps = model.beam_decode(g["x"].to(cuda), g["decode_step"], g["state_len"], g["beam"])
     assert [h.outIndex for h in hyps] == [r["tokens"] for r in g["hyps"]]
+
+
+@pytest.mark.parametrize("quantum,ctc_w", [(0.5, 0.0), (4.0, 0.0), (1e9, 0.0), (0.5, 0.5)])
+def test_topk_fast_path_equals_bisection_under_ties(cuda, quantum, ctc_w):
+    """cta_topk has two paths (csrc/beam.cu): candidates above a bound taken from the threads' local maxima and ranked
+    exactly (vocabularies <= 6144), and the 32-round CTA bisection (larger vocabularies, or more than 256 entries at or
+    above the bound).  The same search is run at V=5000 and embedded in V=7000 (extra entries -inf / log 0): tokens and
+    scores must agree exactly, with scores quantised so that ties at the k-th value are the rule (quantum 1e9: ALL
+    entries equal -- the fast path overflows its 256-entry buffer and falls back)."""
+    beam = _m("beam")
+    V, V2, n, steps, M, T = 5000, 7000, 8, 6, 8, 40
+    g = torch.Generator().manual_seed(11)
+    att = F.log_softmax(torch.randn(steps, M, V, generator=g) * 2, dim=-1)
+    att = torch.round(att / quantum) * quantum
+    x_ctc = F.log_softmax(torch.randn(T, V, generator=g) * 2, dim=-1) if ctc_w > 0 else None
+    runs = []
+    for vv in (V, V2):
+        a = torch.full((steps, M, vv), -float("inf"))
+        a[:, :, :V] = att
+        xc = None
+        if x_ctc is not None:
+            xc = torch.full((T, vv), -1e30)
+            xc[:, :V] = x_ctc
+        bs = beam.BeamSearch(vv, n, steps, cuda, x_ctc=xc, ctc_weight=ctc_w, lm_weight=0.0)
+        a_d = a.to(cuda)
+        for t in range(steps):
+            bs.step(a_d[t].index_select(0, bs.last_tokens % M).contiguous(), None)
+        runs.append(bs.results())
+    got, want = runs
+    assert [h.outIndex for h in got] == [h.outIndex for h in want]
+    for h, e in zip(got, want):
+        assert [float(s) for s in h.output_scores] == [float(s) for s in e.output_scores]
