@@ -378,6 +378,7 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_fwd_mma_kernel(const SeqArgs a) 
   const int st_half = ((ul >> 2) * BS + row) * 8 + (ul & 3);
   float c = 0.f;
   unsigned phase = 0;
+  bool dead = false;
   long long cyc_wait = 0, cyc_mac = 0, cyc_rest = 0;
   __syncthreads();
   cluster_arrive();
@@ -408,7 +409,9 @@ __global__ void __launch_bounds__(H, 1) lstm_cl_fwd_mma_kernel(const SeqArgs a) 
     }
     const long long c0 = clock64();
     if (s > 0) {                              // h_{t-1}: all 16 slices have landed in h_s[p]
-      if (!mbar_wait_bounded(&full[p], (phase >> p) & 1u)) { atomicExch(a.status, 1); return; }
+      // a timed-out wait (status word, checked by the caller) must not leave the partner warp at its named barrier
+      // or the peers without this CTA's slices: keep walking on whatever is in the buffer
+      if (!dead && !mbar_wait_bounded(&full[p], (phase >> p) & 1u)) { atomicExch(a.status, 1); dead = true; }
       phase ^= 1u << p;
       if (tid == 0) mbar_expect_tx(&full[p], NCL * CH * 4);    // re-arm for frame s+2
     }
